@@ -1,0 +1,101 @@
+"""CPU: the C oracle (oracle/ba_oracle.c) against golden vectors produced by the reference
+itself (tests/golden/make_golden.py imports reference src/geom/ba.py on CPU)."""
+import numpy as np
+import pytest
+
+import synth
+from helpers import STATE_RTOL, load_golden, rel, sign_normalise
+from oracle import oracle
+
+
+@pytest.mark.parametrize("name", ["A", "R"])
+def test_ba_geom_mode_matches_reference_fp64(name):
+    g, z, kw = load_golden(name)
+    o = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj,
+                  g.t0, g.t1, g.iters, g.lm, g.ep, mode=oracle.MODE_GEOM_PY, precision="f64")
+    assert o.fail == 0
+    # same algorithm in the same precision: far inside the 1e-4 bar
+    assert rel(sign_normalise(o.poses), sign_normalise(z["poses_f64"])) < 1e-8
+    assert rel(o.disps, z["disps_f64"].reshape(o.disps.shape)) < 1e-7
+
+
+@pytest.mark.parametrize("name", ["A", "R"])
+def test_ba_geom_mode_fp32_within_bar(name):
+    g, z, kw = load_golden(name)
+    o = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj,
+                  g.t0, g.t1, g.iters, g.lm, g.ep, mode=oracle.MODE_GEOM_PY, precision="f32")
+    for ref in ("f32", "f64"):
+        assert rel(sign_normalise(o.poses), sign_normalise(z["poses_" + ref])) < STATE_RTOL
+        assert rel(o.disps, z["disps_" + ref].reshape(o.disps.shape)) < STATE_RTOL
+
+
+@pytest.mark.parametrize("name", ["A", "R"])
+def test_dspo_matches_reference(name):
+    g, z, kw = load_golden(name)
+    synth.with_mono_prior(g, seed=kw["seed"] + 1)
+    tg = np.ascontiguousarray(g.targets.transpose(0, 2, 3, 1))
+    wg = np.ascontiguousarray(g.weights.transpose(0, 2, 3, 1))
+    for prec, tol in (("f64", 1e-6), ("f32", STATE_RTOL)):
+        disps, sc, sh = g.disps, g.scales, g.shifts
+        for _ in range(2):
+            o = oracle.dspo(g.poses, disps, g.intrinsics, tg, wg, g.eta, g.ii, g.jj, g.mono_disps, sc, sh,
+                            g.valid_depth_mask, 0, g.lm, g.ep, g.alpha, interleaved=True, precision=prec)
+            assert o.fail == 0
+            disps, sc, sh = o.disps, o.scales, o.shifts
+        wq = np.stack([sc, sh], -1)
+        assert rel(disps, z["dspo_disps_f64"]) < tol
+        assert rel(wq, z["dspo_wqs_f64"]) < tol
+
+
+def test_planar_and_interleaved_layouts_agree():
+    g = synth.with_mono_prior(synth.make_graph(5, 8, 1, seed=2, ht=8, wd=12))
+    tg = np.ascontiguousarray(g.targets.transpose(0, 2, 3, 1))
+    wg = np.ascontiguousarray(g.weights.transpose(0, 2, 3, 1))
+    a = oracle.dspo(g.poses, g.disps, g.intrinsics, tg, wg, g.eta, g.ii, g.jj, g.mono_disps, g.scales, g.shifts,
+                    g.valid_depth_mask, 0, 1e-4, 0.1, 0.01, interleaved=True)
+    b = oracle.dspo(g.poses, g.disps, g.intrinsics, g.targets, g.weights, g.eta, g.ii, g.jj, g.mono_disps,
+                    g.scales, g.shifts, g.valid_depth_mask, 0, 1e-4, 0.1, 0.01, interleaved=False)
+    np.testing.assert_array_equal(a.disps, b.disps)
+
+
+def test_modes_differ_as_surveyed():
+    """the two reference implementations do not agree to 1e-4 (D1, D2)."""
+    g, z, kw = load_golden("A")
+    a = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj,
+                  g.t0, g.t1, 1, g.lm, g.ep, mode=oracle.MODE_DROID_CUDA, precision="f64")
+    b = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj,
+                  g.t0, g.t1, 1, g.lm, g.ep, mode=oracle.MODE_GEOM_PY, precision="f64")
+    assert rel(a.dx, b.dx) > 1e-3
+    assert rel(a.dz, b.dz) > 1e-3
+
+
+def test_index_structures_and_flags():
+    g = synth.make_graph(7, 12, 1, seed=5, ht=8, wd=12, t0=2)
+    o = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj,
+                  g.t0, g.t1, 1, 1e-4, 0.1, mode=oracle.MODE_DROID_CUDA, debug=True)
+    kx = np.unique(np.concatenate([np.arange(g.t0, g.t1), g.ii]))
+    np.testing.assert_array_equal(o.kx, kx)
+    assert o.dx.shape == (g.t1 - g.t0, 6) and o.dz.shape == (len(kx), g.hw)
+    # symmetric up to fp32 rounding of (E_r Q) E_s^T vs (E_s Q) E_r^T, as in the reference
+    np.testing.assert_allclose(o.M, o.M.T, rtol=1e-4, atol=1e-5)
+    # motion_only leaves disparities alone; depth_only leaves poses alone
+    m = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj,
+                  g.t0, g.t1, 2, 1e-4, 0.1, motion_only=True)
+    np.testing.assert_array_equal(m.disps, g.disps)
+    assert rel(m.poses, g.poses) > 0
+    d = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj,
+                  g.t0, g.t1, 2, 1e-4, 0.1, depth_only=True)
+    np.testing.assert_array_equal(d.poses, g.poses)
+    assert rel(d.disps, g.disps) > 0
+    # fixed poses never move
+    np.testing.assert_array_equal(o.poses[: g.t0], g.poses[: g.t0])
+
+
+def test_non_spd_gives_zero_update():
+    """Reference contract: failed factorisation -> zero pose update (droid_kernels.cu:1207-1210)."""
+    g = synth.make_graph(5, 8, 1, seed=7, ht=8, wd=12)
+    o = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj,
+                  g.t0, g.t1, 1, -2.0, 0.0, motion_only=True)  # lm = -2 flips the diagonal sign
+    assert o.fail == 1
+    np.testing.assert_array_equal(o.dx, 0)
+    np.testing.assert_array_equal(o.poses, g.poses)
