@@ -1,0 +1,479 @@
+// gba_api.cu -- host side of libgba.so: context, launch sequencing, the extern "C" boundary
+// declared in include/gba.h.  No torch types, no CPU compute path.
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "../../include/gba.h"
+#include "gba_common.cuh"
+#include "gba_dspo.cuh"
+#include "gba_kernels.cuh"
+#include "gba_solver.cuh"
+
+static thread_local char g_create_err[512] = "";
+
+struct gba_ctx {
+  int device, N_max, E_max, ht, wd, HW, sm_count;
+  // index structures
+  int *kx, *fmap, *deg, *eptr, *eidx, *ek;
+  unsigned long long *goff;
+  Status *st_d, *st_h;
+  // workspaces
+  EdgeGeo *geo;
+  float *hpart, *edge_hv, *Q, *W, *gram, *dx, *dzbuf, *dspo_part, *dwq;
+  size_t gram_cap, sys_cap;
+  double *sys, *invL;
+  int *tslot, *colrows, *colcnt, *fail, *dspo_bad;
+  unsigned char *tmask;
+  int nT_max, hpart_chunks;
+  // state of the current call
+  BaParams p;
+  cudaStream_t stream;
+  int begun, launches, variant, gsplit, total_fail, last_P;
+  size_t sys_count;
+  char err[512];
+};
+
+static int fail_msg(gba_ctx *c, int code, const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(c ? c->err : g_create_err, 512, fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define CK(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess) return fail_msg(c, GBA_ECUDA, "%s failed: %s", #call, cudaGetErrorString(e_)); \
+  } while (0)
+
+#define LAUNCH_CHECK(name)                                                                         \
+  do {                                                                                             \
+    c->launches++;                                                                                 \
+    cudaError_t e_ = cudaGetLastError();                                                           \
+    if (e_ != cudaSuccess) return fail_msg(c, GBA_ECUDA, "launch of %s failed: %s", name, cudaGetErrorString(e_)); \
+  } while (0)
+
+template <typename T>
+static cudaError_t dalloc(T **p, size_t n) {
+  return cudaMalloc((void **)p, std::max<size_t>(n, 1) * sizeof(T));
+}
+
+static const int kSolverSmem = 2 * GBA_NB * (GBA_NB + 1) * (int)sizeof(double);
+static const int kGramSmemMax = 200 * 1024;
+static const int kTriSmemMax = 200 * 1024;
+
+extern "C" const char *gba_last_error(const gba_ctx *c) { return c ? c->err : g_create_err; }
+
+extern "C" void gba_destroy(gba_ctx *c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  void *ptrs[] = {c->kx, c->fmap, c->deg, c->eptr, c->eidx, c->ek, c->goff, c->st_d, c->geo, c->hpart, c->edge_hv,
+                  c->Q, c->W, c->gram, c->dx, c->dzbuf, c->dspo_part, c->dwq, c->sys, c->invL, c->tslot, c->colrows, c->colcnt,
+                  c->fail, c->dspo_bad, c->tmask};
+  for (void *q : ptrs)
+    if (q) cudaFree(q);
+  if (c->st_h) cudaFreeHost(c->st_h);
+  free(c);
+}
+
+extern "C" int gba_create(gba_ctx **out, int device, int max_frames, int max_edges, int ht, int wd) {
+  gba_ctx *c = nullptr;
+  if (!out) return fail_msg(c, GBA_EINVAL, "out is NULL");
+  *out = nullptr;
+  if (max_frames < 2 || max_edges < 0 || ht < 1 || wd < 1)
+    return fail_msg(c, GBA_EINVAL, "bad sizes: frames %d edges %d grid %dx%d", max_frames, max_edges, ht, wd);
+  if ((ht * wd) % 4 != 0) return fail_msg(c, GBA_EINVAL, "ht*wd must be a multiple of 4 (got %d)", ht * wd);
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || device < 0 || device >= ndev) {
+    cudaGetLastError();
+    return fail_msg(c, GBA_ECUDA, "no usable CUDA device %d (found %d); libgba has no CPU path", device, ndev);
+  }
+  gba_ctx *ctx = (gba_ctx *)calloc(1, sizeof(gba_ctx));
+  c = ctx;
+  c->device = device;
+  c->N_max = max_frames;
+  c->E_max = max_edges;
+  c->ht = ht;
+  c->wd = wd;
+  c->HW = ht * wd;
+  const size_t N = max_frames, E = std::max(max_edges, 1), HW = c->HW;
+  c->nT_max = (6 * max_frames + GBA_NB - 1) / GBA_NB;
+  const size_t nT = c->nT_max, ld = nT * GBA_NB;
+  if (ld * sizeof(double) > (size_t)kTriSmemMax) {
+    free(ctx);
+    return fail_msg(nullptr, GBA_ECAPACITY, "max_frames %d too large for the single-CTA solve (limit %d)", max_frames,
+                    kTriSmemMax / 8 / 6);
+  }
+#define CKC(call)                                                                                  \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess) {                                                                       \
+      fail_msg(nullptr, GBA_ECUDA, "%s failed: %s", #call, cudaGetErrorString(e_));                \
+      gba_destroy(ctx);                                                                            \
+      return GBA_ECUDA;                                                                            \
+    }                                                                                              \
+  } while (0)
+  CKC(cudaSetDevice(device));
+  CKC(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device));
+  c->hpart_chunks = (int)((HW + 511) / 512);
+  c->gram_cap = std::min<size_t>((size_t)(6 * 64 + 8) * (6 * E + 8 * N), (size_t)1 << 30);
+  c->sys_cap = std::min<size_t>(nT * (nT + 1) / 2, (size_t)131072) * GBA_NB2 + ld;
+  CKC(dalloc(&c->kx, N));
+  CKC(dalloc(&c->fmap, N));
+  CKC(dalloc(&c->deg, N));
+  CKC(dalloc(&c->eptr, N + 1));
+  CKC(dalloc(&c->eidx, E));
+  CKC(dalloc(&c->ek, E));
+  CKC(dalloc(&c->goff, N));
+  CKC(dalloc(&c->st_d, 1));
+  CKC(cudaMallocHost((void **)&c->st_h, sizeof(Status)));
+  CKC(dalloc(&c->geo, E));
+  CKC(dalloc(&c->hpart, E * c->hpart_chunks * 32));
+  CKC(dalloc(&c->edge_hv, E * 32));
+  CKC(dalloc(&c->Q, N * HW));
+  CKC(dalloc(&c->W, N * HW));
+  CKC(dalloc(&c->gram, c->gram_cap));
+  CKC(dalloc(&c->dx, 6 * N));
+  CKC(dalloc(&c->dzbuf, N * HW));
+  CKC(dalloc(&c->dspo_part, N * c->hpart_chunks * 8));
+  CKC(dalloc(&c->dwq, 2 * N));
+  CKC(dalloc(&c->sys, c->sys_cap));
+  CKC(dalloc(&c->invL, nT * GBA_NB2));
+  CKC(dalloc(&c->tslot, nT * nT));
+  CKC(dalloc(&c->colrows, nT * nT));
+  CKC(dalloc(&c->colcnt, nT));
+  CKC(dalloc(&c->fail, 1));
+  CKC(dalloc(&c->dspo_bad, 1));
+  CKC(dalloc(&c->tmask, nT * nT));
+  CKC(cudaMemset(c->fail, 0, sizeof(int)));
+  CKC(cudaMemset(c->st_d, 0, sizeof(Status)));
+  CKC(cudaFuncSetAttribute(k_gram, cudaFuncAttributeMaxDynamicSharedMemorySize, kGramSmemMax));
+  CKC(cudaFuncSetAttribute(k_potrf_diag, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolverSmem));
+  CKC(cudaFuncSetAttribute(k_trsm, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolverSmem));
+  CKC(cudaFuncSetAttribute(k_syrk, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolverSmem));
+  CKC(cudaFuncSetAttribute(k_tri_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, kTriSmemMax));
+#undef CKC
+  *out = ctx;
+  return GBA_OK;
+}
+
+// ---- index build shared by BA and DSPO ---------------------------------------------------------
+static int build_index(gba_ctx *c, const int64_t *kx_global, int n_kx, bool want_tiles) {
+  BaParams &p = c->p;
+  cudaStream_t s = c->stream;
+  k_prep_frames<<<1, 1024, 0, s>>>(p, kx_global, n_kx);
+  LAUNCH_CHECK("k_prep_frames");
+  if (p.E > 0) {
+    k_prep_edges<<<(p.E + 255) / 256, 256, 0, s>>>(p);
+    LAUNCH_CHECK("k_prep_edges");
+  }
+  k_prep_scan<<<1, 1024, 0, s>>>(p);
+  LAUNCH_CHECK("k_prep_scan");
+  if (p.E > 0) {
+    k_prep_fill<<<(p.N * 32 + 255) / 256, 256, 0, s>>>(p);
+    LAUNCH_CHECK("k_prep_fill");
+  }
+  if (want_tiles) {
+    CK(cudaMemsetAsync(c->tmask, 0, (size_t)p.nT * p.nT, s));
+    k_tile_mark<<<p.N, 128, 0, s>>>(p, c->tmask);
+    LAUNCH_CHECK("k_tile_mark");
+    k_tile_fill<<<1, 1024, 0, s>>>(p, c->tmask, c->colrows, c->colcnt);
+    LAUNCH_CHECK("k_tile_fill");
+  }
+  CK(cudaMemcpyAsync(c->st_h, c->st_d, sizeof(Status), cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  const Status &st = *c->st_h;
+  if (st.err & 1) return fail_msg(c, GBA_EINVAL, "ii/jj (or kx) contain keyframe indices outside [0,%d)", p.N);
+  if (st.err & 4) return fail_msg(c, GBA_EINVAL, "an edge's source keyframe is missing from kx_global");
+  return GBA_OK;
+}
+
+extern "C" int gba_ba_begin(gba_ctx *c, float *poses, float *disps, const float *intrinsics, const float *disps_sens,
+                            const float *targets, const float *weights, const float *eta, const int64_t *ii,
+                            const int64_t *jj, int n_frames, int n_edges, int eta_rows, int t0, int t1, float lm,
+                            float ep, int motion_only, int depth_only, int mode, const int64_t *kx_global, int n_kx,
+                            const uint8_t *owned, void *stream) {
+  if (!c) return GBA_EINVAL;
+  c->begun = 0;
+  if (!poses || !disps || !intrinsics || !disps_sens || !eta || (n_edges > 0 && (!targets || !weights || !ii || !jj)))
+    return fail_msg(c, GBA_EINVAL, "NULL array argument");
+  if (n_frames < 1 || n_frames > c->N_max)
+    return fail_msg(c, GBA_ECAPACITY, "n_frames %d outside [1,%d]", n_frames, c->N_max);
+  if (n_edges < 0 || n_edges > c->E_max) return fail_msg(c, GBA_ECAPACITY, "n_edges %d outside [0,%d]", n_edges, c->E_max);
+  if (t0 < 0 || t1 <= t0 || t1 > n_frames)
+    return fail_msg(c, GBA_EINVAL, "optimised window [%d,%d) not inside [0,%d)", t0, t1, n_frames);
+  if (mode != GBA_MODE_DROID_CUDA && mode != GBA_MODE_GEOM_PY) return fail_msg(c, GBA_EINVAL, "unknown mode %d", mode);
+  CK(cudaSetDevice(c->device));
+  c->stream = (cudaStream_t)stream;
+  c->launches = 0;
+  c->total_fail = 0;
+  BaParams &p = c->p;
+  memset(&p, 0, sizeof(p));
+  p.poses = poses; p.disps = disps; p.intr = intrinsics; p.sens = disps_sens; p.targets = targets;
+  p.weights = weights; p.eta = eta; p.ii = ii; p.jj = jj;
+  p.N = n_frames; p.E = n_edges; p.HW = c->HW; p.wd = c->wd; p.t0 = t0; p.t1 = t1; p.P = t1 - t0;
+  p.mode = mode; p.motion_only = motion_only ? 1 : 0; p.depth_only = depth_only ? 1 : 0; p.lm = lm; p.ep = ep;
+  p.kx = c->kx; p.fmap = c->fmap; p.deg = c->deg; p.eptr = c->eptr; p.eidx = c->eidx; p.ek = c->ek;
+  p.owned = owned; p.goff = c->goff; p.st = c->st_d; p.geo = c->geo; p.hpart = c->hpart; p.edge_hv = c->edge_hv;
+  p.Q = c->Q; p.W = c->W; p.gram = c->gram; p.dx = c->dx; p.dz_out = c->dzbuf; p.sys = c->sys; p.tslot = c->tslot;
+  p.nT = (6 * p.P + GBA_NB - 1) / GBA_NB;
+  p.ld = p.nT * GBA_NB;
+  c->last_P = p.P;
+  int rc = build_index(c, kx_global, n_kx, true);
+  if (rc) return rc;
+  const Status &st = *c->st_h;
+  if (!motion_only && eta_rows != st.K)
+    return fail_msg(c, GBA_EINVAL, "eta has %d rows but the graph has K = %d depth keyframes", eta_rows, st.K);
+  if ((size_t)st.n_slots * GBA_NB2 + p.ld > c->sys_cap)
+    return fail_msg(c, GBA_ECAPACITY, "reduced system needs %d tiles, capacity exceeded", st.n_slots);
+  c->sys_count = (size_t)st.n_slots * GBA_NB2 + p.ld;
+  if (!motion_only) {
+    if (st.gram_floats > c->gram_cap)
+      return fail_msg(c, GBA_ECAPACITY, "Schur Gram buffers need %llu floats (capacity %zu); max out-degree %d",
+                      st.gram_floats, c->gram_cap, st.max_deg);
+    const int nb = (6 * st.max_deg + 1 + 7) / 8, RS = ((2 * nb + 7) & ~7) * 4;
+    if ((size_t)GRAM_T * RS * sizeof(float) > (size_t)kGramSmemMax)
+      return fail_msg(c, GBA_ECAPACITY, "out-degree %d too large for the shared-memory Gram tile", st.max_deg);
+  }
+  // launch shape of the streaming passes: largest CTA footprint that still gives >= 2 CTAs per SM
+  const int K = std::max(st.K, 1), want = 2 * c->sm_count;
+  const int foot[3] = {2048, 1024, 512};
+  c->variant = 2;
+  for (int v = 0; v < 3; v++)
+    if ((long long)K * ((c->HW + foot[v] - 1) / foot[v]) >= want) {
+      c->variant = v;
+      break;
+    }
+  p.nchunk = (c->HW + foot[c->variant] - 1) / foot[c->variant];
+  const int ntile = (c->HW + GRAM_T - 1) / GRAM_T;
+  c->gsplit = std::max(1, std::min(ntile, (3 * c->sm_count + K - 1) / K));
+  c->begun = 1;
+  return GBA_OK;
+}
+
+extern "C" int gba_ba_build(gba_ctx *c) {
+  if (!c || !c->begun) return c ? fail_msg(c, GBA_EINVAL, "gba_ba_build without gba_ba_begin") : GBA_EINVAL;
+  BaParams &p = c->p;
+  cudaStream_t s = c->stream;
+  const Status &st = *c->st_h;
+  CK(cudaSetDevice(c->device));
+  CK(cudaMemsetAsync(c->sys, 0, c->sys_count * sizeof(double), s));
+  if (p.ld > 6 * p.P) {
+    k_pad_diag<<<1, GBA_NB, 0, s>>>(p);
+    LAUNCH_CHECK("k_pad_diag");
+  }
+  if (p.E > 0) {
+    k_edge_geo<<<(p.E + 255) / 256, 256, 0, s>>>(p);
+    LAUNCH_CHECK("k_edge_geo");
+  }
+  if (st.K > 0) {
+    dim3 grid(p.nchunk, st.K);
+    if (c->variant == 0) k_linearize<256, 2><<<grid, 256, 0, s>>>(p);
+    else if (c->variant == 1) k_linearize<128, 2><<<grid, 128, 0, s>>>(p);
+    else k_linearize<128, 1><<<grid, 128, 0, s>>>(p);
+    LAUNCH_CHECK("k_linearize");
+  }
+  if (p.E > 0) {
+    k_edge_finish<<<(p.E + 127) / 128, 128, 0, s>>>(p);
+    LAUNCH_CHECK("k_edge_finish");
+  }
+  if (p.mode == GBA_MODE_GEOM_PY) {  // damping on H before the Schur complement (chol.py:66-68)
+    k_damp<<<(6 * p.P + 255) / 256, 256, 0, s>>>(p, p.lm, p.ep);
+    LAUNCH_CHECK("k_damp");
+  }
+  if (!p.motion_only && p.E > 0 && st.K > 0) {
+    if (c->gsplit > 1) CK(cudaMemsetAsync(c->gram, 0, (size_t)st.gram_floats * sizeof(float), s));
+    const int nb = (6 * st.max_deg + 1 + 7) / 8, RS = ((2 * nb + 7) & ~7) * 4;
+    k_gram<<<dim3(c->gsplit, st.K), GRAM_NT, (size_t)GRAM_T * RS * sizeof(float), s>>>(p);
+    LAUNCH_CHECK("k_gram");
+    k_schur<<<st.K, SCHUR_NT, (size_t)6 * (6 * st.max_deg + 1) * sizeof(float), s>>>(p);
+    LAUNCH_CHECK("k_schur");
+  }
+  return GBA_OK;
+}
+
+extern "C" int gba_ba_system(gba_ctx *c, double **buf, size_t *count) {
+  if (!c || !c->begun || !buf || !count) return GBA_EINVAL;
+  *buf = c->sys;
+  *count = c->sys_count;
+  return GBA_OK;
+}
+
+extern "C" int gba_ba_solve(gba_ctx *c) {
+  if (!c || !c->begun) return c ? fail_msg(c, GBA_EINVAL, "gba_ba_solve without gba_ba_begin") : GBA_EINVAL;
+  BaParams &p = c->p;
+  cudaStream_t s = c->stream;
+  const Status &st = *c->st_h;
+  CK(cudaSetDevice(c->device));
+  if (p.mode == GBA_MODE_DROID_CUDA) {  // damping after the Schur complement (droid_kernels.cu:1197,1407)
+    k_damp<<<(6 * p.P + 255) / 256, 256, 0, s>>>(p, p.lm, p.ep);
+    LAUNCH_CHECK("k_damp");
+  }
+  for (int kk = 0; kk < p.nT; kk++) {
+    k_potrf_diag<<<1, 256, kSolverSmem, s>>>(p, kk, c->invL, c->fail);
+    LAUNCH_CHECK("k_potrf_diag");
+    if (st.max_col > 0 && kk + 1 < p.nT) {
+      k_trsm<<<st.max_col, 256, kSolverSmem, s>>>(p, kk, c->invL, c->colrows, c->colcnt, c->fail);
+      LAUNCH_CHECK("k_trsm");
+      k_syrk<<<st.max_col * (st.max_col + 1) / 2, 256, kSolverSmem, s>>>(p, kk, c->colrows, c->colcnt, c->fail);
+      LAUNCH_CHECK("k_syrk");
+    }
+  }
+  k_tri_solve<<<1, 256, (size_t)p.ld * sizeof(double), s>>>(p, c->invL, c->colrows, c->colcnt, c->fail);
+  LAUNCH_CHECK("k_tri_solve");
+  if (!p.motion_only && st.K > 0) {
+    dim3 grid(p.nchunk, st.K);
+    if (c->variant == 0) k_backsub<256, 2><<<grid, 256, 0, s>>>(p);
+    else if (c->variant == 1) k_backsub<128, 2><<<grid, 128, 0, s>>>(p);
+    else k_backsub<128, 1><<<grid, 128, 0, s>>>(p);
+    LAUNCH_CHECK("k_backsub");
+  }
+  if (p.motion_only || !p.depth_only) {
+    k_pose_retr<<<(p.P + 127) / 128, 128, 0, s>>>(p);
+    LAUNCH_CHECK("k_pose_retr");
+  }
+  return GBA_OK;
+}
+
+extern "C" int gba_ba_end(gba_ctx *c, float *dx_out, float *dz_out) {
+  if (!c || !c->begun) return GBA_EINVAL;
+  if (dx_out)
+    CK(cudaMemcpyAsync(dx_out, c->dx, (size_t)6 * c->p.P * sizeof(float), cudaMemcpyDeviceToDevice, c->stream));
+  if (dz_out && !c->p.motion_only)
+    CK(cudaMemcpyAsync(dz_out, c->dzbuf, (size_t)c->st_h->K * c->HW * sizeof(float), cudaMemcpyDeviceToDevice,
+                       c->stream));
+  return GBA_OK;
+}
+
+extern "C" int gba_ba(gba_ctx *c, float *poses, float *disps, const float *intrinsics, const float *disps_sens,
+                      const float *targets, const float *weights, const float *eta, const int64_t *ii,
+                      const int64_t *jj, int n_frames, int n_edges, int eta_rows, int t0, int t1, int iters, float lm,
+                      float ep, int motion_only, int depth_only, int mode, float *dx_out, float *dz_out, void *stream) {
+  int rc = gba_ba_begin(c, poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, n_frames, n_edges,
+                        eta_rows, t0, t1, lm, ep, motion_only, depth_only, mode, nullptr, 0, nullptr, stream);
+  if (rc) return rc;
+  for (int it = 0; it < iters; it++) {
+    if ((rc = gba_ba_build(c))) return rc;
+    if ((rc = gba_ba_solve(c))) return rc;
+  }
+  return gba_ba_end(c, dx_out, dz_out);
+}
+
+// ---- DSPO stage 2 ------------------------------------------------------------------------------
+extern "C" int gba_dspo(gba_ctx *c, const float *poses, float *disps, const float *intrinsics, const float *targets,
+                        const float *weights, const float *eta, const int64_t *ii, const int64_t *jj,
+                        const float *mono_disps, float *scales, float *shifts, const uint8_t *valid_mask,
+                        int n_frames, int n_edges, int eta_rows, int ignore_frames, float lm, float ep, float alpha,
+                        int interleaved, void *stream) {
+  if (!c) return GBA_EINVAL;
+  c->begun = 0;
+  if (!poses || !disps || !intrinsics || !targets || !weights || !eta || !ii || !jj || !mono_disps || !scales ||
+      !shifts || !valid_mask)
+    return fail_msg(c, GBA_EINVAL, "NULL array argument");
+  if (n_frames < 1 || n_frames > c->N_max)
+    return fail_msg(c, GBA_ECAPACITY, "n_frames %d outside [1,%d]", n_frames, c->N_max);
+  if (n_edges < 1 || n_edges > c->E_max) return fail_msg(c, GBA_ECAPACITY, "n_edges %d outside [1,%d]", n_edges, c->E_max);
+  CK(cudaSetDevice(c->device));
+  c->stream = (cudaStream_t)stream;
+  c->launches = 0;
+  cudaStream_t s = c->stream;
+  BaParams &p = c->p;
+  memset(&p, 0, sizeof(p));
+  p.poses = const_cast<float *>(poses); p.disps = disps; p.intr = intrinsics; p.ii = ii; p.jj = jj;
+  p.N = n_frames; p.E = n_edges; p.HW = c->HW; p.wd = c->wd; p.t0 = 0; p.t1 = n_frames; p.P = n_frames;
+  p.mode = GBA_MODE_GEOM_PY;  // kx = unique(ii) (ba.py:139)
+  p.kx = c->kx; p.fmap = c->fmap; p.deg = c->deg; p.eptr = c->eptr; p.eidx = c->eidx; p.ek = c->ek;
+  p.goff = c->goff; p.st = c->st_d; p.geo = c->geo;
+  int rc = build_index(c, nullptr, 0, false);
+  if (rc) return rc;
+  const Status &st = *c->st_h;
+  if (eta_rows != st.K) return fail_msg(c, GBA_EINVAL, "eta has %d rows but unique(ii) has %d", eta_rows, st.K);
+  DspoParams d;
+  memset(&d, 0, sizeof(d));
+  d.poses = poses; d.disps = disps; d.intr = intrinsics; d.targets = targets; d.weights = weights; d.eta = eta;
+  d.mono = mono_disps; d.scales = scales; d.shifts = shifts; d.mask = valid_mask; d.ii = ii; d.jj = jj;
+  d.N = n_frames; d.E = n_edges; d.HW = c->HW; d.wd = c->wd; d.ignore_frames = ignore_frames;
+  d.interleaved = interleaved; d.lm = lm; d.ep = ep;
+  d.sqrt_alpha = sqrtf(alpha);  // torch.tensor(alpha).sqrt() is fp32 (ba.py:141)
+  d.kx = c->kx; d.eptr = c->eptr; d.eidx = c->eidx; d.st = c->st_d; d.geo = c->geo; d.Q = c->Q; d.W = c->W;
+  d.part = c->dspo_part; d.dwq = c->dwq; d.bad = c->dspo_bad;
+  d.nchunk = (c->HW + 511) / 512;
+  CK(cudaMemsetAsync(c->dspo_bad, 0, sizeof(int), s));
+  k_edge_geo<<<(p.E + 255) / 256, 256, 0, s>>>(p);
+  LAUNCH_CHECK("k_edge_geo");
+  dim3 grid(d.nchunk, st.K);
+  if (interleaved) k_dspo_lin<128, true><<<grid, 128, 0, s>>>(d);
+  else k_dspo_lin<128, false><<<grid, 128, 0, s>>>(d);
+  LAUNCH_CHECK("k_dspo_lin");
+  k_dspo_solve<<<1, 256, 0, s>>>(d);
+  LAUNCH_CHECK("k_dspo_solve");
+  k_dspo_update<128><<<grid, 128, 0, s>>>(d);
+  LAUNCH_CHECK("k_dspo_update");
+  return GBA_OK;
+}
+
+// ---- introspection ------------------------------------------------------------------------------
+extern "C" int gba_query(gba_ctx *c, gba_info *info) {
+  if (!c || !info) return GBA_EINVAL;
+  CK(cudaSetDevice(c->device));
+  CK(cudaMemcpyAsync(c->st_h, c->st_d, sizeof(Status), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  const Status &st = *c->st_h;
+  info->n_depth_frames = st.K;
+  info->n_poses = c->last_P;
+  info->max_out_degree = st.max_deg;
+  info->chol_failures = st.chol_fail;
+  info->n_tiles = c->p.nT;
+  info->n_active_tiles = st.n_slots;
+  info->kernel_launches = c->launches;
+  info->reserved = 0;
+  return GBA_OK;
+}
+
+extern "C" int gba_get(gba_ctx *c, int what, void *dst, size_t bytes) {
+  if (!c || !dst) return GBA_EINVAL;
+  CK(cudaSetDevice(c->device));
+  CK(cudaStreamSynchronize(c->stream));
+  const Status &st = *c->st_h;
+  const BaParams &p = c->p;
+  const void *src = nullptr;
+  size_t need = 0;
+  switch (what) {
+    case GBA_GET_KX: src = c->kx; need = (size_t)st.K * 4; break;
+    case GBA_GET_EPTR: src = c->eptr; need = (size_t)(st.K + 1) * 4; break;
+    case GBA_GET_EIDX: src = c->eidx; need = (size_t)p.E * 4; break;
+    case GBA_GET_EDGE_HV: src = c->edge_hv; need = (size_t)p.E * 32 * 4; break;
+    case GBA_GET_Q: src = c->Q; need = (size_t)st.K * p.HW * 4; break;
+    case GBA_GET_W: src = c->W; need = (size_t)st.K * p.HW * 4; break;
+    case GBA_GET_TILEMASK: src = c->tmask; need = (size_t)p.nT * p.nT; break;
+    case GBA_GET_SYSTEM: {
+      const size_t n = 6 * (size_t)p.P;
+      need = (n * n + n) * sizeof(double);
+      if (bytes < need) return fail_msg(c, GBA_EINVAL, "gba_get: buffer too small (%zu < %zu)", bytes, need);
+      std::vector<double> h(c->sys_count);
+      std::vector<int> slot((size_t)p.nT * p.nT);
+      CK(cudaMemcpy(h.data(), c->sys, c->sys_count * sizeof(double), cudaMemcpyDeviceToHost));
+      CK(cudaMemcpy(slot.data(), c->tslot, slot.size() * sizeof(int), cudaMemcpyDeviceToHost));
+      double *out = (double *)dst;
+      memset(out, 0, need);
+      for (size_t r = 0; r < n; r++)
+        for (size_t q = 0; q <= r; q++) {
+          const int sl = slot[(r / GBA_NB) * p.nT + q / GBA_NB];
+          if (sl >= 0) out[r * n + q] = h[(size_t)sl * GBA_NB2 + (r % GBA_NB) * GBA_NB + q % GBA_NB];
+        }
+      for (size_t r = 0; r < n; r++) out[n * n + r] = h[(size_t)st.n_slots * GBA_NB2 + r];
+      return GBA_OK;
+    }
+    default: return fail_msg(c, GBA_EINVAL, "gba_get: unknown selector %d", what);
+  }
+  if (bytes < need) return fail_msg(c, GBA_EINVAL, "gba_get: buffer too small (%zu < %zu)", bytes, need);
+  CK(cudaMemcpy(dst, src, need, cudaMemcpyDeviceToHost));
+  return GBA_OK;
+}

@@ -1,0 +1,166 @@
+// gba_common.cuh -- shared types and per-pixel math of the B200 dense-BA kernels.
+//
+// Not a port of the reference's src/lib/droid_kernels.cu: the reference accumulates a
+// 12x12 Hessian per pixel and materialises E rows in HBM (droid_kernels.cu:281-378); here
+// only the 21+6 entries of (H_jj, v_j) are accumulated per edge (J_i = -Ad^T J_j is applied
+// once per edge afterwards) and E rows never leave the SM.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define GBA_NB 64            // tile size of the reduced camera matrix (fp64)
+#define GBA_NB2 (GBA_NB * GBA_NB)
+
+// Per-edge geometry, rebuilt from the current poses at the start of every iteration.
+// Matches G_ij = T_j * T_i^-1 of droid_kernels.cu:96-107 / projective_ops.py:103.
+struct __align__(16) EdgeGeo {
+  float R[9];   // rotation of G_ij, row major
+  float t[3];   // translation of G_ij
+  int pi;       // ii - t0 if that pose is optimised, else -1
+  int pj;       // jj - t0 if that pose is optimised, else -1
+  int flags;    // bit0: stereo self edge (ii == jj): pose terms dropped (droid_kernels.cu:323,356)
+  int pad;
+};
+static_assert(sizeof(EdgeGeo) == 64, "EdgeGeo must be 64 bytes");
+
+struct Status {          // device -> host after the index build
+  int K;                 // depth keyframes
+  int max_deg;           // largest out-degree
+  int err;               // bit0 index out of range, bit1 capacity, bit2 kx_global mismatch
+  int n_tiles;           // tile rows
+  int n_slots;           // active lower tiles after fill
+  int max_col;           // max active sub-diagonal tiles in a tile column
+  int chol_fail;         // running count of failed factorisations
+  int pad;
+  unsigned long long gram_floats;  // total size of the per-frame Gram buffers
+};
+
+struct BaParams {
+  // caller arrays
+  float *poses, *disps;
+  const float *intr, *sens, *targets, *weights, *eta;
+  const int64_t *ii, *jj;
+  int N, E, HW, wd, t0, t1, P, mode, motion_only, depth_only;
+  float lm, ep;
+  // index structures
+  int *kx, *fmap, *deg, *eptr, *eidx, *ek;
+  const unsigned char *owned;
+  unsigned long long *goff;
+  Status *st;
+  // per-iteration workspaces
+  EdgeGeo *geo;
+  float *hpart;   // [E][nchunk][32]
+  float *edge_hv; // [E][32]
+  int nchunk;
+  float *Q, *W;   // [K][HW]
+  float *gram;
+  float *dx;      // [P][6]
+  float *dz_out;
+  // reduced system (tile packed, fp64)
+  double *sys;    // [n_slots][NB*NB] then rhs [ld]
+  int *tslot;     // [nT][nT]
+  int nT, ld;
+};
+
+__device__ __forceinline__ float ldg_stream(const float *p) { return __ldcs(p); }
+__device__ __forceinline__ float4 ldg_stream4(const float *p) { return __ldcs(reinterpret_cast<const float4 *>(p)); }
+
+// address of element (r, c), r >= c, of the tile-packed lower-triangular system
+__device__ __forceinline__ double *sys_at(const BaParams &p, int r, int c) {
+  const int tr = r / GBA_NB, tc = c / GBA_NB;
+  const int slot = p.tslot[tr * p.nT + tc];
+  return p.sys + (size_t)slot * GBA_NB2 + (r % GBA_NB) * GBA_NB + (c % GBA_NB);
+}
+
+// y = B x with B = -Ad(G_ij)^T  (J_i = B J_j; droid_kernels.cu:79-94,325-326; se3.h:58-67,84-86)
+template <typename T>
+__device__ __forceinline__ void apply_B(const float *R, const float *t, const T *x, T *y) {
+  // Ad^T [a;b] = [R^T a ; R^T (b - t x a)]
+  const T a0 = x[0], a1 = x[1], a2 = x[2];
+  const T c0 = x[3] - ((T)t[1] * a2 - (T)t[2] * a1);
+  const T c1 = x[4] - ((T)t[2] * a0 - (T)t[0] * a2);
+  const T c2 = x[5] - ((T)t[0] * a1 - (T)t[1] * a0);
+  y[0] = -((T)R[0] * a0 + (T)R[3] * a1 + (T)R[6] * a2);
+  y[1] = -((T)R[1] * a0 + (T)R[4] * a1 + (T)R[7] * a2);
+  y[2] = -((T)R[2] * a0 + (T)R[5] * a1 + (T)R[8] * a2);
+  y[3] = -((T)R[0] * c0 + (T)R[3] * c1 + (T)R[6] * c2);
+  y[4] = -((T)R[1] * c0 + (T)R[4] * c1 + (T)R[7] * c2);
+  y[5] = -((T)R[2] * c0 + (T)R[5] * c1 + (T)R[8] * c2);
+}
+
+// y = B^T x = -Ad(G_ij) x,  Ad [a;b] = [R a + t x (R b) ; R b]
+__device__ __forceinline__ void apply_Bt(const float *R, const float *t, const float *x, float *y) {
+  const float ra0 = R[0] * x[0] + R[1] * x[1] + R[2] * x[2];
+  const float ra1 = R[3] * x[0] + R[4] * x[1] + R[5] * x[2];
+  const float ra2 = R[6] * x[0] + R[7] * x[1] + R[8] * x[2];
+  const float rb0 = R[0] * x[3] + R[1] * x[4] + R[2] * x[5];
+  const float rb1 = R[3] * x[3] + R[4] * x[4] + R[5] * x[5];
+  const float rb2 = R[6] * x[3] + R[7] * x[4] + R[8] * x[5];
+  y[0] = -(ra0 + (t[1] * rb2 - t[2] * rb1));
+  y[1] = -(ra1 + (t[2] * rb0 - t[0] * rb2));
+  y[2] = -(ra2 + (t[0] * rb1 - t[1] * rb0));
+  y[3] = -rb0;
+  y[4] = -rb1;
+  y[5] = -rb2;
+}
+
+// Linearisation of one edge pixel (Appendix A of SURVEY.md).
+//   droid: droid_kernels.cu:290-319,345-352 (MIN_DEPTH 0.25: d = 0, w = 0 behind it)
+//   geom : projective_ops.py:44,112 (valid = Z > 0.2; Z < 0.1 -> d = 1)
+// J_j(u) = (ju0, 0, ju2, ju3, ju4, ju5), J_j(v) = (0, jv1, jv2, jv3, jv4, jv5).
+struct PixLin {
+  float ru, rv, wu, wv, jzu, jzv;
+  float ju0, ju2, ju3, ju4, ju5;
+  float jv1, jv2, jv3, jv4, jv5;
+};
+
+__device__ __forceinline__ void pix_linearize(const float *__restrict__ R, const float *__restrict__ t, float fx,
+                                              float fy, float cx, float cy, int mode, float x0, float y0, float z,
+                                              float tu, float tv, float wgu, float wgv, PixLin &o) {
+  const float X = fmaf(R[0], x0, fmaf(R[1], y0, R[2])) + t[0] * z;
+  const float Y = fmaf(R[3], x0, fmaf(R[4], y0, R[5])) + t[1] * z;
+  const float Z = fmaf(R[6], x0, fmaf(R[7], y0, R[8])) + t[2] * z;
+  bool invalid;
+  float d;
+  if (mode == 0) {
+    invalid = Z < 0.25f;
+    d = invalid ? 0.0f : __frcp_rn(Z);
+  } else {
+    invalid = !(Z > 0.2f);
+    d = (Z < 0.1f) ? 1.0f : __frcp_rn(Z);
+  }
+  const float d2 = d * d;
+  o.wu = invalid ? 0.0f : 0.001f * wgu;
+  o.wv = invalid ? 0.0f : 0.001f * wgv;
+  o.ru = tu - fmaf(fx * d, X, cx);
+  o.rv = tv - fmaf(fy * d, Y, cy);
+  const float fxd = fx * d, fyd = fy * d, fxd2 = fx * d2, fyd2 = fy * d2;
+  o.ju0 = fxd * z;
+  o.ju2 = -fxd2 * X * z;
+  o.ju3 = -fxd2 * X * Y;
+  o.ju4 = fmaf(fxd2 * X, X, fx);
+  o.ju5 = -fxd * Y;
+  o.jv1 = fyd * z;
+  o.jv2 = -fyd2 * Y * z;
+  o.jv3 = -fmaf(fyd2 * Y, Y, fy);
+  o.jv4 = fyd2 * X * Y;
+  o.jv5 = fyd * X;
+  o.jzu = fxd * t[0] - fxd2 * X * t[2];
+  o.jzv = fyd * t[1] - fyd2 * Y * t[2];
+}
+
+// Sum NV (<= 32) per-lane values across the warp so that lane l ends up holding the total of
+// v[l]: 31 shuffles instead of 5 per value (butterfly that halves the live values per stage).
+__device__ __forceinline__ float warp_transpose_reduce32(float (&v)[32], int lane) {
+#pragma unroll
+  for (int s = 16; s >= 1; s >>= 1) {
+    const bool upper = (lane & s) != 0;
+#pragma unroll
+    for (int i = 0; i < s; i++) {
+      const float send = upper ? v[i] : v[i + s];
+      const float keep = upper ? v[i + s] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
+    }
+  }
+  return v[0];
+}

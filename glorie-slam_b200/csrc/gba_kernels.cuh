@@ -1,0 +1,867 @@
+// gba_kernels.cuh -- index build and the per-edge / per-frame kernels of the dense BA.
+#pragma once
+#include "gba_common.cuh"
+
+// ============================================================================================
+// Index build (once per call, on device).  Replaces the host-side work of the reference:
+// torch::_unique over cat(ts, ii) (droid_kernels.cu:1337-1345) and the D2H + argsort + CSR loop
+// that every accum_cuda call repeats (droid_kernels.cu:948-984).
+// ============================================================================================
+
+// one CTA: depth-keyframe list kx (sorted unique of [t0,t1) U ii), frame -> k map
+__global__ void __launch_bounds__(1024) k_prep_frames(BaParams p, const int64_t *kx_global, int n_kx) {
+  __shared__ int s_carry;
+  __shared__ int s_warp[32];
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+    p.st->err = 0;
+    p.st->chol_fail = 0;
+  }
+  for (int f = tid; f < p.N; f += blockDim.x) p.fmap[f] = 0;
+  __syncthreads();
+  if (kx_global) {
+    for (int k = tid; k < n_kx; k += blockDim.x) {
+      const long long f = kx_global[k];
+      if (f < 0 || f >= p.N) atomicOr(&p.st->err, 1);
+      else {
+        p.kx[k] = (int)f;
+        p.fmap[f] = k + 1;
+      }
+    }
+    __syncthreads();
+    for (int n = tid; n < p.E; n += blockDim.x) {
+      const long long i = p.ii[n];
+      if (i < 0 || i >= p.N) atomicOr(&p.st->err, 1);
+      else if (p.fmap[i] == 0) atomicOr(&p.st->err, 4);
+    }
+    __syncthreads();
+    for (int f = tid; f < p.N; f += blockDim.x) p.fmap[f] -= 1;
+    for (int k = tid; k < n_kx; k += blockDim.x) p.deg[k] = 0;
+    if (tid == 0) p.st->K = n_kx;
+    return;
+  }
+  if (p.mode == 0)
+    for (int f = p.t0 + tid; f < p.t1 && f < p.N; f += blockDim.x)
+      if (f >= 0) p.fmap[f] = 1;
+  for (int n = tid; n < p.E; n += blockDim.x) {
+    const long long i = p.ii[n];
+    if (i < 0 || i >= p.N) atomicOr(&p.st->err, 1);
+    else p.fmap[i] = 1;
+  }
+  if (tid == 0) s_carry = 0;
+  __syncthreads();
+  // exclusive scan of the presence flags, 1024 frames per round
+  for (int base = 0; base < p.N; base += blockDim.x) {
+    const int f = base + tid;
+    const int flag = (f < p.N) ? p.fmap[f] : 0;
+    int v = flag;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int u = __shfl_up_sync(0xffffffffu, v, o);
+      if ((tid & 31) >= o) v += u;
+    }
+    if ((tid & 31) == 31) s_warp[tid >> 5] = v;
+    __syncthreads();
+    if (tid < 32) {
+      int w = s_warp[tid];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int u = __shfl_up_sync(0xffffffffu, w, o);
+        if (tid >= o) w += u;
+      }
+      s_warp[tid] = w;
+    }
+    __syncthreads();
+    const int incl = v + ((tid >> 5) ? s_warp[(tid >> 5) - 1] : 0) + s_carry;
+    if (f < p.N) {
+      if (flag) {
+        p.kx[incl - 1] = f;
+        p.fmap[f] = incl - 1;
+        p.deg[incl - 1] = 0;
+      } else
+        p.fmap[f] = -1;
+    }
+    __syncthreads();
+    if (tid == blockDim.x - 1) s_carry = incl;
+    __syncthreads();
+  }
+  if (tid == 0) p.st->K = s_carry;
+}
+
+// edge -> k, out-degree histogram, range checks
+__global__ void k_prep_edges(BaParams p) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= p.E) return;
+  const long long i = p.ii[n], j = p.jj[n];
+  if (i < 0 || i >= p.N || j < 0 || j >= p.N) {
+    atomicOr(&p.st->err, 1);
+    p.ek[n] = -1;
+    return;
+  }
+  const int k = p.fmap[i];
+  p.ek[n] = k;
+  if (k >= 0) atomicAdd(&p.deg[k], 1);
+}
+
+// one CTA: CSR row pointers, per-frame Gram offsets, max degree
+__global__ void __launch_bounds__(1024) k_prep_scan(BaParams p) {
+  __shared__ int s_warp[32];
+  __shared__ int s_carry, s_maxdeg;
+  __shared__ unsigned long long s_gcarry;
+  __shared__ unsigned long long s_gwarp[32];
+  const int tid = threadIdx.x, K = p.st->K;
+  if (tid == 0) {
+    s_carry = 0;
+    s_maxdeg = 0;
+    s_gcarry = 0ull;
+    p.eptr[0] = 0;
+  }
+  __syncthreads();
+  for (int base = 0; base < K; base += blockDim.x) {
+    const int k = base + tid;
+    const int d = (k < K) ? p.deg[k] : 0;
+    const int nb = (6 * d + 1 + 7) / 8;
+    const unsigned long long g = (k < K && d > 0) ? (unsigned long long)(nb * 8) * (nb * 8) : 0ull;
+    int v = d;
+    unsigned long long gv = g;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int u = __shfl_up_sync(0xffffffffu, v, o);
+      const unsigned long long gu = __shfl_up_sync(0xffffffffu, gv, o);
+      if ((tid & 31) >= o) {
+        v += u;
+        gv += gu;
+      }
+    }
+    if ((tid & 31) == 31) {
+      s_warp[tid >> 5] = v;
+      s_gwarp[tid >> 5] = gv;
+    }
+    atomicMax(&s_maxdeg, d);
+    __syncthreads();
+    if (tid < 32) {
+      int w = s_warp[tid];
+      unsigned long long gw = s_gwarp[tid];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int u = __shfl_up_sync(0xffffffffu, w, o);
+        const unsigned long long gu = __shfl_up_sync(0xffffffffu, gw, o);
+        if (tid >= o) {
+          w += u;
+          gw += gu;
+        }
+      }
+      s_warp[tid] = w;
+      s_gwarp[tid] = gw;
+    }
+    __syncthreads();
+    const int incl = v + ((tid >> 5) ? s_warp[(tid >> 5) - 1] : 0) + s_carry;
+    const unsigned long long gincl = gv + ((tid >> 5) ? s_gwarp[(tid >> 5) - 1] : 0ull) + s_gcarry;
+    if (k < K) {
+      p.eptr[k + 1] = incl;
+      p.goff[k] = gincl - g;
+    }
+    __syncthreads();
+    if (tid == blockDim.x - 1) {
+      s_carry = incl;
+      s_gcarry = gincl;
+    }
+    __syncthreads();
+  }
+  if (tid == 0) {
+    p.st->max_deg = s_maxdeg;
+    p.st->gram_floats = s_gcarry;
+  }
+}
+
+// one warp per depth keyframe: stable fill of its edge list (edge order, like argsort's CSR)
+__global__ void k_prep_fill(BaParams p) {
+  const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (k >= p.st->K) return;
+  int cnt = p.eptr[k];
+  for (int base = 0; base < p.E; base += 32) {
+    const int n = base + lane;
+    const bool m = (n < p.E) && (p.ek[n] == k);
+    const unsigned b = __ballot_sync(0xffffffffu, m);
+    if (m) p.eidx[cnt + __popc(b & ((1u << lane) - 1u))] = n;
+    cnt += __popc(b);
+  }
+}
+
+// ============================================================================================
+// Per-iteration kernels
+// ============================================================================================
+
+// Relative pose of every edge from the current poses (droid_kernels.cu:96-107 relSE3).
+__global__ void k_edge_geo(BaParams p) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= p.E) return;
+  const int i = (int)p.ii[n], j = (int)p.jj[n];
+  EdgeGeo g;
+  float q[4], t[3];
+  g.flags = 0;
+  if (i == j) {  // stereo pair: droid_kernels.cu:219-229
+    q[0] = q[1] = q[2] = 0.f;
+    q[3] = 1.f;
+    t[0] = -0.1f;
+    t[1] = t[2] = 0.f;
+    g.flags = 1;
+  } else {
+    const float *Pi = p.poses + 7 * (size_t)i, *Pj = p.poses + 7 * (size_t)j;
+    const float *qi = Pi + 3, *qj = Pj + 3;
+    q[0] = -qj[3] * qi[0] + qj[0] * qi[3] - qj[1] * qi[2] + qj[2] * qi[1];
+    q[1] = -qj[3] * qi[1] + qj[1] * qi[3] - qj[2] * qi[0] + qj[0] * qi[2];
+    q[2] = -qj[3] * qi[2] + qj[2] * qi[3] - qj[0] * qi[1] + qj[1] * qi[0];
+    q[3] = qj[3] * qi[3] + qj[0] * qi[0] + qj[1] * qi[1] + qj[2] * qi[2];
+    // t_ij = t_j - q_ij * t_i  (actSO3, droid_kernels.cu:58-68)
+    const float uv0 = 2.f * (q[1] * Pi[2] - q[2] * Pi[1]);
+    const float uv1 = 2.f * (q[2] * Pi[0] - q[0] * Pi[2]);
+    const float uv2 = 2.f * (q[0] * Pi[1] - q[1] * Pi[0]);
+    t[0] = Pj[0] - (Pi[0] + q[3] * uv0 + (q[1] * uv2 - q[2] * uv1));
+    t[1] = Pj[1] - (Pi[1] + q[3] * uv1 + (q[2] * uv0 - q[0] * uv2));
+    t[2] = Pj[2] - (Pi[2] + q[3] * uv2 + (q[0] * uv1 - q[1] * uv0));
+  }
+  // rotation matrix equivalent to the quaternion sandwich X + w*uv + q x uv, uv = 2 q x X
+  const float x = q[0], y = q[1], z = q[2], w = q[3];
+  g.R[0] = 1.f - 2.f * (y * y + z * z);
+  g.R[1] = 2.f * (x * y - w * z);
+  g.R[2] = 2.f * (x * z + w * y);
+  g.R[3] = 2.f * (x * y + w * z);
+  g.R[4] = 1.f - 2.f * (x * x + z * z);
+  g.R[5] = 2.f * (y * z - w * x);
+  g.R[6] = 2.f * (x * z - w * y);
+  g.R[7] = 2.f * (y * z + w * x);
+  g.R[8] = 1.f - 2.f * (x * x + y * y);
+  g.t[0] = t[0];
+  g.t[1] = t[1];
+  g.t[2] = t[2];
+  const int pi = i - p.t0, pj = j - p.t0;
+  g.pi = (pi >= 0 && pi < p.P) ? pi : -1;  // update_lhs drops negative indices (droid_kernels.cu:1146)
+  g.pj = (pj >= 0 && pj < p.P) ? pj : -1;
+  g.pad = 0;
+  p.geo[n] = g;
+}
+
+// --------------------------------------------------------------------------------------------
+// Pass A: linearisation.  CTA = (pixel chunk, depth keyframe k); each thread owns NV groups of 4
+// consecutive pixels and walks the out-edges of k.  Reads target/weight once (float4, streaming),
+// keeps the per-pixel depth diagonal C and w in registers, reduces the 27 entries of (H_jj, v_j)
+// per edge with a 31-shuffle transposed warp reduction and a per-warp shared-memory stage
+// (no global atomics).  Replaces projective_transform_kernel (droid_kernels.cu:176-424) and the
+// accum_cuda calls for C and w (droid_kernels.cu:1399-1401).
+// --------------------------------------------------------------------------------------------
+#define LIN_EB 8  // edges per shared-memory batch
+
+template <int NT, int NV>
+__global__ void __launch_bounds__(NT) k_linearize(BaParams p) {
+  constexpr int NW = NT / 32;
+  __shared__ EdgeGeo s_geo[LIN_EB];
+  __shared__ int s_eid[LIN_EB];
+  __shared__ float s_red[NW][LIN_EB][28];
+
+  const int k = blockIdx.y;
+  if (k >= p.st->K) return;
+  if (p.owned && !p.owned[k]) return;
+  const int chunk = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int frame = p.kx[k];
+  const int HW = p.HW;
+  const float fx = p.intr[0], fy = p.intr[1], cx = p.intr[2], cy = p.intr[3];
+  const float ifx = 1.0f / fx, ify = 1.0f / fy;
+
+  int px[NV];
+  float x0[NV][4], y0[NV][4], z[NV][4], cacc[NV][4], wacc[NV][4];
+#pragma unroll
+  for (int g = 0; g < NV; g++) {
+    px[g] = (chunk * NV + g) * (NT * 4) + tid * 4;
+    float4 zz = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (px[g] < HW) zz = *reinterpret_cast<const float4 *>(p.disps + (size_t)frame * HW + px[g]);
+    z[g][0] = zz.x; z[g][1] = zz.y; z[g][2] = zz.z; z[g][3] = zz.w;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      const int q = px[g] + i;
+      x0[g][i] = ((float)(q % p.wd) - cx) / fx;  // droid_kernels.cu:290-291
+      y0[g][i] = ((float)(q / p.wd) - cy) / fy;
+      cacc[g][i] = 0.f;
+      wacc[g][i] = 0.f;
+    }
+  }
+  (void)ifx; (void)ify;
+
+  const int e0 = p.eptr[k], e1 = p.eptr[k + 1];
+  for (int eb = e0; eb < e1; eb += LIN_EB) {
+    const int nb = min(LIN_EB, e1 - eb);
+    __syncthreads();
+    if (tid < nb) s_eid[tid] = p.eidx[eb + tid];
+    __syncthreads();
+    for (int i = tid; i < nb * 16; i += NT)
+      reinterpret_cast<float *>(s_geo)[i] = reinterpret_cast<const float *>(p.geo + s_eid[i >> 4])[i & 15];
+    __syncthreads();
+
+    for (int q = 0; q < nb; q++) {
+      const int n = s_eid[q];
+      const float *R = s_geo[q].R, *t = s_geo[q].t;
+      const bool stereo = s_geo[q].flags & 1;
+      const float *tg = p.targets + (size_t)n * 2 * HW, *wg = p.weights + (size_t)n * 2 * HW;
+      float4 tu[NV], tv[NV], wu[NV], wv[NV];
+#pragma unroll
+      for (int g = 0; g < NV; g++) {
+        if (px[g] < HW) {
+          tu[g] = ldg_stream4(tg + px[g]);
+          tv[g] = ldg_stream4(tg + HW + px[g]);
+          wu[g] = ldg_stream4(wg + px[g]);
+          wv[g] = ldg_stream4(wg + HW + px[g]);
+        } else {
+          tu[g] = tv[g] = wu[g] = wv[g] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      }
+      float acc[32];
+#pragma unroll
+      for (int i = 0; i < 32; i++) acc[i] = 0.f;
+#pragma unroll
+      for (int g = 0; g < NV; g++) {
+        const float tua[4] = {tu[g].x, tu[g].y, tu[g].z, tu[g].w}, tva[4] = {tv[g].x, tv[g].y, tv[g].z, tv[g].w};
+        const float wua[4] = {wu[g].x, wu[g].y, wu[g].z, wu[g].w}, wva[4] = {wv[g].x, wv[g].y, wv[g].z, wv[g].w};
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+          PixLin L;
+          pix_linearize(R, t, fx, fy, cx, cy, p.mode, x0[g][i], y0[g][i], z[g][i], tua[i], tva[i], wua[i], wva[i],
+                        L);
+          // depth diagonal keeps the un-zeroed weight even for stereo pairs (droid_kernels.cu:320-323)
+          cacc[g][i] += L.wu * L.jzu * L.jzu + L.wv * L.jzv * L.jzv;
+          wacc[g][i] += L.wu * L.ru * L.jzu + L.wv * L.rv * L.jzv;
+          const float wu_ = stereo ? 0.f : L.wu, wv_ = stereo ? 0.f : L.wv;
+          const float a0 = wu_ * L.ju0, a2 = wu_ * L.ju2, a3 = wu_ * L.ju3, a4 = wu_ * L.ju4, a5 = wu_ * L.ju5;
+          const float b1 = wv_ * L.jv1, b2 = wv_ * L.jv2, b3 = wv_ * L.jv3, b4 = wv_ * L.jv4, b5 = wv_ * L.jv5;
+          // upper triangle of H_jj, row major: (0,0..5) (1,1..5) (2,2..5) (3,3..5) (4,4..5) (5,5)
+          acc[0] += a0 * L.ju0;
+          acc[2] += a0 * L.ju2;
+          acc[3] += a0 * L.ju3;
+          acc[4] += a0 * L.ju4;
+          acc[5] += a0 * L.ju5;
+          acc[6] += b1 * L.jv1;
+          acc[7] += b1 * L.jv2;
+          acc[8] += b1 * L.jv3;
+          acc[9] += b1 * L.jv4;
+          acc[10] += b1 * L.jv5;
+          acc[11] += a2 * L.ju2 + b2 * L.jv2;
+          acc[12] += a2 * L.ju3 + b2 * L.jv3;
+          acc[13] += a2 * L.ju4 + b2 * L.jv4;
+          acc[14] += a2 * L.ju5 + b2 * L.jv5;
+          acc[15] += a3 * L.ju3 + b3 * L.jv3;
+          acc[16] += a3 * L.ju4 + b3 * L.jv4;
+          acc[17] += a3 * L.ju5 + b3 * L.jv5;
+          acc[18] += a4 * L.ju4 + b4 * L.jv4;
+          acc[19] += a4 * L.ju5 + b4 * L.jv5;
+          acc[20] += a5 * L.ju5 + b5 * L.jv5;
+          // v_j
+          acc[21] += a0 * L.ru;
+          acc[22] += b1 * L.rv;
+          acc[23] += a2 * L.ru + b2 * L.rv;
+          acc[24] += a3 * L.ru + b3 * L.rv;
+          acc[25] += a4 * L.ru + b4 * L.rv;
+          acc[26] += a5 * L.ru + b5 * L.rv;
+        }
+      }
+      const float tot = warp_transpose_reduce32(acc, lane);
+      if (lane < 28) s_red[warp][q][lane] = tot;
+    }
+    __syncthreads();
+    for (int i = tid; i < nb * 27; i += NT) {
+      const int q = i / 27, l = i - q * 27;
+      float s = 0.f;
+#pragma unroll
+      for (int w = 0; w < NW; w++) s += s_red[w][q][l];
+      p.hpart[((size_t)s_eid[q] * p.nchunk + chunk) * 32 + l] = s;
+    }
+  }
+
+  if (p.motion_only) return;
+  // depth diagonal: C = sum Cii + m*alpha + (1-m)*eta, w = sum wi - m*alpha*(disp - sens)
+  // (droid_kernels.cu:1397-1401; ba.py:92-103), Q = 1/C
+  const float alpha = 0.05f;
+#pragma unroll
+  for (int g = 0; g < NV; g++) {
+    if (px[g] >= HW) continue;
+    const float4 sn = *reinterpret_cast<const float4 *>(p.sens + (size_t)frame * HW + px[g]);
+    const float4 et = *reinterpret_cast<const float4 *>(p.eta + (size_t)k * HW + px[g]);
+    const float sna[4] = {sn.x, sn.y, sn.z, sn.w}, eta4[4] = {et.x, et.y, et.z, et.w};
+    float qo[4], wo[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      const float m = sna[i] > 0.f ? 1.f : 0.f;
+      const float C = cacc[g][i] + m * alpha + (1.f - m) * eta4[i];
+      wo[i] = wacc[g][i] - m * alpha * (z[g][i] - sna[i]);
+      qo[i] = 1.0f / C;
+    }
+    *reinterpret_cast<float4 *>(p.Q + (size_t)k * HW + px[g]) = make_float4(qo[0], qo[1], qo[2], qo[3]);
+    *reinterpret_cast<float4 *>(p.W + (size_t)k * HW + px[g]) = make_float4(wo[0], wo[1], wo[2], wo[3]);
+  }
+}
+
+// --------------------------------------------------------------------------------------------
+// Per edge: sum the chunk partials, derive the four pose blocks from H_jj through
+// B = -Ad(G_ij)^T (H_ii = B H B^T, H_ij = B H, H_ji = H B^T, v_i = B v_j) and add them to the
+// reduced camera system (fp64, lower triangle).  Replaces SparseBlock::update_lhs/update_rhs
+// (droid_kernels.cu:1131-1173,1377-1384) -- no D2H copy, no triplets.
+// --------------------------------------------------------------------------------------------
+__global__ void k_edge_finish(BaParams p) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= p.E) return;
+  if (p.ek[n] < 0 || (p.owned && !p.owned[p.ek[n]])) return;
+  double hv[27];
+  for (int l = 0; l < 27; l++) {
+    float s = 0.f;
+    for (int c = 0; c < p.nchunk; c++) s += p.hpart[((size_t)n * p.nchunk + c) * 32 + l];
+    hv[l] = (double)s;
+    p.edge_hv[(size_t)n * 32 + l] = s;
+  }
+  const EdgeGeo g = p.geo[n];
+  const int pi = g.pi, pj = g.pj;
+  if (pi < 0 && pj < 0) return;
+  double H[6][6];
+  {
+    int l = 0;
+    for (int r = 0; r < 6; r++)
+      for (int c = r; c < 6; c++) {
+        H[r][c] = hv[l];
+        H[c][r] = hv[l];
+        l++;
+      }
+  }
+  const double *v = hv + 21;
+  // jj,jj block and v_j
+  if (pj >= 0) {
+    for (int r = 0; r < 6; r++) {
+      for (int c = 0; c <= r; c++) atomicAdd(sys_at(p, 6 * pj + r, 6 * pj + c), H[r][c]);
+      atomicAdd(p.sys + (size_t)p.st->n_slots * GBA_NB2 + 6 * pj + r, v[r]);
+    }
+  }
+  if (pi < 0) return;
+  // BH = B H (columns of H mapped through B)
+  double BH[6][6];
+  for (int c = 0; c < 6; c++) {
+    double x[6], y[6];
+    for (int r = 0; r < 6; r++) x[r] = H[r][c];
+    apply_B<double>(g.R, g.t, x, y);
+    for (int r = 0; r < 6; r++) BH[r][c] = y[r];
+  }
+  // ii,ii block = (B H) B^T: row r of BH mapped through B
+  for (int r = 0; r < 6; r++) {
+    double x[6], y[6];
+    for (int c = 0; c < 6; c++) x[c] = BH[r][c];
+    apply_B<double>(g.R, g.t, x, y);
+    for (int c = 0; c <= r; c++) atomicAdd(sys_at(p, 6 * pi + r, 6 * pi + c), y[c]);
+  }
+  {
+    double y[6];
+    apply_B<double>(g.R, g.t, v, y);
+    for (int r = 0; r < 6; r++) atomicAdd(p.sys + (size_t)p.st->n_slots * GBA_NB2 + 6 * pi + r, y[r]);
+  }
+  if (pj >= 0 && pi != pj) {
+    // off-diagonal: block (pi,pj) = B H, block (pj,pi) = (B H)^T; store the lower one
+    for (int r = 0; r < 6; r++)
+      for (int c = 0; c < 6; c++) {
+        if (pi > pj) atomicAdd(sys_at(p, 6 * pi + r, 6 * pj + c), BH[r][c]);
+        else atomicAdd(sys_at(p, 6 * pj + c, 6 * pi + r), BH[r][c]);
+      }
+  }
+}
+
+// --------------------------------------------------------------------------------------------
+// Pass B: Schur Gram.  For depth keyframe k with out-edges n_1..n_d the rows
+// a_n[c][pix] = sqrt(Q) * sum_{u,v} w J_z J_j[c]  (c = 0..5) and the extra row sqrt(Q) * w_k are
+// rebuilt tile by tile in shared memory (never written to HBM) and the Gram matrix
+// G = A A^T is accumulated in registers, 8x8 outputs per thread over the block-upper triangle.
+// G[6n+r, 6m+c] = sum_pix E_n[r] Q E_m[c];  G[6n+r, 6d] = sum_pix E_n[r] Q w.
+// Replaces Eii/Eij materialisation + accum + EEt6x6/Ev6x1 (droid_kernels.cu:340-341,373-374,
+// 1001-1093,1222-1296): the (i,j,k) triples of schur_block are exactly the block pairs of G.
+// --------------------------------------------------------------------------------------------
+#define GRAM_T 32   // pixels per shared-memory tile
+#define GRAM_NT 256
+
+__device__ __forceinline__ int gram_off(int p, int col, int nb, int RS) {
+  const int chunk = (col >> 3) + (((col >> 2) & 1) ? nb : 0);
+  return p * RS + (((chunk ^ (p & 7)) << 2) | (col & 3));
+}
+
+__global__ void __launch_bounds__(GRAM_NT) k_gram(BaParams p) {
+  extern __shared__ float s_tile[];
+  const int k = blockIdx.y;
+  if (k >= p.st->K) return;
+  if (p.owned && !p.owned[k]) return;
+  const int e0 = p.eptr[k], deg = p.eptr[k + 1] - e0;
+  if (deg == 0) return;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int Rw = 6 * deg;  // column of the w row
+  const int nb = (Rw + 1 + 7) / 8, Rp = nb * 8;
+  const int RS = ((2 * nb + 7) & ~7) * 4;
+  const int nblk = nb * (nb + 1) / 2;
+  const int npass = (nblk + GRAM_NT - 1) / GRAM_NT;
+  const int HW = p.HW, frame = p.kx[k];
+  const float fx = p.intr[0], fy = p.intr[1], cx = p.intr[2], cy = p.intr[3];
+  const int ntile = (HW + GRAM_T - 1) / GRAM_T;
+  float *G = p.gram + p.goff[k];
+  const float4 *tile4 = reinterpret_cast<const float4 *>(s_tile);
+  const int RS4 = RS >> 2;
+
+  for (int pass = 0; pass < npass; pass++) {
+    const int blk = pass * GRAM_NT + tid;
+    int bi = 0, bj = 0;
+    const bool active = blk < nblk;
+    if (active) {  // blk -> (bi <= bj), row major over the block-upper triangle
+      int rem = blk;
+      while (rem >= nb - bi) {
+        rem -= nb - bi;
+        bi++;
+      }
+      bj = bi + rem;
+    }
+    float acc[8][8];
+#pragma unroll
+    for (int r = 0; r < 8; r++)
+#pragma unroll
+      for (int c = 0; c < 8; c++) acc[r][c] = 0.f;
+
+    // zero the tile once (padding columns stay zero; data columns are rewritten per tile)
+    __syncthreads();
+    for (int i = tid; i < GRAM_T * RS; i += GRAM_NT) s_tile[i] = 0.f;
+
+    for (int tt = blockIdx.x; tt < ntile; tt += gridDim.x) {
+      __syncthreads();
+      // ---- phase 1: rebuild the rows of this pixel tile --------------------------------------
+      const int pix = tt * GRAM_T + lane;
+      const bool pv = pix < HW;
+      const float zq = pv ? p.disps[(size_t)frame * HW + pix] : 1.f;
+      const float sq = pv ? sqrtf(p.Q[(size_t)k * HW + pix]) : 0.f;
+      const float x0 = ((float)(pix % p.wd) - cx) / fx, y0 = ((float)(pix / p.wd) - cy) / fy;
+      if (warp == 0) s_tile[gram_off(lane, Rw, nb, RS)] = pv ? sq * p.W[(size_t)k * HW + pix] : 0.f;
+      for (int q = warp; q < deg; q += GRAM_NT / 32) {
+        const int n = p.eidx[e0 + q];
+        const EdgeGeo *g = p.geo + n;
+        float R[9], t[3];
+        {
+          const float4 g0 = __ldg(reinterpret_cast<const float4 *>(g)), g1 = __ldg(reinterpret_cast<const float4 *>(g) + 1),
+                       g2 = __ldg(reinterpret_cast<const float4 *>(g) + 2);
+          R[0] = g0.x; R[1] = g0.y; R[2] = g0.z; R[3] = g0.w;
+          R[4] = g1.x; R[5] = g1.y; R[6] = g1.z; R[7] = g1.w;
+          R[8] = g2.x; t[0] = g2.y; t[1] = g2.z; t[2] = g2.w;
+        }
+        const bool stereo = __ldg(&g->flags) & 1;
+        float e[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        if (pv && !stereo) {
+          const float *tg = p.targets + (size_t)n * 2 * HW, *wg = p.weights + (size_t)n * 2 * HW;
+          PixLin L;
+          pix_linearize(R, t, fx, fy, cx, cy, p.mode, x0, y0, zq, ldg_stream(tg + pix), ldg_stream(tg + HW + pix),
+                        ldg_stream(wg + pix), ldg_stream(wg + HW + pix), L);
+          const float su = sq * L.wu * L.jzu, sv = sq * L.wv * L.jzv;
+          e[0] = su * L.ju0;
+          e[1] = sv * L.jv1;
+          e[2] = su * L.ju2 + sv * L.jv2;
+          e[3] = su * L.ju3 + sv * L.jv3;
+          e[4] = su * L.ju4 + sv * L.jv4;
+          e[5] = su * L.ju5 + sv * L.jv5;
+        }
+#pragma unroll
+        for (int c = 0; c < 6; c++) s_tile[gram_off(lane, 6 * q + c, nb, RS)] = e[c];
+      }
+      __syncthreads();
+      // ---- phase 2: rank-GRAM_T update of the 8x8 register block --------------------------
+      if (active) {
+#pragma unroll 4
+        for (int pp = 0; pp < GRAM_T; pp++) {
+          const int s = pp & 7;
+          const float4 a0 = tile4[pp * RS4 + (bi ^ s)], a1 = tile4[pp * RS4 + ((nb + bi) ^ s)];
+          const float4 b0 = tile4[pp * RS4 + (bj ^ s)], b1 = tile4[pp * RS4 + ((nb + bj) ^ s)];
+          const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+          const float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+          for (int r = 0; r < 8; r++)
+#pragma unroll
+            for (int c = 0; c < 8; c++) acc[r][c] = fmaf(a[r], b[c], acc[r][c]);
+        }
+      }
+    }
+    if (active) {
+#pragma unroll
+      for (int r = 0; r < 8; r++)
+#pragma unroll
+        for (int c = 0; c < 8; c++) {
+          float *dst = G + (size_t)(8 * bi + r) * Rp + 8 * bj + c;
+          if (gridDim.x == 1) *dst = acc[r][c];
+          else atomicAdd(dst, acc[r][c]);
+        }
+    }
+  }
+}
+
+// --------------------------------------------------------------------------------------------
+// Per depth keyframe: subtract its Schur contribution from the reduced camera system.
+// Edge rows carry pose jj[n]; the keyframe's own pose row is E_i = sum_n B_n E_n, so its blocks
+// follow algebraically: S[k,m] = sum_n B_n G[n,m], S[k,k] = sum_{n,m} B_n G[n,m] B_m^T.
+// Replaces schur_block's host-side adjacency + O(P^2 deg^2) triple loop + sparse assembly
+// (droid_kernels.cu:1241-1311) and `A - S` (droid_kernels.cu:1175-1177,1407).
+// --------------------------------------------------------------------------------------------
+#define SCHUR_NT 128
+
+__device__ __forceinline__ float gram_at(const float *G, int Rp, int r, int c) {
+  return (r <= c) ? G[(size_t)r * Rp + c] : G[(size_t)c * Rp + r];
+}
+
+__global__ void __launch_bounds__(SCHUR_NT) k_schur(BaParams p) {
+  extern __shared__ float s_U[];  // [6][Rw + 1]
+  const int k = blockIdx.x;
+  if (k >= p.st->K) return;
+  if (p.owned && !p.owned[k]) return;
+  const int e0 = p.eptr[k], deg = p.eptr[k + 1] - e0;
+  if (deg == 0) return;
+  const int tid = threadIdx.x;
+  const int Rw = 6 * deg, nb = (Rw + 1 + 7) / 8, Rp = nb * 8;
+  const float *G = p.gram + p.goff[k];
+  double *rhs = p.sys + (size_t)p.st->n_slots * GBA_NB2;
+  const int pcr = p.kx[k] - p.t0;
+  const int pc = (pcr >= 0 && pcr < p.P) ? pcr : -1;
+
+  // (a) edge-row x edge-row blocks, lower triangle only
+  for (int idx = tid; idx < deg * deg; idx += SCHUR_NT) {
+    const int n = idx / deg, m = idx - n * deg;
+    const int a = p.geo[p.eidx[e0 + n]].pj, b = p.geo[p.eidx[e0 + m]].pj;
+    if (a < 0 || b < 0 || a < b) continue;
+    for (int r = 0; r < 6; r++)
+      for (int c = 0; c < 6; c++) {
+        const int Rg = 6 * a + r, Cg = 6 * b + c;
+        if (Rg < Cg) continue;
+        atomicAdd(sys_at(p, Rg, Cg), -(double)gram_at(G, Rp, 6 * n + r, 6 * m + c));
+      }
+  }
+  // (b) rhs: v -= E Q w  (Ev6x1 + update_rhs, droid_kernels.cu:1298-1308)
+  for (int idx = tid; idx < Rw; idx += SCHUR_NT) {
+    const int n = idx / 6, r = idx - 6 * n;
+    const int a = p.geo[p.eidx[e0 + n]].pj;
+    if (a >= 0) atomicAdd(rhs + 6 * a + r, -(double)G[(size_t)idx * Rp + Rw]);
+  }
+  if (pc < 0) return;
+  // (c) the keyframe's own pose row: U[:, col] = sum_n B_n G[n-block, col] for col in [0, Rw]
+  for (int col = tid; col <= Rw; col += SCHUR_NT) {
+    float u[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int n = 0; n < deg; n++) {
+      const EdgeGeo *g = p.geo + p.eidx[e0 + n];
+      float x[6], y[6];
+      for (int r = 0; r < 6; r++) x[r] = gram_at(G, Rp, 6 * n + r, col);
+      apply_B<float>(g->R, g->t, x, y);
+      for (int r = 0; r < 6; r++) u[r] += y[r];
+    }
+    for (int r = 0; r < 6; r++) s_U[r * (Rw + 1) + col] = u[r];
+  }
+  __syncthreads();
+  // cross blocks S[k, jj[m]] = U_m, stored on the lower side
+  for (int idx = tid; idx < Rw; idx += SCHUR_NT) {
+    const int m = idx / 6, c = idx - 6 * m;
+    const int b = p.geo[p.eidx[e0 + m]].pj;
+    if (b < 0 || b == pc) continue;
+    for (int r = 0; r < 6; r++) {
+      const double val = -(double)s_U[r * (Rw + 1) + idx];
+      if (pc > b) atomicAdd(sys_at(p, 6 * pc + r, 6 * b + c), val);
+      else atomicAdd(sys_at(p, 6 * b + c, 6 * pc + r), val);
+    }
+  }
+  // diagonal block S[k,k] = sum_m U_m B_m^T and rhs
+  if (tid < 6) {
+    const int r = tid;
+    float w[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int m = 0; m < deg; m++) {
+      const EdgeGeo *g = p.geo + p.eidx[e0 + m];
+      float x[6], y[6];
+      for (int c = 0; c < 6; c++) x[c] = s_U[r * (Rw + 1) + 6 * m + c];
+      apply_B<float>(g->R, g->t, x, y);
+      for (int c = 0; c < 6; c++) w[c] += y[c];
+    }
+    for (int c = 0; c <= r; c++) atomicAdd(sys_at(p, 6 * pc + r, 6 * pc + c), -(double)w[c]);
+    atomicAdd(rhs + 6 * pc + r, -(double)s_U[r * (Rw + 1) + Rw]);
+  }
+}
+
+// Levenberg-Marquardt damping of the diagonal: d += ep + lm * d
+// (droid_kernels.cu:1197 after the Schur complement; chol.py:66-68 before it).
+__global__ void k_damp(BaParams p, float lm, float ep) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 6 * p.P) return;
+  double *d = sys_at(p, i, i);
+  *d += (double)ep + (double)lm * (*d);
+}
+
+// --------------------------------------------------------------------------------------------
+// Pass C: back-substitution + disparity retraction, fused.  dz = Q (w - sum_rows E_r . dx_r):
+// the E rows are rebuilt from target/weight (second streaming read) and contracted on the fly
+// with one 6-vector per edge, delta_n = dx[jj] + B_n^T dx[k]; disps is updated in place.
+// Replaces EvT6x1 + accum + disp_retr (droid_kernels.cu:1095-1115,1409-1418,933-946,1428-1431).
+// --------------------------------------------------------------------------------------------
+template <int NT, int NV>
+__global__ void __launch_bounds__(NT) k_backsub(BaParams p) {
+  __shared__ EdgeGeo s_geo[LIN_EB];
+  __shared__ float s_delta[LIN_EB][8];
+  __shared__ int s_eid[LIN_EB];
+  const int k = blockIdx.y;
+  if (k >= p.st->K) return;
+  if (p.owned && !p.owned[k]) return;
+  const int chunk = blockIdx.x, tid = threadIdx.x;
+  const int frame = p.kx[k], HW = p.HW;
+  const float fx = p.intr[0], fy = p.intr[1], cx = p.intr[2], cy = p.intr[3];
+  const int pcr = frame - p.t0;
+  // EvT6x1 skips pose index <= 0 (droid_kernels.cu:1105); chol.py:81 does not
+  const int lo = (p.mode == 0) ? 1 : 0;
+  const bool kvalid = (pcr >= lo && pcr < p.P);
+
+  int px[NV];
+  float x0[NV][4], y0[NV][4], z[NV][4], dw[NV][4];
+#pragma unroll
+  for (int g = 0; g < NV; g++) {
+    px[g] = (chunk * NV + g) * (NT * 4) + tid * 4;
+    float4 zz = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (px[g] < HW) zz = *reinterpret_cast<const float4 *>(p.disps + (size_t)frame * HW + px[g]);
+    z[g][0] = zz.x; z[g][1] = zz.y; z[g][2] = zz.z; z[g][3] = zz.w;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      const int q = px[g] + i;
+      x0[g][i] = ((float)(q % p.wd) - cx) / fx;
+      y0[g][i] = ((float)(q / p.wd) - cy) / fy;
+      dw[g][i] = 0.f;
+    }
+  }
+  const int e0 = p.eptr[k], e1 = p.eptr[k + 1];
+  for (int eb = e0; eb < e1; eb += LIN_EB) {
+    const int nb = min(LIN_EB, e1 - eb);
+    __syncthreads();
+    if (tid < nb) s_eid[tid] = p.eidx[eb + tid];
+    __syncthreads();
+    for (int i = tid; i < nb * 16; i += NT)
+      reinterpret_cast<float *>(s_geo)[i] = reinterpret_cast<const float *>(p.geo + s_eid[i >> 4])[i & 15];
+    __syncthreads();
+    if (tid < nb) {
+      const EdgeGeo &g = s_geo[tid];
+      float d[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      if (g.pj >= lo)
+        for (int r = 0; r < 6; r++) d[r] = p.dx[6 * g.pj + r];
+      if (kvalid) {
+        float y[6];
+        apply_Bt(g.R, g.t, p.dx + 6 * pcr, y);
+        for (int r = 0; r < 6; r++) d[r] += y[r];
+      }
+      if (g.flags & 1)
+        for (int r = 0; r < 6; r++) d[r] = 0.f;
+      for (int r = 0; r < 6; r++) s_delta[tid][r] = d[r];
+    }
+    __syncthreads();
+    for (int q = 0; q < nb; q++) {
+      const int n = s_eid[q];
+      const float *R = s_geo[q].R, *t = s_geo[q].t, *dl = s_delta[q];
+      const float *tg = p.targets + (size_t)n * 2 * HW, *wg = p.weights + (size_t)n * 2 * HW;
+      float4 tu[NV], tv[NV], wu[NV], wv[NV];
+#pragma unroll
+      for (int g = 0; g < NV; g++) {
+        if (px[g] < HW) {
+          tu[g] = ldg_stream4(tg + px[g]);
+          tv[g] = ldg_stream4(tg + HW + px[g]);
+          wu[g] = ldg_stream4(wg + px[g]);
+          wv[g] = ldg_stream4(wg + HW + px[g]);
+        } else {
+          tu[g] = tv[g] = wu[g] = wv[g] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      }
+#pragma unroll
+      for (int g = 0; g < NV; g++) {
+        const float tua[4] = {tu[g].x, tu[g].y, tu[g].z, tu[g].w}, tva[4] = {tv[g].x, tv[g].y, tv[g].z, tv[g].w};
+        const float wua[4] = {wu[g].x, wu[g].y, wu[g].z, wu[g].w}, wva[4] = {wv[g].x, wv[g].y, wv[g].z, wv[g].w};
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+          PixLin L;
+          pix_linearize(R, t, fx, fy, cx, cy, p.mode, x0[g][i], y0[g][i], z[g][i], tua[i], tva[i], wua[i], wva[i],
+                        L);
+          const float du = L.ju0 * dl[0] + L.ju2 * dl[2] + L.ju3 * dl[3] + L.ju4 * dl[4] + L.ju5 * dl[5];
+          const float dv = L.jv1 * dl[1] + L.jv2 * dl[2] + L.jv3 * dl[3] + L.jv4 * dl[4] + L.jv5 * dl[5];
+          dw[g][i] += L.wu * L.jzu * du + L.wv * L.jzv * dv;
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int g = 0; g < NV; g++) {
+    if (px[g] >= HW) continue;
+    const float4 q4 = *reinterpret_cast<const float4 *>(p.Q + (size_t)k * HW + px[g]);
+    const float4 w4 = *reinterpret_cast<const float4 *>(p.W + (size_t)k * HW + px[g]);
+    const float qa[4] = {q4.x, q4.y, q4.z, q4.w}, wa[4] = {w4.x, w4.y, w4.z, w4.w};
+    float dzv[4], zn[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      dzv[i] = qa[i] * (wa[i] - dw[g][i]);
+      zn[i] = z[g][i] + dzv[i];
+      if (p.mode == 1 && zn[i] < 0.f) zn[i] = 0.f;  // ba.py:119
+    }
+    *reinterpret_cast<float4 *>(p.disps + (size_t)frame * HW + px[g]) = make_float4(zn[0], zn[1], zn[2], zn[3]);
+    if (p.dz_out)
+      *reinterpret_cast<float4 *>(p.dz_out + (size_t)k * HW + px[g]) = make_float4(dzv[0], dzv[1], dzv[2], dzv[3]);
+  }
+}
+
+// SE3 retraction T <- Exp(xi) T for the optimised poses.
+//   droid: droid_kernels.cu:110-175,877-931 (thresholds 1e-8 / 1e-4, no renormalisation)
+//   geom : lietorch Exp + mul (so3.h:153-190, se3.h:134-142,45-47), quaternions renormalised
+__global__ void k_pose_retr(BaParams p) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= p.P) return;
+  float *T = p.poses + 7 * (size_t)(p.t0 + i);
+  const float *xi = p.dx + 6 * i;
+  const float tau[3] = {xi[0], xi[1], xi[2]}, phi[3] = {xi[3], xi[4], xi[5]};
+  const float th2 = phi[0] * phi[0] + phi[1] * phi[1] + phi[2] * phi[2];
+  const float th = sqrtf(th2);
+  float imag, real, dt[3] = {tau[0], tau[1], tau[2]};
+  const bool small_q = (p.mode == 0) ? (th2 < 1e-8f) : (th < 1e-6f);
+  if (small_q) {
+    const float th4 = th2 * th2;
+    imag = 0.5f - (1.0f / 48.0f) * th2 + (1.0f / 3840.0f) * th4;
+    real = 1.0f - (1.0f / 8.0f) * th2 + (1.0f / 384.0f) * th4;
+  } else {
+    imag = sinf(0.5f * th) / th;
+    real = cosf(0.5f * th);
+  }
+  float dq[4] = {imag * phi[0], imag * phi[1], imag * phi[2], real};
+  float c1[3] = {phi[1] * tau[2] - phi[2] * tau[1], phi[2] * tau[0] - phi[0] * tau[2], phi[0] * tau[1] - phi[1] * tau[0]};
+  float c2[3] = {phi[1] * c1[2] - phi[2] * c1[1], phi[2] * c1[0] - phi[0] * c1[2], phi[0] * c1[1] - phi[1] * c1[0]};
+  float q[4] = {T[3], T[4], T[5], T[6]};
+  if (p.mode == 0) {
+    if (th > 1e-4f) {
+      const float a = (1.f - cosf(th)) / th2, b = (th - sinf(th)) / (th * th2);
+      for (int r = 0; r < 3; r++) dt[r] += a * c1[r] + b * c2[r];
+    }
+  } else {
+    const float a = (th < 1e-6f) ? 0.5f - (1.0f / 24.0f) * th2 : (1.f - cosf(th)) / th2;
+    const float b = (th < 1e-6f) ? (1.0f / 6.0f) - (1.0f / 120.0f) * th2 : (th - sinf(th)) / (th2 * th);
+    for (int r = 0; r < 3; r++) dt[r] += a * c1[r] + b * c2[r];
+    const float nd = rsqrtf(dq[0] * dq[0] + dq[1] * dq[1] + dq[2] * dq[2] + dq[3] * dq[3]);
+    const float nq = rsqrtf(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+    for (int r = 0; r < 4; r++) {
+      dq[r] *= nd;
+      q[r] *= nq;
+    }
+  }
+  float q1[4];
+  q1[0] = dq[3] * q[0] + dq[0] * q[3] + dq[1] * q[2] - dq[2] * q[1];
+  q1[1] = dq[3] * q[1] + dq[1] * q[3] + dq[2] * q[0] - dq[0] * q[2];
+  q1[2] = dq[3] * q[2] + dq[2] * q[3] + dq[0] * q[1] - dq[1] * q[0];
+  q1[3] = dq[3] * q[3] - dq[0] * q[0] - dq[1] * q[1] - dq[2] * q[2];
+  if (p.mode == 1) {
+    const float n1 = rsqrtf(q1[0] * q1[0] + q1[1] * q1[1] + q1[2] * q1[2] + q1[3] * q1[3]);
+    for (int r = 0; r < 4; r++) q1[r] *= n1;
+  }
+  const float t[3] = {T[0], T[1], T[2]};
+  const float uv0 = 2.f * (dq[1] * t[2] - dq[2] * t[1]);
+  const float uv1 = 2.f * (dq[2] * t[0] - dq[0] * t[2]);
+  const float uv2 = 2.f * (dq[0] * t[1] - dq[1] * t[0]);
+  T[0] = t[0] + dq[3] * uv0 + (dq[1] * uv2 - dq[2] * uv1) + dt[0];
+  T[1] = t[1] + dq[3] * uv1 + (dq[2] * uv0 - dq[0] * uv2) + dt[1];
+  T[2] = t[2] + dq[3] * uv2 + (dq[0] * uv1 - dq[1] * uv0) + dt[2];
+  T[3] = q1[0];
+  T[4] = q1[1];
+  T[5] = q1[2];
+  T[6] = q1[3];
+}

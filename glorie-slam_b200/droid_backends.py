@@ -1,0 +1,89 @@
+"""Drop-in for the reference's `droid_backends` extension module -- `ba` only.
+
+Reference: src/lib/droid.cpp:89-119 (wrapper + pybind export :239-241) calling
+src/lib/droid_kernels.cu:1314-1437 (ba_cuda); the only call site is
+src/depth_video.py:217-218.  Same 16 positional arguments, same in-place update of `poses`
+and `disps`, same return value `[dx, dz]` of the last iteration.  Put this directory first on
+sys.path and `import droid_backends` resolves here; depth_video.py stays unchanged.
+
+The work is done by libgba.so (hand-written sm_100a CUDA behind the C ABI in include/gba.h);
+torch only supplies device memory and the current stream.  The other functions of the
+reference module (frame_distance, projmap, depth_filter, iproj, corr kernels) are outside this
+repository's scope; set GBA_REFERENCE_BACKENDS to a module name to
+forward them.
+"""
+from __future__ import annotations
+
+import importlib
+import os
+
+import torch
+
+import _gba
+
+# "droid_cuda" reproduces ba_cuda (default for the drop-in); "geom_py" reproduces
+# src/geom/ba.py::BA (SURVEY.md section 8.1 lists the differences).
+SEMANTICS = os.environ.get("GBA_SEMANTICS", "droid_cuda")
+# The reference returns [dx, dz]; GlORIE-SLAM discards them.  Sizing dz needs K on the host,
+# which costs one stream synchronisation after the call; set False to skip it.
+RETURN_UPDATES = True
+
+
+def _chk(t, name, dtype):
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise RuntimeError("%s must be a CUDA tensor" % name)
+    if not t.is_contiguous():
+        raise RuntimeError("%s must be contiguous" % name)  # CHECK_CONTIGUOUS, droid.cpp:85-86
+    if t.dtype != dtype:
+        raise RuntimeError("%s must have dtype %s, got %s" % (name, dtype, t.dtype))
+
+
+def ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1, iterations, lm, ep,
+       motion_only, depth_only=False):
+    """Dense bundle adjustment over the factor graph (ii -> jj), in place on poses / disps.
+
+    poses [N,7] f32, disps [N,ht,wd] f32, intrinsics [4], disps_sens [N,ht,wd],
+    targets / weights [E,2,ht,wd], eta [K,ht,wd], ii / jj [E] int64, all CUDA + contiguous.
+    Returns [dx [t1-t0,6], dz [K,ht*wd]] of the last iteration (dz is None when motion_only).
+    """
+    for t, n in ((poses, "poses"), (disps, "disps"), (intrinsics, "intrinsics"), (disps_sens, "disps_sens"),
+                 (targets, "targets"), (weights, "weights")):
+        _chk(t, n, torch.float32)
+    _chk(eta, "eta", torch.float32)
+    _chk(ii, "ii", torch.int64)
+    _chk(jj, "jj", torch.int64)
+    if poses.dim() != 2 or poses.shape[1] != 7 or disps.dim() != 3 or disps.shape[0] != poses.shape[0]:
+        raise RuntimeError("poses must be [N,7] and disps [N,ht,wd]")
+    N, ht, wd = disps.shape
+    E = int(ii.shape[0])
+    if targets.numel() != E * 2 * ht * wd or weights.numel() != E * 2 * ht * wd or jj.shape[0] != E:
+        raise RuntimeError("targets/weights must be [E,2,ht,wd] for E = len(ii) = len(jj)")
+    t0, t1, iterations = int(t0), int(t1), int(iterations)
+    dev = poses.device
+    with torch.cuda.device(dev):
+        ctx = _gba.context(dev.index, N, E, ht, wd)
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        P = t1 - t0
+        dx = torch.zeros((max(P, 0), 6), dtype=torch.float32, device=dev)
+        dz = None
+        if RETURN_UPDATES and not motion_only:
+            dz = torch.zeros((N, ht * wd), dtype=torch.float32, device=dev)
+        eta_rows = int(eta.shape[0]) if eta.dim() > 0 else 0
+        rc = _gba.lib().gba_ba(ctx, poses.data_ptr(), disps.data_ptr(), intrinsics.data_ptr(), disps_sens.data_ptr(),
+                               targets.data_ptr(), weights.data_ptr(), eta.data_ptr(), ii.data_ptr(), jj.data_ptr(),
+                               N, E, eta_rows, t0, t1, iterations, float(lm), float(ep), int(bool(motion_only)),
+                               int(bool(depth_only)), _gba.MODES[SEMANTICS], dx.data_ptr(),
+                               dz.data_ptr() if dz is not None else None, stream)
+        _gba.check(ctx, rc)
+        if dz is not None:
+            dz = dz[: _gba.query(ctx).n_depth_frames]
+    return [dx, dz]
+
+
+def __getattr__(name):
+    fwd = os.environ.get("GBA_REFERENCE_BACKENDS")
+    if fwd:
+        return getattr(importlib.import_module(fwd), name)
+    raise AttributeError(
+        "droid_backends.%s is outside the B200 hot path (only `ba` is provided); set GBA_REFERENCE_BACKENDS "
+        "to the reference extension's module name to forward it" % name)

@@ -1,0 +1,133 @@
+/*
+ * gba.h -- C ABI of the B200-native dense bundle-adjustment / DSPO library (libgba.so).
+ *
+ * This is the drop-in boundary for ONE hot path of GlORIE-SLAM: the call
+ *     droid_backends.ba(poses, disps, intrinsics, disps_sens, targets, weights, eta,
+ *                       ii, jj, t0, t1, iterations, lm, ep, motion_only, depth_only)
+ * (reference src/lib/droid.cpp:89-119 -> src/lib/droid_kernels.cu:1314-1437) and its DSPO
+ * stage-2 variant src/geom/ba.py:127-216 (BA_with_scale_shift), both dispatched from
+ * reference src/depth_video.py:198-288.
+ *
+ * Conventions
+ *   - plain C, no C++ / torch types; every array argument is a raw DEVICE pointer owned by
+ *     the caller (e.g. torch.Tensor.data_ptr()), contiguous, fp32 unless stated; ii/jj are
+ *     int64 as in the reference.  `stream` is a cudaStream_t passed as void*.
+ *   - functions return 0 on success, a negative GBA_E* code otherwise; gba_last_error() gives
+ *     the text.  A non-SPD reduced camera system is NOT an error: like the reference
+ *     (droid_kernels.cu:1207-1210, chol.py:13-15) the pose update is zero; the count of such
+ *     iterations is reported by gba_query().
+ *   - a context is bound to one device and is not re-entrant; calls are asynchronous on
+ *     `stream` except for one small status read-back after the index build.
+ *   - no CPU fallback exists: every entry point fails with GBA_ECUDA when no device is usable.
+ */
+#ifndef GBA_H_
+#define GBA_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct gba_ctx gba_ctx;
+
+/* semantics modes (the reference's two BA implementations differ) */
+#define GBA_MODE_DROID_CUDA 0 /* src/lib/droid_kernels.cu::ba_cuda -- what droid_backends.ba runs */
+#define GBA_MODE_GEOM_PY 1    /* src/geom/ba.py::BA + src/geom/chol.py::schur_solve              */
+
+#define GBA_OK 0
+#define GBA_EINVAL -1   /* bad argument / index out of range / eta rows != K */
+#define GBA_ECUDA -2    /* CUDA runtime error (text in gba_last_error)       */
+#define GBA_ECAPACITY -3 /* problem exceeds the sizes given to gba_create    */
+
+/* Creates a context on `device` with workspaces for up to max_frames keyframes, max_edges
+ * factor-graph edges and ht x wd disparity maps (1/8 resolution, e.g. 48 x 64).  All device
+ * memory the library ever uses is allocated here.  Replaces the per-call torch::zeros /
+ * Eigen allocations of droid_kernels.cu:1351-1356,1117-1129. */
+int gba_create(gba_ctx **out, int device, int max_frames, int max_edges, int ht, int wd);
+void gba_destroy(gba_ctx *ctx);
+/* ctx may be NULL: returns the text of the last gba_create failure on this thread. */
+const char *gba_last_error(const gba_ctx *ctx);
+
+/* Dense bundle adjustment, `iters` Gauss-Newton iterations; replaces
+ * droid_backends.ba == ba_cuda (src/lib/droid_kernels.cu:1314-1437).
+ *   poses      [n_frames,7]  in/out  (tx,ty,tz,qx,qy,qz,qw), rows [t0,t1) updated in place
+ *   disps      [n_frames,ht,wd] in/out, rows kx[] updated in place (no clamp in droid mode;
+ *                              clamp(min=0) per iteration in geom mode, ba.py:119)
+ *   intrinsics [4] fx,fy,cx,cy;  disps_sens [n_frames,ht,wd] (zeros = no sensor depth)
+ *   targets, weights [n_edges,2,ht,wd] planar (u plane, v plane)
+ *   eta        [eta_rows,ht,wd], eta_rows must equal K = |unique([t0,t1) U ii)| (droid) or
+ *              |unique(ii)| (geom)
+ *   ii, jj     [n_edges] int64 source / destination keyframe of each edge
+ *   dx_out     [t1-t0,6] or NULL : last iteration's pose update
+ *   dz_out     [K,ht*wd] or NULL : last iteration's disparity update (untouched if motion_only)
+ */
+int gba_ba(gba_ctx *ctx, float *poses, float *disps, const float *intrinsics, const float *disps_sens,
+           const float *targets, const float *weights, const float *eta, const int64_t *ii, const int64_t *jj,
+           int n_frames, int n_edges, int eta_rows, int t0, int t1, int iters, float lm, float ep, int motion_only,
+           int depth_only, int mode, float *dx_out, float *dz_out, void *stream);
+
+/* DSPO stage 2: one iteration of src/geom/ba.py:127-216 (BA_with_scale_shift): optimises
+ * disparities and per-keyframe (scale, shift) of the mono-depth prior, poses fixed.
+ *   targets, weights: [n_edges,ht,wd,2] when interleaved != 0 (the layout this reference entry
+ *                     point receives), else planar [n_edges,2,ht,wd]
+ *   eta [eta_rows,ht,wd] with eta_rows == |unique(ii)|;  mono_disps [n_frames,ht,wd]
+ *   scales, shifts [n_frames] in/out;  valid_mask [n_frames,ht,wd] one byte per pixel
+ *   disps updated in place and clamped at 0 (ba.py:214).
+ * The reference returns new tensors; the Python mirror clones before calling. */
+int gba_dspo(gba_ctx *ctx, const float *poses, float *disps, const float *intrinsics, const float *targets,
+             const float *weights, const float *eta, const int64_t *ii, const int64_t *jj, const float *mono_disps,
+             float *scales, float *shifts, const uint8_t *valid_mask, int n_frames, int n_edges, int eta_rows,
+             int ignore_frames, float lm, float ep, float alpha, int interleaved, void *stream);
+
+/* ---- split-phase form of gba_ba for edge-sharded multi-GPU runs --------
+ * Every rank calls begin with ITS edges (all edges of a source keyframe live on one rank),
+ * `kx_global` = the global sorted list of depth keyframes (so eta rows and dz rows are the
+ * same on every rank; NULL = derive from the local edges) and `owned` (one byte per kx entry,
+ * NULL = all) marking whose disparities this rank updates.  Per iteration:
+ *   gba_ba_build  -> local contribution to the reduced camera system, packed in a buffer
+ *   (caller sums the buffer over ranks, e.g. ncclAllReduce / torch.distributed.all_reduce)
+ *   gba_ba_solve  -> damping, factorisation, solve, back-substitution, retraction
+ * gba_ba() is begin + iters x (build, solve) + end on one rank. */
+int gba_ba_begin(gba_ctx *ctx, float *poses, float *disps, const float *intrinsics, const float *disps_sens,
+                 const float *targets, const float *weights, const float *eta, const int64_t *ii, const int64_t *jj,
+                 int n_frames, int n_edges, int eta_rows, int t0, int t1, float lm, float ep, int motion_only,
+                 int depth_only, int mode, const int64_t *kx_global, int n_kx, const uint8_t *owned, void *stream);
+int gba_ba_build(gba_ctx *ctx);
+/* device pointer + element count (doubles) of the packed reduced system of the last build */
+int gba_ba_system(gba_ctx *ctx, double **buf, size_t *count);
+int gba_ba_solve(gba_ctx *ctx);
+int gba_ba_end(gba_ctx *ctx, float *dx_out, float *dz_out);
+
+/* ---- introspection (used by the parity tests; synchronises the stream) ----------------- */
+typedef struct gba_info {
+  int n_depth_frames;   /* K                                                  */
+  int n_poses;          /* P = t1 - t0                                        */
+  int max_out_degree;   /* largest number of edges sharing a source keyframe  */
+  int chol_failures;    /* iterations whose factorisation hit a pivot <= 0    */
+  int n_tiles;          /* tile rows of the reduced camera matrix             */
+  int n_active_tiles;   /* lower-triangular tiles touched after symbolic fill */
+  int kernel_launches;  /* kernels launched by the last gba_ba / gba_dspo call */
+  int reserved;
+} gba_info;
+int gba_query(gba_ctx *ctx, gba_info *info);
+
+/* Copies an internal device array of the last call to HOST memory `dst` (capacity `bytes`).
+ * what: */
+#define GBA_GET_KX 1       /* int32 [K]   sorted depth keyframes (droid_kernels.cu:1341-1345) */
+#define GBA_GET_EPTR 2     /* int32 [K+1] CSR row pointers by source keyframe (:948-984)      */
+#define GBA_GET_EIDX 3     /* int32 [E]   edge ids grouped by source keyframe, edge order     */
+#define GBA_GET_EDGE_HV 4  /* float [E,32] per edge: 21 upper-tri of H_jj then 6 of v_j       */
+#define GBA_GET_Q 5        /* float [K,HW] 1/C of the last iteration                          */
+#define GBA_GET_W 6        /* float [K,HW] w of the last iteration                            */
+#define GBA_GET_SYSTEM 7   /* double [6P*6P + 6P] row-major lower triangle of the reduced camera matrix A - S as
+                              left by the last gba_ba_build (geom mode: damping already on A; droid mode: not
+                              yet damped), then the rhs b - vS.  Valid between gba_ba_build and gba_ba_solve. */
+#define GBA_GET_TILEMASK 8 /* uint8 [nT,nT] lower-triangular tile structure after fill        */
+int gba_get(gba_ctx *ctx, int what, void *dst, size_t bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GBA_H_ */

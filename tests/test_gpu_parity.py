@@ -1,0 +1,325 @@
+"""GPU parity tests proper: libgba.so (through the C ABI) against the CPU oracle on the same seeded
+inputs, against the golden vectors produced by the reference itself, and -- at full size --
+through size-independent properties.  Tolerance: BASELINE.json:north_star, 1e-4 relative on the
+state (poses, disparities) after a fixed iteration count, fp32 arithmetic; index structures exact."""
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+
+import synth
+from helpers import STATE_RTOL, load_golden, rel, sign_normalise
+from oracle import oracle
+
+pytestmark = pytest.mark.gpu
+
+import _gba  # noqa: E402
+from gba_run import get_array, run_ba, split_phase, to_dev  # noqa: E402
+
+
+def small_graphs():
+    return {
+        "A": synth.make_config("A"),
+        "R": synth.make_graph(6, 14, 2, iters=2, lm=1e-5, ep=1e-2, seed=3, ht=30, wd=40, t0=2),
+        "tiny": synth.make_graph(5, 8, 1, iters=2, seed=2, ht=8, wd=12),
+        "B": synth.make_config("B"),
+    }
+
+
+# ------------------------------------------------------------------------------------------
+# index structures: bit-exact (droid_kernels.cu:948-984,1337-1345)
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["A", "R", "tiny", "B"])
+def test_index_structures_exact(name):
+    g = small_graphs()[name]
+    r = run_ba(g, iters=1)
+    kx = np.unique(np.concatenate([np.arange(g.t0, g.t1), g.ii]))
+    K = len(kx)
+    assert r.info.n_depth_frames == K
+    np.testing.assert_array_equal(get_array(r.ctx, _gba.GET_KX, (K,), np.int32), kx)
+    order = np.argsort(g.ii, kind="stable")  # accum_cuda: argsort + CSR by source keyframe
+    ptr = np.searchsorted(g.ii[order], kx, side="left")
+    ptr = np.concatenate([ptr, [g.n_edges]]) if kx[-1] >= g.ii.max() else None
+    eptr = get_array(r.ctx, _gba.GET_EPTR, (K + 1,), np.int32)
+    eidx = get_array(r.ctx, _gba.GET_EIDX, (g.n_edges,), np.int32)
+    counts = np.array([(g.ii == f).sum() for f in kx])
+    np.testing.assert_array_equal(np.diff(eptr), counts)
+    np.testing.assert_array_equal(eidx, order)
+    assert r.info.max_out_degree == counts.max()
+
+
+def test_index_structures_shuffled_edges_and_sparse_window():
+    """edges in random order, a window keyframe without out-edges, edges from fixed keyframes"""
+    g = synth.make_graph(9, 20, 2, iters=1, seed=11, ht=8, wd=12, t0=3)
+    rng = np.random.default_rng(0)
+    keep = g.ii != 5  # keyframe 5 keeps no out-edge but stays in the window
+    perm = rng.permutation(int(keep.sum()))
+    g.ii, g.jj = g.ii[keep][perm], g.jj[keep][perm]
+    g.targets, g.weights = g.targets[keep][perm], g.weights[keep][perm]
+    kx = np.unique(np.concatenate([np.arange(g.t0, g.t1), g.ii]))
+    g.eta = np.resize(g.eta, (len(kx),) + g.eta.shape[1:]).astype(np.float32)
+    r = run_ba(g, iters=1)
+    np.testing.assert_array_equal(get_array(r.ctx, _gba.GET_KX, (len(kx),), np.int32), kx)
+    np.testing.assert_array_equal(get_array(r.ctx, _gba.GET_EIDX, (g.n_edges,), np.int32),
+                                  np.argsort(g.ii, kind="stable"))
+    o = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj, g.t0, g.t1,
+                  1, g.lm, g.ep, precision="f64")
+    assert rel(sign_normalise(r.poses), sign_normalise(o.poses)) < STATE_RTOL
+    assert rel(r.disps, o.disps) < STATE_RTOL
+
+
+# ------------------------------------------------------------------------------------------
+# first-iteration fields against the oracle
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["A", "R", "B"])
+def test_linearisation_and_reduced_system(name):
+    g = small_graphs()[name]
+    o = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj, g.t0, g.t1,
+                  1, g.lm, g.ep, precision="f64", debug=True)
+    s = split_phase(g, mode=0, iters=1)
+    # reduced camera matrix A - S (lower triangle) and rhs b - vS
+    n = 6 * (g.t1 - g.t0)
+    Mo = np.tril(o.M)
+    assert rel(s.M, Mo) < 2e-5
+    assert rel(s.rhs, o.rhs) < 2e-5
+    # pose update and state after one iteration
+    assert rel(sign_normalise(s.poses), sign_normalise(o.poses)) < STATE_RTOL
+    assert rel(s.disps, o.disps) < STATE_RTOL
+    # per-edge H_jj / v_j and the depth diagonal through the one-shot entry point
+    r = run_ba(g, iters=1)
+    hv = get_array(r.ctx, _gba.GET_EDGE_HV, (g.n_edges, 32), np.float32)
+    iu = np.triu_indices(6)
+    Hjj = o.Hs[:, 3][:, iu[0], iu[1]]
+    assert rel(hv[:, :21], Hjj) < 1e-5
+    assert rel(hv[:, 21:27], o.vs[:, 1]) < 1e-5
+    K = len(o.kx)
+    # Q, W of the call are from its only iteration
+    Q = get_array(r.ctx, _gba.GET_Q, (K, g.hw), np.float32)
+    W = get_array(r.ctx, _gba.GET_W, (K, g.hw), np.float32)
+    assert rel(1.0 / Q, o.C) < 1e-5
+    assert rel(W, o.w) < 1e-5
+    assert rel(r.dx, o.dx) < 1e-3  # dx itself is small; the bar is on the state
+    assert rel(r.dz, o.dz) < 1e-3
+
+
+# ------------------------------------------------------------------------------------------
+# state after the configured iteration count, both semantics modes
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["A", "R", "tiny", "B"])
+@pytest.mark.parametrize("mode", ["droid_cuda", "geom_py"])
+def test_state_matches_oracle(name, mode):
+    g = small_graphs()[name]
+    o = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj, g.t0, g.t1,
+                  g.iters, g.lm, g.ep, mode=oracle.MODE_DROID_CUDA if mode == "droid_cuda" else oracle.MODE_GEOM_PY,
+                  precision="f64")
+    r = run_ba(g, mode=mode)
+    assert r.info.chol_failures == 0 and o.fail == 0
+    assert rel(sign_normalise(r.poses), sign_normalise(o.poses)) < STATE_RTOL
+    assert rel(r.disps, o.disps) < STATE_RTOL
+    np.testing.assert_array_equal(r.poses[: g.t0], g.poses[: g.t0])  # fixed poses never move
+
+
+@pytest.mark.parametrize("name", ["A", "R"])
+def test_geom_mode_matches_reference_golden(name):
+    """golden vectors = the reference's own src/geom/ba.py::BA run on CPU (tests/golden/make_golden.py)"""
+    g, z, kw = load_golden(name)
+    r = run_ba(g, mode="geom_py")
+    for ref in ("f64", "f32"):
+        assert rel(sign_normalise(r.poses), sign_normalise(z["poses_" + ref])) < STATE_RTOL
+        assert rel(r.disps, z["disps_" + ref].reshape(r.disps.shape)) < STATE_RTOL
+
+
+def test_geom_ba_mirror_is_functional():
+    import geom_ba
+
+    g, z, kw = load_golden("A")
+    d = to_dev(g)
+    target = d.targets.permute(0, 2, 3, 1).contiguous()[None]
+    weight = d.weights.permute(0, 2, 3, 1).contiguous()[None]
+    poses, disps = d.poses[None].clone(), d.disps[None].clone()
+    intr = d.intr[None, None].repeat(1, g.n_frames, 1)
+    for _ in range(g.iters):
+        poses, disps = geom_ba.BA(target, weight, d.eta, poses, disps, intr, d.ii, d.jj, lm=g.lm, ep=g.ep, fixedp=g.t0)
+    assert rel(sign_normalise(poses[0].cpu().numpy()), sign_normalise(z["poses_f64"])) < STATE_RTOL
+    assert rel(disps[0].cpu().numpy(), z["disps_f64"]) < STATE_RTOL
+    np.testing.assert_array_equal(d.poses.cpu().numpy(), g.poses)  # inputs untouched
+
+
+# ------------------------------------------------------------------------------------------
+# flags, contracts, errors
+# ------------------------------------------------------------------------------------------
+def test_motion_only_and_depth_only():
+    g = small_graphs()["R"]
+    for kw in (dict(motion_only=True), dict(depth_only=True)):
+        o = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj, g.t0,
+                      g.t1, 2, g.lm, g.ep, precision="f64", **kw)
+        r = run_ba(g, iters=2, **kw)
+        assert rel(sign_normalise(r.poses), sign_normalise(o.poses)) < STATE_RTOL
+        assert rel(r.disps, o.disps) < STATE_RTOL
+        if "motion_only" in kw:
+            np.testing.assert_array_equal(r.disps, g.disps)
+            assert r.dz is None
+        else:
+            np.testing.assert_array_equal(r.poses, g.poses)
+            assert rel(r.dx, o.dx) < 1e-3
+
+
+def test_sensor_depth_prior():
+    g = small_graphs()["tiny"]
+    rng = np.random.default_rng(4)
+    g.disps_sens = (g.disps_gt * (rng.uniform(size=g.disps.shape) < 0.5)).astype(np.float32)
+    o = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj, g.t0, g.t1,
+                  2, g.lm, g.ep, precision="f64")
+    r = run_ba(g, iters=2)
+    assert rel(r.disps, o.disps) < STATE_RTOL
+    assert rel(sign_normalise(r.poses), sign_normalise(o.poses)) < STATE_RTOL
+
+
+def test_non_spd_system_gives_zero_update():
+    """failed factorisation -> zero pose update, no exception (droid_kernels.cu:1207-1210)"""
+    g = small_graphs()["tiny"]
+    r = run_ba(g, iters=1, motion_only=True, lm=-2.0, ep=0.0)
+    assert r.info.chol_failures == 1
+    np.testing.assert_array_equal(r.dx, 0)
+    np.testing.assert_array_equal(r.poses, g.poses)
+
+
+def test_argument_errors():
+    import droid_backends
+
+    g = small_graphs()["tiny"]
+    d = to_dev(g)
+    args = [d.poses, d.disps, d.intr, d.sens, d.targets, d.weights, d.eta, d.ii, d.jj, g.t0, g.t1, 1, 1e-4, 0.1, False]
+    with pytest.raises(RuntimeError, match="contiguous"):
+        bad = list(args)
+        bad[4] = d.targets.permute(0, 1, 3, 2)
+        droid_backends.ba(*bad)
+    with pytest.raises(RuntimeError, match="eta"):
+        bad = list(args)
+        bad[6] = d.eta[:-1].contiguous()
+        droid_backends.ba(*bad)
+    with pytest.raises(RuntimeError, match="outside"):
+        bad = list(args)
+        bad[8] = d.jj + 100
+        droid_backends.ba(*bad)
+    with pytest.raises(RuntimeError):
+        droid_backends.ba(*[a.cpu() if isinstance(a, torch.Tensor) else a for a in args])
+    # 16th positional argument (depth_only) is accepted like the reference (depth_video.py:217-218)
+    droid_backends.ba(*(args + [False]))
+
+
+# ------------------------------------------------------------------------------------------
+# DSPO stage 2
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["A", "R"])
+def test_dspo_matches_reference_golden(name):
+    import geom_ba
+
+    g, z, kw = load_golden(name)
+    synth.with_mono_prior(g, seed=kw["seed"] + 1)
+    d = to_dev(g)
+    target = d.targets.permute(0, 2, 3, 1).contiguous()[None]
+    weight = d.weights.permute(0, 2, 3, 1).contiguous()[None]
+    disps = d.disps[None]
+    poses = d.poses[None]
+    intr = d.intr[None, None].repeat(1, g.n_frames, 1)
+    mono = torch.from_numpy(g.mono_disps).cuda()[None]
+    mask = torch.from_numpy(g.valid_depth_mask).cuda()[None]
+    scales = torch.from_numpy(g.scales).cuda()[None]
+    shifts = torch.from_numpy(g.shifts).cuda()[None]
+    d0 = disps.clone()
+    for _ in range(2):
+        poses, disps, wqs = geom_ba.BA_with_scale_shift(target, weight, d.eta, poses, disps, intr, d.ii, d.jj, mono,
+                                                        scales, shifts, mask, 0, g.lm, g.ep, alpha=g.alpha)
+        scales, shifts = wqs[..., 0], wqs[..., 1]
+    assert torch.equal(d0, d.disps[None])  # functional: caller tensors untouched
+    assert rel(disps[0].cpu().numpy(), z["dspo_disps_f64"]) < STATE_RTOL
+    assert rel(wqs[0].cpu().numpy(), z["dspo_wqs_f64"]) < STATE_RTOL
+
+
+def test_dspo_against_oracle_config_b_with_ignored_frames():
+    import geom_ba
+
+    g = synth.with_mono_prior(synth.make_config("B"), seed=5)
+    tg = np.ascontiguousarray(g.targets.transpose(0, 2, 3, 1))
+    wg = np.ascontiguousarray(g.weights.transpose(0, 2, 3, 1))
+    o = oracle.dspo(g.poses, g.disps, g.intrinsics, tg, wg, g.eta, g.ii, g.jj, g.mono_disps, g.scales, g.shifts,
+                    g.valid_depth_mask, 3, g.lm, g.ep, g.alpha, precision="f64")
+    d = to_dev(g)
+    _, disps, wqs = geom_ba.BA_with_scale_shift(
+        torch.from_numpy(tg).cuda()[None], torch.from_numpy(wg).cuda()[None], d.eta, d.poses[None], d.disps[None],
+        d.intr[None, None].repeat(1, g.n_frames, 1), d.ii, d.jj, torch.from_numpy(g.mono_disps).cuda()[None],
+        torch.from_numpy(g.scales).cuda()[None], torch.from_numpy(g.shifts).cuda()[None],
+        torch.from_numpy(g.valid_depth_mask).cuda()[None], 3, g.lm, g.ep, alpha=g.alpha)
+    assert rel(disps[0].cpu().numpy(), o.disps) < STATE_RTOL
+    assert rel(wqs[0].cpu().numpy(), np.stack([o.scales, o.shifts], -1)) < STATE_RTOL
+
+
+# ------------------------------------------------------------------------------------------
+# edge sharding (two emulated ranks on one GPU; the NCCL plumbing itself is covered on CPU/gloo)
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["A", "B"])
+def test_sharded_build_sums_to_single_rank(name):
+    g = small_graphs()[name]
+    one = split_phase(g, iters=2)
+    K = len(one.kx)
+    m0 = (np.arange(K) % 2 == 0).astype(np.uint8)
+    two = split_phase(g, owned_masks=[m0, 1 - m0], iters=2)
+    assert rel(two.M, one.M) < 1e-6
+    assert rel(two.rhs, one.rhs) < 1e-6
+    assert rel(sign_normalise(two.poses), sign_normalise(one.poses)) < 1e-5
+    assert rel(two.disps, one.disps) < 1e-5
+
+
+# ------------------------------------------------------------------------------------------
+# full BASELINE sizes: properties instead of the (too slow) oracle
+# ------------------------------------------------------------------------------------------
+def reprojection_cost(g, poses, disps):
+    pred = synth.project(poses, disps, g.intrinsics, g.ii, g.jj)
+    return float(np.mean(g.weights * (g.targets - pred) ** 2))
+
+
+@pytest.mark.parametrize("name", ["C"])
+def test_full_size_properties(name):
+    g = synth.make_config(name)
+    c0 = reprojection_cost(g, g.poses, g.disps)
+    r = run_ba(g)
+    assert r.info.chol_failures == 0
+    assert np.isfinite(r.poses).all() and np.isfinite(r.disps).all()
+    c1 = reprojection_cost(g, r.poses, r.disps)
+    assert c1 < 0.5 * c0, (c0, c1)  # Gauss-Newton must cut the weighted reprojection cost
+    assert rel(r.poses[1:, :3], g.poses_gt[1:, :3]) < rel(g.poses[1:, :3], g.poses_gt[1:, :3])
+    np.testing.assert_allclose(np.linalg.norm(r.poses[:, 3:], axis=1), 1.0, atol=1e-4)
+    # determinism of the state up to atomics-order noise, and edge-permutation invariance
+    r2 = run_ba(g)
+    assert rel(r2.poses, r.poses) < 1e-6 and rel(r2.disps, r.disps) < 1e-6
+    perm = np.random.default_rng(1).permutation(g.n_edges)
+    g.ii, g.jj, g.targets, g.weights = g.ii[perm], g.jj[perm], g.targets[perm], g.weights[perm]
+    r3 = run_ba(g)
+    assert rel(r3.poses, r.poses) < 1e-5 and rel(r3.disps, r.disps) < 1e-5
+
+
+def test_reference_cuda_backend_if_present():
+    """On the B200 box: the reference's own droid_backends.ba (oracle/_ref, built by
+    oracle/build_ref.py from the unmodified sources) against libgba on configs A, R and B."""
+    import importlib.util
+    import os
+
+    from helpers import ROOT
+
+    so = os.path.join(ROOT, "oracle", "_ref", "ref_droid_backends.so")
+    if not os.path.exists(so):
+        pytest.skip("oracle/_ref/ref_droid_backends.so not built")
+    spec = importlib.util.spec_from_file_location("ref_droid_backends", so)
+    ref = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ref)
+    for name in ("A", "R", "B"):
+        g = small_graphs()[name]
+        d = to_dev(g)
+        ref.ba(d.poses, d.disps, d.intr, d.sens, d.targets, d.weights, d.eta, d.ii, d.jj, g.t0, g.t1, g.iters, g.lm,
+               g.ep, False, False)
+        torch.cuda.synchronize()
+        r = run_ba(g)
+        assert rel(sign_normalise(r.poses), sign_normalise(d.poses.cpu().numpy())) < STATE_RTOL, name
+        assert rel(r.disps, d.disps.cpu().numpy()) < STATE_RTOL, name
