@@ -1,0 +1,328 @@
+#!/usr/bin/env python
+"""bench.py -- dense BA hot path on B200: edge-pixel residuals/s and ms per BA iteration.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--config E] [--impl b200|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
+
+A "step" is one `droid_backends.ba` call (`iters` Gauss-Newton iterations, BASELINE.json's
+backend setting 2) over one synthetic factor graph.  Default workload: config E (ScanNet-scale
+global BA, 1000 keyframes / 20000 edges / 48x64), the configuration BASELINE.json's metric and
+target are quoted on; it fits one GPU.  At N > 1 the SAME graph is edge-sharded by source keyframe
+over the ranks (strong scaling) with one NCCL all-reduce of the packed reduced camera system per
+iteration.
+
+Printed JSON (one line, rank 0): the driver contract plus
+  roofline     -- the per-edge HBM kernel (k_linearize): algorithmic bytes / its CUDA-event time
+  stages       -- device ms per step of every stage (events on the launch stream, separate pass)
+  cpu_baseline -- the CPU oracle (port of the reference's ba_cuda) on a bounded sample, host cores
+  e2e          -- same metric through the public API with pinned HOST buffers, copies timed
+`--impl reference` times the CPU port on the host cores (the reference's Python BA cannot travel
+to the GPU box and its CUDA build has no CPU path).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "glorie-slam_b200")
+for _p in (ROOT, PKG):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+
+METRIC = "edge-pixel residuals/sec (global BA; ms per BA iteration in ms_per_ba_iteration)"
+UNIT = "edge-pixels/s"
+CPU_SAMPLE = dict(n=60, e=1000, r=9, iters=2, lm=1e-5, ep=1e-2, seed=0)
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.path = index, None, None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for line in open(self.path):
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        os.unlink(self.path)
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons),
+                       samples=len(sm))
+        return out
+
+
+def cpu_baseline(steps=1):
+    """CPU oracle (C port of the reference's ba_cuda, OpenMP over edges / keyframes) on a bounded
+    sample of the same kind of graph; edge-pixels/s on this box's host cores."""
+    import synth
+    from oracle import oracle
+
+    g = synth.make_graph(**CPU_SAMPLE)
+    best = None
+    for _ in range(max(steps, 1)):
+        t = time.perf_counter()
+        oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj, g.t0, g.t1,
+                  g.iters, g.lm, g.ep, precision="f32")
+        dt = time.perf_counter() - t
+        best = dt if best is None else min(best, dt)
+    return {
+        "value": g.n_edges * g.hw * g.iters / best, "unit": UNIT, "cores": oracle.num_threads(), "kind": "port",
+        "sample": "%d keyframes / %d edges / %dx%d / %d iterations, best of %d (%.2f s each)" % (
+            g.n_frames, g.n_edges, g.disps.shape[1], g.disps.shape[2], g.iters, max(steps, 1), best),
+        "ms_per_ba_iteration": 1e3 * best / g.iters,
+    }
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    for _ in range(args.warmup if args.warmup < 2 else 1):
+        cpu_baseline(1)
+    cb = cpu_baseline(args.steps)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_ba_iteration"] * CPU_SAMPLE["iters"],
+        "ms_per_ba_iteration": cb["ms_per_ba_iteration"], "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "config %s (global BA), timed on the bounded CPU sample in cpu_baseline.sample" % args.config},
+        "cpu_baseline": cb,
+        "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="E", choices=["A", "B", "C", "E"])
+    ap.add_argument("--skip-e2e", action="store_true")
+    ap.add_argument("--skip-cpu", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    import _gba
+    import droid_backends
+    import sharded
+    import synth
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: libgba has no CPU path (use --impl reference for the CPU port)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    args.warmup = max(args.warmup, 3)
+
+    # ---- workload -----------------------------------------------------------------------------
+    g = synth.make_config(args.config)
+    iters = g.iters
+    N, ht, wd = g.disps.shape
+    HW = ht * wd
+    kx = sharded.frame_list(g.ii, g.t0, g.t1)
+    owner = sharded.partition(g.ii, kx, world)
+    sel = sharded.local_edges(g.ii, kx, owner, rank)
+    E_total, E_local = g.n_edges, int(sel.sum())
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    host = dict(poses=pin(g.poses), disps=pin(g.disps), intr=pin(g.intrinsics), sens=pin(g.disps_sens),
+                targets=pin(g.targets[sel]), weights=pin(g.weights[sel]), eta=pin(g.eta), ii=pin(g.ii[sel]),
+                jj=pin(g.jj[sel]))
+    d = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
+    poses0, disps0 = d["poses"].clone(), d["disps"].clone()
+    kx_t = torch.from_numpy(kx).to(dev)
+    owned_t = torch.from_numpy((owner == rank).astype(np.uint8)).to(dev)
+    droid_backends.RETURN_UPDATES = False  # GlORIE-SLAM discards [dx, dz]; skip the extra sync
+    input_bytes = sum(v.numel() * v.element_size() for k, v in host.items())
+    l2_flush = None
+    if input_bytes < 400e6:  # inputs not much larger than the 126 MB L2: flush it between steps
+        l2_flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def reset():
+        d["poses"].copy_(poses0)
+        d["disps"].copy_(disps0)
+
+    def step():
+        if world == 1:
+            droid_backends.ba(d["poses"], d["disps"], d["intr"], d["sens"], d["targets"], d["weights"], d["eta"],
+                              d["ii"], d["jj"], g.t0, g.t1, iters, g.lm, g.ep, False, False)
+        else:
+            sharded.ba_sharded(d["poses"], d["disps"], d["intr"], d["sens"], d["targets"], d["weights"], d["eta"],
+                               d["ii"], d["jj"], g.t0, g.t1, iters, g.lm, g.ep, kx_t, owned_t)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(nsteps, fn):
+        """sum of per-step CUDA-event times (ms) on the launch stream; state reset and the L2 flush
+        stay outside the event pairs"""
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(nsteps)]
+        barrier()
+        for a, b in evs:
+            reset()
+            if l2_flush is not None:
+                l2_flush.fill_(1)
+            a.record()
+            fn()
+            b.record()
+        barrier()
+        ms = sum(a.elapsed_time(b) for a, b in evs)
+        if world > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    # ---- warm-up, then the device-timed region ---------------------------------------------------
+    for _ in range(args.warmup):
+        reset()
+        step()
+    barrier()
+    ctx = _gba.context(local_rank, N, max(E_local, 1), ht, wd)
+    info = _gba.query(ctx)
+    launches_per_step = info.kernel_launches
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    total_ms = timed(args.steps, step)
+    clocks = sampler.stop() if rank == 0 else None
+    ms_per_step = total_ms / args.steps
+    value = E_total * HW * iters / (ms_per_step * 1e-3)
+
+    # ---- per-stage pass (events inside the library, on the launch stream) ------------------------
+    _gba.set_timing(ctx, True)
+    for _ in range(args.steps):
+        reset()
+        if l2_flush is not None:
+            l2_flush.fill_(1)
+        step()
+    tm = _gba.get_timing(ctx)
+    _gba.set_timing(ctx, False)
+    stages = {s: {"ms_per_step": v[0] / args.steps, "launches_per_step": v[1] / args.steps} for s, v in tm.items()
+              if v[1] > 0}
+    pk, pk_src = peaks()
+    K_local = int(owned_t.sum().item())
+    # algorithmic bytes of ONE k_linearize launch on this rank: target + weight
+    # 16 B per edge pixel, and per depth-keyframe pixel disparity 4 + eta 4 + sensor 4 + Q/w out 8
+    alg_bytes = 16.0 * E_local * HW + 20.0 * K_local * HW
+    lin_ms = stages.get("linearize", {}).get("ms_per_step", 0.0) / max(iters, 1)
+    achieved = alg_bytes / (lin_ms * 1e-3) / 1e9 if lin_ms > 0 else 0.0
+    roofline = {"bound": "hbm", "kernel": "k_linearize", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
+                "frac": achieved / pk["hbm_gbs"], "traffic": None, "peak_source": pk_src,
+                "algorithmic_bytes_per_launch": alg_bytes, "ms_per_launch": lin_ms}
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            roofline["traffic"] = json.load(f).get("k_linearize_%s_dram_bytes" % args.config)
+    except Exception:
+        pass
+
+    # ---- end to end: pinned host buffers -> public API -> host, copies inside the timed region ----
+    e2e = None
+    if not args.skip_e2e:
+        out_p, out_d = torch.empty_like(host["poses"]).pin_memory(), torch.empty_like(host["disps"]).pin_memory()
+
+        def e2e_step():
+            for k in ("poses", "disps", "intr", "sens", "targets", "weights", "eta", "ii", "jj"):
+                d[k].copy_(host[k], non_blocking=True)
+            step()
+            out_p.copy_(d["poses"], non_blocking=True)
+            out_d.copy_(d["disps"], non_blocking=True)
+
+        for _ in range(2):
+            e2e_step()
+        e2e_ms = timed(max(args.steps // 2, 2), e2e_step) / max(args.steps // 2, 2)
+        e2e = {"value": E_total * HW * iters / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
+               "h2d_bytes_per_step": int(input_bytes),
+               "d2h_bytes_per_step": int(out_p.numel() * 4 + out_d.numel() * 4)}
+        if world > 1:
+            t = torch.tensor([e2e["h2d_bytes_per_step"]], dtype=torch.float64, device=dev)
+            dist.all_reduce(t)
+            e2e["h2d_bytes_per_step"] = int(t.item())
+
+    cb = None
+    if rank == 0 and world == 1 and not args.skip_cpu:
+        cb = cpu_baseline(2)
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_per_step, "ms_per_ba_iteration": ms_per_step / iters,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32 (fp64 reduced-system solve)",
+            "data": "synthetic",
+            "config": {"workload": "config %s: global BA, %d keyframes / %d edges / %dx%d, %d iterations per step"
+                                   % (args.config, N, E_total, ht, wd, iters),
+                       "lm": g.lm, "ep": g.ep, "sharding": "by source keyframe, %d rank(s)" % world,
+                       "l2": "inputs (%.0f MB per rank) larger than L2" % (input_bytes / 1e6) if l2_flush is None
+                             else "256 MB L2 flush between steps"},
+            "roofline": roofline, "stages": stages, "cpu_baseline": cb, "e2e": e2e,
+            "gpu_launches": int(launches_per_step * args.steps), "gpu_launches_per_step": int(launches_per_step),
+            "clocks": clocks,
+            "solver": {"tiles": info.n_tiles, "active_tiles": info.n_active_tiles, "chol_failures": info.chol_failures},
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -50,6 +50,10 @@ def lib():
         L.gba_ba_end.argtypes = [vp, vp, vp]
         L.gba_query.argtypes = [vp, ctypes.POINTER(Info)]
         L.gba_get.argtypes = [vp, ci, vp, ctypes.c_size_t]
+        L.gba_set_timing.argtypes = [vp, ci]
+        L.gba_get_timing.argtypes = [vp, ctypes.POINTER(cf), ctypes.POINTER(ci)]
+        L.gba_set_timing.restype = ci
+        L.gba_get_timing.restype = ci
         for f in ("gba_create", "gba_ba", "gba_dspo", "gba_ba_begin", "gba_ba_build", "gba_ba_system",
                   "gba_ba_solve", "gba_ba_end", "gba_query", "gba_get"):
             getattr(L, f).restype = ci
@@ -98,6 +102,21 @@ def release_all():
     for h, _, _ in _ctx.values():
         lib().gba_destroy(h)
     _ctx.clear()
+
+
+STAGES = ("index", "linearize", "pose_blocks", "gram", "schur", "factor", "solve", "backsub", "retract", "dspo")
+
+
+def set_timing(ctx, enable):
+    check(ctx, lib().gba_set_timing(ctx, int(enable)))
+
+
+def get_timing(ctx):
+    """{stage: (milliseconds, kernel launches)} accumulated since the last read (synchronises)."""
+    ms = (ctypes.c_float * len(STAGES))()
+    ln = (ctypes.c_int * len(STAGES))()
+    check(ctx, lib().gba_get_timing(ctx, ms, ln))
+    return {s: (float(ms[i]), int(ln[i])) for i, s in enumerate(STAGES)}
 
 
 def query(ctx):

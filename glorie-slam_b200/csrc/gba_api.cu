@@ -37,7 +37,35 @@ struct gba_ctx {
   int begun, launches, variant, gsplit, total_fail, last_P;
   size_t sys_count;
   char err[512];
+  // optional stage timing
+  int timing, cur_stage, cur_launch0;
+  std::vector<cudaEvent_t> *ev_pool;
+  std::vector<int> *ev_stage;   // stage of event pair i (events 2i, 2i+1)
+  std::vector<int> *ev_launch;  // launches inside pair i
+  size_t ev_used;
 };
+
+// RAII-free stage brackets: stage_begin/stage_end record an event pair on the call's stream
+static void stage_begin(gba_ctx *c, int stage) {
+  if (!c->timing) return;
+  if (c->ev_used + 2 > c->ev_pool->size()) {
+    cudaEvent_t a, b;
+    cudaEventCreate(&a);
+    cudaEventCreate(&b);
+    c->ev_pool->push_back(a);
+    c->ev_pool->push_back(b);
+  }
+  cudaEventRecord((*c->ev_pool)[c->ev_used], c->stream);
+  c->cur_stage = stage;
+  c->cur_launch0 = c->launches;
+}
+static void stage_end(gba_ctx *c) {
+  if (!c->timing) return;
+  cudaEventRecord((*c->ev_pool)[c->ev_used + 1], c->stream);
+  c->ev_stage->push_back(c->cur_stage);
+  c->ev_launch->push_back(c->launches - c->cur_launch0);
+  c->ev_used += 2;
+}
 
 static int fail_msg(gba_ctx *c, int code, const char *fmt, ...) {
   va_list ap;
@@ -80,6 +108,12 @@ extern "C" void gba_destroy(gba_ctx *c) {
   for (void *q : ptrs)
     if (q) cudaFree(q);
   if (c->st_h) cudaFreeHost(c->st_h);
+  if (c->ev_pool) {
+    for (cudaEvent_t e : *c->ev_pool) cudaEventDestroy(e);
+    delete c->ev_pool;
+    delete c->ev_stage;
+    delete c->ev_launch;
+  }
   free(c);
 }
 
@@ -97,6 +131,9 @@ extern "C" int gba_create(gba_ctx **out, int device, int max_frames, int max_edg
   }
   gba_ctx *ctx = (gba_ctx *)calloc(1, sizeof(gba_ctx));
   c = ctx;
+  c->ev_pool = new std::vector<cudaEvent_t>();
+  c->ev_stage = new std::vector<int>();
+  c->ev_launch = new std::vector<int>();
   c->device = device;
   c->N_max = max_frames;
   c->E_max = max_edges;
@@ -168,6 +205,7 @@ extern "C" int gba_create(gba_ctx **out, int device, int max_frames, int max_edg
 static int build_index(gba_ctx *c, const int64_t *kx_global, int n_kx, bool want_tiles) {
   BaParams &p = c->p;
   cudaStream_t s = c->stream;
+  stage_begin(c, GBA_STAGE_INDEX);
   k_prep_frames<<<1, 1024, 0, s>>>(p, kx_global, n_kx);
   LAUNCH_CHECK("k_prep_frames");
   if (p.E > 0) {
@@ -187,6 +225,7 @@ static int build_index(gba_ctx *c, const int64_t *kx_global, int n_kx, bool want
     k_tile_fill<<<1, 1024, 0, s>>>(p, c->tmask, c->colrows, c->colcnt);
     LAUNCH_CHECK("k_tile_fill");
   }
+  stage_end(c);
   CK(cudaMemcpyAsync(c->st_h, c->st_d, sizeof(Status), cudaMemcpyDeviceToHost, s));
   CK(cudaStreamSynchronize(s));
   const Status &st = *c->st_h;
@@ -264,21 +303,26 @@ extern "C" int gba_ba_build(gba_ctx *c) {
   cudaStream_t s = c->stream;
   const Status &st = *c->st_h;
   CK(cudaSetDevice(c->device));
-  CK(cudaMemsetAsync(c->sys, 0, c->sys_count * sizeof(double), s));
-  if (p.ld > 6 * p.P) {
-    k_pad_diag<<<1, GBA_NB, 0, s>>>(p);
-    LAUNCH_CHECK("k_pad_diag");
-  }
   if (p.E > 0) {
+    stage_begin(c, GBA_STAGE_POSE);
     k_edge_geo<<<(p.E + 255) / 256, 256, 0, s>>>(p);
     LAUNCH_CHECK("k_edge_geo");
+    stage_end(c);
   }
+  stage_begin(c, GBA_STAGE_LINEARIZE);  // brackets k_linearize alone (roofline kernel)
   if (st.K > 0) {
     dim3 grid(p.nchunk, st.K);
     if (c->variant == 0) k_linearize<256, 2><<<grid, 256, 0, s>>>(p);
     else if (c->variant == 1) k_linearize<128, 2><<<grid, 128, 0, s>>>(p);
     else k_linearize<128, 1><<<grid, 128, 0, s>>>(p);
     LAUNCH_CHECK("k_linearize");
+  }
+  stage_end(c);
+  stage_begin(c, GBA_STAGE_POSE);
+  CK(cudaMemsetAsync(c->sys, 0, c->sys_count * sizeof(double), s));
+  if (p.ld > 6 * p.P) {
+    k_pad_diag<<<1, GBA_NB, 0, s>>>(p);
+    LAUNCH_CHECK("k_pad_diag");
   }
   if (p.E > 0) {
     k_edge_finish<<<(p.E + 127) / 128, 128, 0, s>>>(p);
@@ -288,13 +332,18 @@ extern "C" int gba_ba_build(gba_ctx *c) {
     k_damp<<<(6 * p.P + 255) / 256, 256, 0, s>>>(p, p.lm, p.ep);
     LAUNCH_CHECK("k_damp");
   }
+  stage_end(c);
   if (!p.motion_only && p.E > 0 && st.K > 0) {
+    stage_begin(c, GBA_STAGE_GRAM);
     if (c->gsplit > 1) CK(cudaMemsetAsync(c->gram, 0, (size_t)st.gram_floats * sizeof(float), s));
     const int nb = (6 * st.max_deg + 1 + 7) / 8, RS = ((2 * nb + 7) & ~7) * 4;
     k_gram<<<dim3(c->gsplit, st.K), GRAM_NT, (size_t)GRAM_T * RS * sizeof(float), s>>>(p);
     LAUNCH_CHECK("k_gram");
+    stage_end(c);
+    stage_begin(c, GBA_STAGE_SCHUR);
     k_schur<<<st.K, SCHUR_NT, (size_t)6 * (6 * st.max_deg + 1) * sizeof(float), s>>>(p);
     LAUNCH_CHECK("k_schur");
+    stage_end(c);
   }
   return GBA_OK;
 }
@@ -312,6 +361,7 @@ extern "C" int gba_ba_solve(gba_ctx *c) {
   cudaStream_t s = c->stream;
   const Status &st = *c->st_h;
   CK(cudaSetDevice(c->device));
+  stage_begin(c, GBA_STAGE_FACTOR);
   if (p.mode == GBA_MODE_DROID_CUDA) {  // damping after the Schur complement (droid_kernels.cu:1197,1407)
     k_damp<<<(6 * p.P + 255) / 256, 256, 0, s>>>(p, p.lm, p.ep);
     LAUNCH_CHECK("k_damp");
@@ -326,18 +376,25 @@ extern "C" int gba_ba_solve(gba_ctx *c) {
       LAUNCH_CHECK("k_syrk");
     }
   }
+  stage_end(c);
+  stage_begin(c, GBA_STAGE_SOLVE);
   k_tri_solve<<<1, 256, (size_t)p.ld * sizeof(double), s>>>(p, c->invL, c->colrows, c->colcnt, c->fail);
   LAUNCH_CHECK("k_tri_solve");
+  stage_end(c);
   if (!p.motion_only && st.K > 0) {
+    stage_begin(c, GBA_STAGE_BACKSUB);
     dim3 grid(p.nchunk, st.K);
     if (c->variant == 0) k_backsub<256, 2><<<grid, 256, 0, s>>>(p);
     else if (c->variant == 1) k_backsub<128, 2><<<grid, 128, 0, s>>>(p);
     else k_backsub<128, 1><<<grid, 128, 0, s>>>(p);
     LAUNCH_CHECK("k_backsub");
+    stage_end(c);
   }
   if (p.motion_only || !p.depth_only) {
+    stage_begin(c, GBA_STAGE_RETR);
     k_pose_retr<<<(p.P + 127) / 128, 128, 0, s>>>(p);
     LAUNCH_CHECK("k_pose_retr");
+    stage_end(c);
   }
   return GBA_OK;
 }
@@ -405,6 +462,7 @@ extern "C" int gba_dspo(gba_ctx *c, const float *poses, float *disps, const floa
   d.kx = c->kx; d.eptr = c->eptr; d.eidx = c->eidx; d.st = c->st_d; d.geo = c->geo; d.Q = c->Q; d.W = c->W;
   d.part = c->dspo_part; d.dwq = c->dwq; d.bad = c->dspo_bad;
   d.nchunk = (c->HW + 511) / 512;
+  stage_begin(c, GBA_STAGE_DSPO);
   CK(cudaMemsetAsync(c->dspo_bad, 0, sizeof(int), s));
   k_edge_geo<<<(p.E + 255) / 256, 256, 0, s>>>(p);
   LAUNCH_CHECK("k_edge_geo");
@@ -416,6 +474,37 @@ extern "C" int gba_dspo(gba_ctx *c, const float *poses, float *disps, const floa
   LAUNCH_CHECK("k_dspo_solve");
   k_dspo_update<128><<<grid, 128, 0, s>>>(d);
   LAUNCH_CHECK("k_dspo_update");
+  stage_end(c);
+  return GBA_OK;
+}
+
+// ---- stage timing -------------------------------------------------------------------------------
+extern "C" int gba_set_timing(gba_ctx *c, int enable) {
+  if (!c) return GBA_EINVAL;
+  c->timing = enable ? 1 : 0;
+  c->ev_used = 0;
+  c->ev_stage->clear();
+  c->ev_launch->clear();
+  return GBA_OK;
+}
+
+extern "C" int gba_get_timing(gba_ctx *c, float *ms, int *launches) {
+  if (!c || !ms) return GBA_EINVAL;
+  CK(cudaSetDevice(c->device));
+  CK(cudaStreamSynchronize(c->stream));
+  for (int i = 0; i < GBA_N_STAGES; i++) {
+    ms[i] = 0.f;
+    if (launches) launches[i] = 0;
+  }
+  for (size_t i = 0; i < c->ev_stage->size(); i++) {
+    float t = 0.f;
+    CK(cudaEventElapsedTime(&t, (*c->ev_pool)[2 * i], (*c->ev_pool)[2 * i + 1]));
+    ms[(*c->ev_stage)[i]] += t;
+    if (launches) launches[(*c->ev_stage)[i]] += (*c->ev_launch)[i];
+  }
+  c->ev_used = 0;
+  c->ev_stage->clear();
+  c->ev_launch->clear();
   return GBA_OK;
 }
 

@@ -127,6 +127,25 @@ int gba_query(gba_ctx *ctx, gba_info *info);
 #define GBA_GET_TILEMASK 8 /* uint8 [nT,nT] lower-triangular tile structure after fill        */
 int gba_get(gba_ctx *ctx, int what, void *dst, size_t bytes);
 
+/* ---- optional per-stage device timing ---------------------------------------------------
+ * When enabled, the library brackets every stage of gba_ba / gba_dspo with CUDA events on the
+ * call's own stream (the stream the kernels are launched on).  gba_get_timing synchronises the
+ * stream, returns the accumulated milliseconds and kernel-launch counts per stage since the last
+ * read and clears them.  The reference has no timers around BA. */
+#define GBA_STAGE_INDEX 0     /* index build + tile structure (once per call)         */
+#define GBA_STAGE_LINEARIZE 1 /* edge geometry + k_linearize (per-edge HBM pass)      */
+#define GBA_STAGE_POSE 2      /* per-edge pose blocks into the reduced system         */
+#define GBA_STAGE_GRAM 3      /* Schur Gram accumulation                              */
+#define GBA_STAGE_SCHUR 4     /* Schur assembly (+ damping)                           */
+#define GBA_STAGE_FACTOR 5    /* tile Cholesky                                        */
+#define GBA_STAGE_SOLVE 6     /* triangular solves                                    */
+#define GBA_STAGE_BACKSUB 7   /* back-substitution + disparity retraction             */
+#define GBA_STAGE_RETR 8      /* pose retraction                                      */
+#define GBA_STAGE_DSPO 9      /* DSPO stage-2 kernels                                 */
+#define GBA_N_STAGES 10
+int gba_set_timing(gba_ctx *ctx, int enable);
+int gba_get_timing(gba_ctx *ctx, float *ms /* [GBA_N_STAGES] */, int *launches /* [GBA_N_STAGES] */);
+
 #ifdef __cplusplus
 }
 #endif
