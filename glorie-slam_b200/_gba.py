@@ -50,6 +50,8 @@ def lib():
         L.gba_ba_end.argtypes = [vp, vp, vp]
         L.gba_query.argtypes = [vp, ctypes.POINTER(Info)]
         L.gba_get.argtypes = [vp, ci, vp, ctypes.c_size_t]
+        L.gba_edge_blocks_static.argtypes = [vp] * 7 + [ci] * 5 + [vp, vp]
+        L.gba_edge_blocks_static.restype = ci
         L.gba_set_timing.argtypes = [vp, ci]
         L.gba_get_timing.argtypes = [vp, ctypes.POINTER(cf), ctypes.POINTER(ci)]
         L.gba_set_timing.restype = ci

@@ -15,7 +15,7 @@
 #include "gba_kernels.cuh"
 #include "gba_solver.cuh"
 
-static thread_local char g_create_err[512] = "";
+thread_local char g_create_err[512] = "";  // also written by gba_noalloc.cu
 
 struct gba_ctx {
   int device, N_max, E_max, ht, wd, HW, sm_count;

@@ -146,6 +146,34 @@ int gba_get(gba_ctx *ctx, int what, void *dst, size_t bytes);
 int gba_set_timing(gba_ctx *ctx, int enable);
 int gba_get_timing(gba_ctx *ctx, float *ms /* [GBA_N_STAGES] */, int *launches /* [GBA_N_STAGES] */);
 
+/* ---- per-edge pose blocks for callers that cannot allocate --------------------------------
+ * No counterpart in the reference: there, these numbers only exist inside ba_cuda.
+ *
+ * Computes, for every edge i -> j, H_jj = sum_pix w J_j^T J_j (21 upper-triangular entries, row
+ * major) followed by v_j = sum_pix w J_j^T r (6 entries) into out[e*32 .. e*32+26] (entries
+ * 27..31 are written as 0) -- the layout of gba_get(GBA_GET_EDGE_HV).  Arguments are device
+ * pointers shaped as in gba_ba: poses [n_frames,7], disps [n_frames,ht,wd], intrinsics [4],
+ * targets / weights [n_edges,2,ht,wd], ii / jj [n_edges] int64; out [n_edges,32] fp32.
+ *
+ * Unlike every other entry point it needs no gba_ctx and performs no allocation of any kind
+ * (no cudaMalloc / cudaFree, no allocating library call): it is meant for callers that must not
+ * or cannot allocate when they need these blocks -- a latency-critical tracking thread that may
+ * not block on the driver's allocator lock, or a process that has already given all device memory
+ * to another allocator.  Its scratch memory is a fixed array inside libgba.so (about 2.6 MB on
+ * every GPU that loads the library), which sets the limits below; larger problems are refused
+ * with GBA_ECAPACITY (text via gba_last_error(NULL)) -- split the edge list or use gba_ba.
+ *   - Works on the CURRENT device.  The first call on each device also looks up the device
+ *     address of the built-in array; make that first call outside any stream capture.
+ *   - All calls share the one array: calls whose kernels may overlap on the GPU (different
+ *     streams, different threads) race with each other.  Serialise them on one stream.
+ *   - ii / jj must lie in [0, n_frames); an edge that does not gets an all-zero block.
+ *   - Asynchronous on `stream`, like gba_ba. */
+#define GBA_STATIC_MAX_EDGES 4096
+#define GBA_STATIC_MAX_PIXELS 4800 /* ht*wd, e.g. 60 x 80 */
+int gba_edge_blocks_static(const float *poses, const float *disps, const float *intrinsics, const float *targets,
+                           const float *weights, const int64_t *ii, const int64_t *jj, int n_frames, int n_edges,
+                           int ht, int wd, int mode, float *out, void *stream);
+
 #ifdef __cplusplus
 }
 #endif
