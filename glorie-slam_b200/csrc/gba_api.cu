@@ -27,10 +27,11 @@ struct gba_ctx {
   EdgeGeo *geo;
   float *hpart, *edge_hv, *Q, *W, *gram, *dx, *dzbuf, *dspo_part, *dwq;
   size_t gram_cap, sys_cap;
-  double *sys, *invL;
-  int *tslot, *colrows, *colcnt, *fail, *dspo_bad;
-  unsigned char *tmask;
-  int nT_max, hpart_chunks;
+  double *sys;
+  int *tslot, *perm, *dspo_bad;
+  SolverBufs sb;
+  unsigned int *flags;  // flagA | cntB | cntD | flagX | ticket, nT_max each
+  int nT_max, hpart_chunks, panel_capacity;
   // state of the current call
   BaParams p;
   cudaStream_t stream;
@@ -93,9 +94,8 @@ static cudaError_t dalloc(T **p, size_t n) {
   return cudaMalloc((void **)p, std::max<size_t>(n, 1) * sizeof(T));
 }
 
-static const int kSolverSmem = 2 * GBA_NB * (GBA_NB + 1) * (int)sizeof(double);
+static const int kSolverSmem = 3 * GBA_NB * (GBA_NB + 1) * (int)sizeof(double);
 static const int kGramSmemMax = 200 * 1024;
-static const int kTriSmemMax = 200 * 1024;
 
 extern "C" const char *gba_last_error(const gba_ctx *c) { return c ? c->err : g_create_err; }
 
@@ -103,8 +103,9 @@ extern "C" void gba_destroy(gba_ctx *c) {
   if (!c) return;
   cudaSetDevice(c->device);
   void *ptrs[] = {c->kx, c->fmap, c->deg, c->eptr, c->eidx, c->ek, c->goff, c->st_d, c->geo, c->hpart, c->edge_hv,
-                  c->Q, c->W, c->gram, c->dx, c->dzbuf, c->dspo_part, c->dwq, c->sys, c->invL, c->tslot, c->colrows, c->colcnt,
-                  c->fail, c->dspo_bad, c->tmask};
+                  c->Q, c->W, c->gram, c->dx, c->dzbuf, c->dspo_part, c->dwq, c->sys, c->tslot, c->perm, c->dspo_bad,
+                  c->sb.tbits, c->sb.colrows, c->sb.colcnt, c->sb.rowcols, c->sb.rowcnt, c->sb.invL, c->sb.fail,
+                  c->flags};
   for (void *q : ptrs)
     if (q) cudaFree(q);
   if (c->st_h) cudaFreeHost(c->st_h);
@@ -143,10 +144,9 @@ extern "C" int gba_create(gba_ctx **out, int device, int max_frames, int max_edg
   const size_t N = max_frames, E = std::max(max_edges, 1), HW = c->HW;
   c->nT_max = (6 * max_frames + GBA_NB - 1) / GBA_NB;
   const size_t nT = c->nT_max, ld = nT * GBA_NB;
-  if (ld * sizeof(double) > (size_t)kTriSmemMax) {
+  if (nT > TS_MAXT) {
     free(ctx);
-    return fail_msg(nullptr, GBA_ECAPACITY, "max_frames %d too large for the single-CTA solve (limit %d)", max_frames,
-                    kTriSmemMax / 8 / 6);
+    return fail_msg(nullptr, GBA_ECAPACITY, "max_frames %d too large (limit %d)", max_frames, TS_MAXT * GBA_NB / 6);
   }
 #define CKC(call)                                                                                  \
   do {                                                                                             \
@@ -182,20 +182,35 @@ extern "C" int gba_create(gba_ctx **out, int device, int max_frames, int max_edg
   CKC(dalloc(&c->dspo_part, N * c->hpart_chunks * 8));
   CKC(dalloc(&c->dwq, 2 * N));
   CKC(dalloc(&c->sys, c->sys_cap));
-  CKC(dalloc(&c->invL, nT * GBA_NB2));
+  CKC(dalloc(&c->sb.invL, nT * GBA_NB2));
   CKC(dalloc(&c->tslot, nT * nT));
-  CKC(dalloc(&c->colrows, nT * nT));
-  CKC(dalloc(&c->colcnt, nT));
-  CKC(dalloc(&c->fail, 1));
+  CKC(dalloc(&c->perm, N));
+  CKC(dalloc(&c->sb.colrows, nT * nT));
+  CKC(dalloc(&c->sb.colcnt, nT));
+  CKC(dalloc(&c->sb.rowcols, nT * nT));
+  CKC(dalloc(&c->sb.rowcnt, nT));
+  CKC(dalloc(&c->sb.fail, 1));
   CKC(dalloc(&c->dspo_bad, 1));
-  CKC(dalloc(&c->tmask, nT * nT));
-  CKC(cudaMemset(c->fail, 0, sizeof(int)));
+  CKC(dalloc(&c->sb.tbits, nT * TS_WORDS));
+  CKC(dalloc(&c->flags, 5 * nT));
+  c->sb.ticket = c->flags + 4 * nT;
+  c->sb.flagA = c->flags;
+  c->sb.cntB = c->flags + nT;
+  c->sb.cntD = c->flags + 2 * nT;
+  c->sb.flagX = c->flags + 3 * nT;
+  CKC(cudaMemset(c->sb.fail, 0, sizeof(int)));
   CKC(cudaMemset(c->st_d, 0, sizeof(Status)));
   CKC(cudaFuncSetAttribute(k_gram, cudaFuncAttributeMaxDynamicSharedMemorySize, kGramSmemMax));
   CKC(cudaFuncSetAttribute(k_potrf_diag, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolverSmem));
   CKC(cudaFuncSetAttribute(k_trsm, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolverSmem));
   CKC(cudaFuncSetAttribute(k_syrk, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolverSmem));
-  CKC(cudaFuncSetAttribute(k_tri_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, kTriSmemMax));
+  CKC(cudaFuncSetAttribute(k_panel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolverSmem));
+  CKC(cudaFuncSetAttribute(k_panel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolverSmem));
+  {
+    int per_sm = 0;
+    CKC(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_panel<16>, 256, kSolverSmem));
+    c->panel_capacity = per_sm * c->sm_count;  // the fused tile-column kernel needs a co-resident grid
+  }
 #undef CKC
   *out = ctx;
   return GBA_OK;
@@ -219,10 +234,12 @@ static int build_index(gba_ctx *c, const int64_t *kx_global, int n_kx, bool want
     LAUNCH_CHECK("k_prep_fill");
   }
   if (want_tiles) {
-    CK(cudaMemsetAsync(c->tmask, 0, (size_t)p.nT * p.nT, s));
-    k_tile_mark<<<p.N, 128, 0, s>>>(p, c->tmask);
+    k_order<<<1, 1024, (size_t)((p.P + 3) / 4) * 4, s>>>(p);
+    LAUNCH_CHECK("k_order");
+    CK(cudaMemsetAsync(c->sb.tbits, 0, (size_t)p.nT * TS_WORDS * sizeof(unsigned int), s));
+    k_tile_mark<<<p.N, 128, 0, s>>>(p, c->sb.tbits);
     LAUNCH_CHECK("k_tile_mark");
-    k_tile_fill<<<1, 1024, 0, s>>>(p, c->tmask, c->colrows, c->colcnt);
+    k_tile_fill<<<1, 512, 0, s>>>(p, c->sb);
     LAUNCH_CHECK("k_tile_fill");
   }
   stage_end(c);
@@ -262,6 +279,7 @@ extern "C" int gba_ba_begin(gba_ctx *c, float *poses, float *disps, const float 
   p.kx = c->kx; p.fmap = c->fmap; p.deg = c->deg; p.eptr = c->eptr; p.eidx = c->eidx; p.ek = c->ek;
   p.owned = owned; p.goff = c->goff; p.st = c->st_d; p.geo = c->geo; p.hpart = c->hpart; p.edge_hv = c->edge_hv;
   p.Q = c->Q; p.W = c->W; p.gram = c->gram; p.dx = c->dx; p.dz_out = c->dzbuf; p.sys = c->sys; p.tslot = c->tslot;
+  p.perm = c->perm;
   p.nT = (6 * p.P + GBA_NB - 1) / GBA_NB;
   p.ld = p.nT * GBA_NB;
   c->last_P = p.P;
@@ -366,20 +384,42 @@ extern "C" int gba_ba_solve(gba_ctx *c) {
     k_damp<<<(6 * p.P + 255) / 256, 256, 0, s>>>(p, p.lm, p.ep);
     LAUNCH_CHECK("k_damp");
   }
-  for (int kk = 0; kk < p.nT; kk++) {
-    k_potrf_diag<<<1, 256, kSolverSmem, s>>>(p, kk, c->invL, c->fail);
-    LAUNCH_CHECK("k_potrf_diag");
-    if (st.max_col > 0 && kk + 1 < p.nT) {
-      k_trsm<<<st.max_col, 256, kSolverSmem, s>>>(p, kk, c->invL, c->colrows, c->colcnt, c->fail);
-      LAUNCH_CHECK("k_trsm");
-      k_syrk<<<st.max_col * (st.max_col + 1) / 2, 256, kSolverSmem, s>>>(p, kk, c->colrows, c->colcnt, c->fail);
-      LAUNCH_CHECK("k_syrk");
+  CK(cudaMemsetAsync(c->flags, 0, (size_t)5 * c->nT_max * sizeof(unsigned int), s));
+  {
+    // fused tile-column kernel; 16-row slabs (4 CTAs per tile) spread the fp64 work over more
+    // SMs while the structure is sparse, whole tiles when a column already has plenty of tiles
+    const int mc = st.max_col, pairs = mc * (mc + 1) / 2;
+    const bool split = (1 + mc + pairs) <= 4 * c->sm_count;
+    for (int kk = 0; kk < p.nT; kk++) {
+      const bool last = kk + 1 >= p.nT;
+      if (getenv("GBA_UNFUSED")) {  // diagnostic: the three phases as separate launches
+        k_potrf_diag<<<1, 256, kSolverSmem, s>>>(p, c->sb, kk);
+        LAUNCH_CHECK("k_potrf_diag");
+        if (mc > 0 && !last) {
+          k_trsm<<<mc, 256, kSolverSmem, s>>>(p, c->sb, kk);
+          LAUNCH_CHECK("k_trsm");
+          k_syrk<<<pairs, 256, kSolverSmem, s>>>(p, c->sb, kk);
+          LAUNCH_CHECK("k_syrk");
+        }
+      } else if (split) {
+        k_panel<16><<<last ? 1 : 1 + 4 * mc + 4 * pairs, 256, kSolverSmem, s>>>(p, c->sb, kk, mc);
+        LAUNCH_CHECK("k_panel");
+      } else {
+        k_panel<64><<<last ? 1 : 1 + mc + pairs, 256, kSolverSmem, s>>>(p, c->sb, kk, mc);
+        LAUNCH_CHECK("k_panel");
+      }
     }
   }
   stage_end(c);
   stage_begin(c, GBA_STAGE_SOLVE);
-  k_tri_solve<<<1, 256, (size_t)p.ld * sizeof(double), s>>>(p, c->invL, c->colrows, c->colcnt, c->fail);
-  LAUNCH_CHECK("k_tri_solve");
+  for (int i = p.nT - 1; i >= 0; i--) {
+    k_back_step<<<1 + (i > 0 ? st.max_row : 0), 256, 0, s>>>(p, c->sb, i);
+    LAUNCH_CHECK("k_back_step");
+  }
+  k_dx_out<<<(6 * p.P + 255) / 256, 256, 0, s>>>(p, c->sb);
+  LAUNCH_CHECK("k_dx_out");
+  k_fail_account<<<1, 1, 0, s>>>(p, c->sb);
+  LAUNCH_CHECK("k_fail_account");
   stage_end(c);
   if (!p.motion_only && st.K > 0) {
     stage_begin(c, GBA_STAGE_BACKSUB);
@@ -541,23 +581,37 @@ extern "C" int gba_get(gba_ctx *c, int what, void *dst, size_t bytes) {
     case GBA_GET_EDGE_HV: src = c->edge_hv; need = (size_t)p.E * 32 * 4; break;
     case GBA_GET_Q: src = c->Q; need = (size_t)st.K * p.HW * 4; break;
     case GBA_GET_W: src = c->W; need = (size_t)st.K * p.HW * 4; break;
-    case GBA_GET_TILEMASK: src = c->tmask; need = (size_t)p.nT * p.nT; break;
+    case GBA_GET_TILEMASK: {
+      need = (size_t)p.nT * p.nT;
+      if (bytes < need) return fail_msg(c, GBA_EINVAL, "gba_get: buffer too small (%zu < %zu)", bytes, need);
+      std::vector<unsigned int> bits((size_t)p.nT * TS_WORDS);
+      CK(cudaMemcpy(bits.data(), c->sb.tbits, bits.size() * sizeof(unsigned int), cudaMemcpyDeviceToHost));
+      unsigned char *out = (unsigned char *)dst;
+      for (int i = 0; i < p.nT; i++)
+        for (int j = 0; j < p.nT; j++) out[(size_t)i * p.nT + j] = (bits[(size_t)i * TS_WORDS + (j >> 5)] >> (j & 31)) & 1;
+      return GBA_OK;
+    }
     case GBA_GET_SYSTEM: {
       const size_t n = 6 * (size_t)p.P;
       need = (n * n + n) * sizeof(double);
       if (bytes < need) return fail_msg(c, GBA_EINVAL, "gba_get: buffer too small (%zu < %zu)", bytes, need);
       std::vector<double> h(c->sys_count);
-      std::vector<int> slot((size_t)p.nT * p.nT);
+      std::vector<int> slot((size_t)p.nT * p.nT), perm(p.P);
       CK(cudaMemcpy(h.data(), c->sys, c->sys_count * sizeof(double), cudaMemcpyDeviceToHost));
       CK(cudaMemcpy(slot.data(), c->tslot, slot.size() * sizeof(int), cudaMemcpyDeviceToHost));
+      CK(cudaMemcpy(perm.data(), c->perm, perm.size() * sizeof(int), cudaMemcpyDeviceToHost));
       double *out = (double *)dst;
       memset(out, 0, need);
+      // undo the arrowhead ordering: element (r, q) of the caller's ordering lives at the permuted
+      // position, on whichever side of the diagonal is stored
       for (size_t r = 0; r < n; r++)
         for (size_t q = 0; q <= r; q++) {
-          const int sl = slot[(r / GBA_NB) * p.nT + q / GBA_NB];
-          if (sl >= 0) out[r * n + q] = h[(size_t)sl * GBA_NB2 + (r % GBA_NB) * GBA_NB + q % GBA_NB];
+          size_t pr = 6 * (size_t)perm[r / 6] + r % 6, pq = 6 * (size_t)perm[q / 6] + q % 6;
+          if (pr < pq) std::swap(pr, pq);
+          const int sl = slot[(pr / GBA_NB) * p.nT + pq / GBA_NB];
+          if (sl >= 0) out[r * n + q] = h[(size_t)sl * GBA_NB2 + (pr % GBA_NB) * GBA_NB + pq % GBA_NB];
         }
-      for (size_t r = 0; r < n; r++) out[n * n + r] = h[(size_t)st.n_slots * GBA_NB2 + r];
+      for (size_t r = 0; r < n; r++) out[n * n + r] = h[(size_t)st.n_slots * GBA_NB2 + 6 * (size_t)perm[r / 6] + r % 6];
       return GBA_OK;
     }
     default: return fail_msg(c, GBA_EINVAL, "gba_get: unknown selector %d", what);

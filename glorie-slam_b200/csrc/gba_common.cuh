@@ -31,7 +31,9 @@ struct Status {          // device -> host after the index build
   int n_slots;           // active lower tiles after fill
   int max_col;           // max active sub-diagonal tiles in a tile column
   int chol_fail;         // running count of failed factorisations
-  int pad;
+  int max_row;           // max active tiles left of the diagonal in a tile row
+  int n_closure;         // poses moved to the end by the arrowhead ordering
+  int band_w;            // chosen long-range threshold (-1: none)
   unsigned long long gram_floats;  // total size of the per-frame Gram buffers
 };
 
@@ -59,6 +61,7 @@ struct BaParams {
   // reduced system (tile packed, fp64)
   double *sys;    // [n_slots][NB*NB] then rhs [ld]
   int *tslot;     // [nT][nT]
+  int *perm;      // [P] pose -> position in the reduced system (arrowhead ordering)
   int nT, ld;
 };
 

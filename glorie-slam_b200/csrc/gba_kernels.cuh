@@ -417,8 +417,9 @@ __global__ void k_edge_finish(BaParams p) {
     p.edge_hv[(size_t)n * 32 + l] = s;
   }
   const EdgeGeo g = p.geo[n];
-  const int pi = g.pi, pj = g.pj;
-  if (pi < 0 && pj < 0) return;
+  if (g.pi < 0 && g.pj < 0) return;
+  // positions in the (permuted) reduced system
+  const int pi = g.pi >= 0 ? p.perm[g.pi] : -1, pj = g.pj >= 0 ? p.perm[g.pj] : -1;
   double H[6][6];
   {
     int l = 0;
@@ -430,11 +431,12 @@ __global__ void k_edge_finish(BaParams p) {
       }
   }
   const double *v = hv + 21;
+  double *rhs = p.sys + (size_t)p.st->n_slots * GBA_NB2;
   // jj,jj block and v_j
   if (pj >= 0) {
     for (int r = 0; r < 6; r++) {
       for (int c = 0; c <= r; c++) atomicAdd(sys_at(p, 6 * pj + r, 6 * pj + c), H[r][c]);
-      atomicAdd(p.sys + (size_t)p.st->n_slots * GBA_NB2 + 6 * pj + r, v[r]);
+      atomicAdd(rhs + 6 * pj + r, v[r]);
     }
   }
   if (pi < 0) return;
@@ -456,7 +458,7 @@ __global__ void k_edge_finish(BaParams p) {
   {
     double y[6];
     apply_B<double>(g.R, g.t, v, y);
-    for (int r = 0; r < 6; r++) atomicAdd(p.sys + (size_t)p.st->n_slots * GBA_NB2 + 6 * pi + r, y[r]);
+    for (int r = 0; r < 6; r++) atomicAdd(rhs + 6 * pi + r, y[r]);
   }
   if (pj >= 0 && pi != pj) {
     // off-diagonal: block (pi,pj) = B H, block (pj,pi) = (B H)^T; store the lower one
@@ -620,12 +622,16 @@ __global__ void __launch_bounds__(SCHUR_NT) k_schur(BaParams p) {
   const float *G = p.gram + p.goff[k];
   double *rhs = p.sys + (size_t)p.st->n_slots * GBA_NB2;
   const int pcr = p.kx[k] - p.t0;
-  const int pc = (pcr >= 0 && pcr < p.P) ? pcr : -1;
+  const int pc = (pcr >= 0 && pcr < p.P) ? p.perm[pcr] : -1;
+  auto pos_of = [&](int q) {  // position of edge q's destination pose in the permuted system
+    const int pj = p.geo[p.eidx[e0 + q]].pj;
+    return pj >= 0 ? p.perm[pj] : -1;
+  };
 
   // (a) edge-row x edge-row blocks, lower triangle only
   for (int idx = tid; idx < deg * deg; idx += SCHUR_NT) {
     const int n = idx / deg, m = idx - n * deg;
-    const int a = p.geo[p.eidx[e0 + n]].pj, b = p.geo[p.eidx[e0 + m]].pj;
+    const int a = pos_of(n), b = pos_of(m);
     if (a < 0 || b < 0 || a < b) continue;
     for (int r = 0; r < 6; r++)
       for (int c = 0; c < 6; c++) {
@@ -637,7 +643,7 @@ __global__ void __launch_bounds__(SCHUR_NT) k_schur(BaParams p) {
   // (b) rhs: v -= E Q w  (Ev6x1 + update_rhs, droid_kernels.cu:1298-1308)
   for (int idx = tid; idx < Rw; idx += SCHUR_NT) {
     const int n = idx / 6, r = idx - 6 * n;
-    const int a = p.geo[p.eidx[e0 + n]].pj;
+    const int a = pos_of(n);
     if (a >= 0) atomicAdd(rhs + 6 * a + r, -(double)G[(size_t)idx * Rp + Rw]);
   }
   if (pc < 0) return;
@@ -657,7 +663,7 @@ __global__ void __launch_bounds__(SCHUR_NT) k_schur(BaParams p) {
   // cross blocks S[k, jj[m]] = U_m, stored on the lower side
   for (int idx = tid; idx < Rw; idx += SCHUR_NT) {
     const int m = idx / 6, c = idx - 6 * m;
-    const int b = p.geo[p.eidx[e0 + m]].pj;
+    const int b = pos_of(m);
     if (b < 0 || b == pc) continue;
     for (int r = 0; r < 6; r++) {
       const double val = -(double)s_U[r * (Rw + 1) + idx];

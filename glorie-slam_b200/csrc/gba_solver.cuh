@@ -1,26 +1,131 @@
-// gba_solver.cuh -- reduced camera system: tile structure, fp64 tile Cholesky, solve.
+// gba_solver.cuh -- reduced camera system: ordering, tile structure, fp64 tile Cholesky, solve.
 //
 // The reference factorises the 6P x 6P system on the HOST: D2H copy, fp32->fp64, triplet
-// assembly and Eigen::SimplicialLLT<double> every iteration (droid_kernels.cu:1131-1213).
-// Here the matrix lives on the device as fp64 NB x NB tiles (lower triangle, only tiles that
-// are structurally non-zero after symbolic fill are stored / touched); the numeric result is
-// that of a dense Cholesky, the work is that of the block-sparse one.
+// assembly and Eigen::SimplicialLLT<double> with AMD ordering every iteration
+// (droid_kernels.cu:1131-1213).  Here everything stays on the device:
+//   * an "arrowhead" pose ordering (temporal band first, loop-closure poses last) plays the role
+//     of the fill-reducing ordering;
+//   * the matrix is stored as fp64 NB x NB tiles of the lower triangle, only the tiles that are
+//     structurally non-zero after a bit-parallel symbolic elimination exist;
+//   * one fused kernel per tile column does Cholesky of the diagonal tile, the triangular solves
+//     of the tiles below it, the trailing update and the forward substitution of the rhs, the
+//     three phases chained by in-kernel flags instead of kernel boundaries;
+//   * the backward substitution is one small launch per tile row.
+// The numbers are those of a dense fp64 Cholesky of the permuted matrix.
 #pragma once
 #include "gba_common.cuh"
 
 #define TS_MAXT 512  // max tile rows (6 * P <= 32768)
+#define TS_WORDS (TS_MAXT / 32)
+
+struct SolverBufs {
+  unsigned int *tbits;    // [nT][TS_WORDS] structure bits, row i bit j (j <= i)
+  int *colrows, *colcnt;  // active tiles below the diagonal, per tile column
+  int *rowcols, *rowcnt;  // active tiles left of the diagonal, per tile row
+  double *invL;           // [nT][NB*NB]
+  int *fail;              // factorisation hit a non-positive pivot
+  unsigned int *flagA, *cntB, *cntD, *flagX, *ticket;  // per-panel in-kernel synchronisation
+};
+
+// ---------------------------------------------------------------------------------------------
+// Pose ordering.  Edges with |i - j| > W are "long range"; their destination poses form the
+// closure set C (through the Schur complement the destination couples with every neighbour of
+// the source, so it cannot stay inside a band).  W is chosen from a few candidates by a flop
+// model of the resulting band + arrow factorisation; perm puts non-C poses first (temporal
+// order), C poses last.  One CTA.
+// ---------------------------------------------------------------------------------------------
+#define ORD_NC 8
+__global__ void __launch_bounds__(1024) k_order(BaParams p) {
+  __shared__ int s_cnt[ORD_NC];
+  __shared__ int s_best, s_warp[32], s_carry;
+  extern __shared__ unsigned int s_flagw[];  // [ceil(P/4)] one byte per pose: bit c = in C for candidate c
+  unsigned char *s_flag = reinterpret_cast<unsigned char *>(s_flagw);
+  const int tid = threadIdx.x, P = p.P;
+  const int cand[ORD_NC] = {4, 8, 16, 32, 64, 128, 256, 1 << 30};
+  for (int i = tid; i < (P + 3) / 4; i += blockDim.x) s_flagw[i] = 0;
+  if (tid < ORD_NC) s_cnt[tid] = 0;
+  __syncthreads();
+  for (int n = tid; n < p.E; n += blockDim.x) {
+    const long long i = p.ii[n], j = p.jj[n];
+    const long long pj = j - p.t0;
+    if (pj < 0 || pj >= P || i == j) continue;
+    const long long d = i > j ? i - j : j - i;
+    unsigned m = 0;
+#pragma unroll
+    for (int c = 0; c < ORD_NC; c++)
+      if (d > cand[c]) m |= 1u << c;
+    if (m) atomicOr(&s_flagw[pj >> 2], m << (8 * (pj & 3)));
+  }
+  __syncthreads();
+  for (int i = tid; i < P; i += blockDim.x) {
+    const unsigned m = s_flag[i];
+#pragma unroll
+    for (int c = 0; c < ORD_NC; c++)
+      if (m & (1u << c)) atomicAdd(&s_cnt[c], 1);
+  }
+  __syncthreads();
+  if (tid == 0) {
+    double best = 1e300;
+    int bi = ORD_NC - 1;
+    for (int c = 0; c < ORD_NC; c++) {
+      const double nC = s_cnt[c], nB = P - nC;
+      const double b = fmin(2.0 * cand[c], nB);  // band half width in poses
+      // band factor + arrow rows + arrow trailing update + dense tail (pose^3 units)
+      const double cost = nB * b * b + nC * nB * b + nB * nC * nC * 0.5 + nC * nC * nC / 3.0;
+      if (cost < best) {
+        best = cost;
+        bi = c;
+      }
+    }
+    s_best = bi;
+    s_carry = 0;
+    p.st->n_closure = s_cnt[bi];
+    p.st->band_w = cand[bi] > 1000000 ? -1 : cand[bi];
+  }
+  __syncthreads();
+  const int bc = s_best, nB = P - s_cnt[bc];
+  // positions: inclusive scan of the "not in C" flags
+  for (int base = 0; base < P; base += blockDim.x) {
+    const int i = base + tid;
+    const int inC = (i < P) ? ((s_flag[i] >> bc) & 1) : 0;
+    const int f = (i < P) ? 1 - inC : 0;
+    int v = f;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int u = __shfl_up_sync(0xffffffffu, v, o);
+      if ((tid & 31) >= o) v += u;
+    }
+    if ((tid & 31) == 31) s_warp[tid >> 5] = v;
+    __syncthreads();
+    if (tid < 32) {
+      int w = s_warp[tid];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int u = __shfl_up_sync(0xffffffffu, w, o);
+        if (tid >= o) w += u;
+      }
+      s_warp[tid] = w;
+    }
+    __syncthreads();
+    const int incl = v + ((tid >> 5) ? s_warp[(tid >> 5) - 1] : 0) + s_carry;  // non-C poses among [0, i]
+    if (i < P) p.perm[i] = inC ? nB + (i - incl) : incl - 1;
+    __syncthreads();
+    if (tid == blockDim.x - 1) s_carry = incl;
+    __syncthreads();
+  }
+}
 
 // Mark the tiles touched by the pose pairs of one depth keyframe (its own pose and the
 // destination poses of its out-edges are all mutually coupled through the Schur complement;
 // the pose-pose Hessian blocks (ii,ii),(ii,jj),(jj,jj) are a subset).
-__global__ void k_tile_mark(BaParams p, unsigned char *tmask) {
+__global__ void k_tile_mark(BaParams p, unsigned int *tbits) {
   const int k = blockIdx.x;
   if (k >= p.st->K) return;
   const int e0 = p.eptr[k], deg = p.eptr[k + 1] - e0;
   const int L = deg + 1;
   auto pose_of = [&](int q) {
     const int pr = (q < deg) ? (int)p.jj[p.eidx[e0 + q]] - p.t0 : p.kx[k] - p.t0;
-    return (pr >= 0 && pr < p.P) ? pr : -1;
+    return (pr >= 0 && pr < p.P) ? p.perm[pr] : -1;
   };
   for (int idx = threadIdx.x; idx < L * L; idx += blockDim.x) {
     const int a = pose_of(idx / L), b = pose_of(idx % L);
@@ -29,45 +134,78 @@ __global__ void k_tile_mark(BaParams p, unsigned char *tmask) {
     const int c0 = (6 * b) / GBA_NB, c1 = (6 * b + 5) / GBA_NB;
     for (int r = r0; r <= r1; r++)
       for (int c = c0; c <= c1; c++)
-        if (r >= c) tmask[r * p.nT + c] = 1;
+        if (r >= c) atomicOr(&tbits[r * TS_WORDS + (c >> 5)], 1u << (c & 31));
   }
 }
 
-// One CTA: symbolic fill of the tile structure (right-looking elimination on booleans), slot
-// numbering, per-column lists of active sub-diagonal tiles.
-__global__ void __launch_bounds__(1024) k_tile_fill(BaParams p, unsigned char *tmask, int *colrows, int *colcnt) {
-  const int nT = p.nT, tid = threadIdx.x;
-  __shared__ int s_cnt, s_max;
-  for (int i = tid; i < nT; i += blockDim.x) tmask[i * nT + i] = 1;
+// One CTA: symbolic fill on bit rows (kept in global memory, L1/L2 resident), slot numbering,
+// column / row lists.
+__global__ void __launch_bounds__(512) k_tile_fill(BaParams p, SolverBufs sb) {
+  __shared__ unsigned int s_col[TS_WORDS];
+  __shared__ int s_start[TS_MAXT + 1];
+  __shared__ int s_maxc, s_maxr;
+  unsigned int *bits = sb.tbits;
+  const int nT = p.nT, tid = threadIdx.x, nW = (nT + 31) / 32;
+  for (int i = tid; i < nT; i += blockDim.x) bits[i * TS_WORDS + (i >> 5)] |= 1u << (i & 31);
+  if (tid == 0) s_maxc = s_maxr = 0;
   __syncthreads();
+  // right-looking elimination: rows i >= j in column kk's structure create tile (i, j)
   for (int kk = 0; kk < nT; kk++) {
-    const int m = nT - kk - 1;
-    for (int idx = tid; idx < m * m; idx += blockDim.x) {
-      const int i = kk + 1 + idx / m, j = kk + 1 + idx % m;
-      if (j <= i && tmask[i * nT + kk] && tmask[j * nT + kk]) tmask[i * nT + j] = 1;
+    for (int w = tid; w < nW; w += blockDim.x) s_col[w] = 0;
+    __syncthreads();
+    for (int i = kk + 1 + tid; i < nT; i += blockDim.x)
+      if ((bits[i * TS_WORDS + (kk >> 5)] >> (kk & 31)) & 1) atomicOr(&s_col[i >> 5], 1u << (i & 31));
+    __syncthreads();
+    for (int i = kk + 1 + tid; i < nT; i += blockDim.x) {
+      if (!((s_col[i >> 5] >> (i & 31)) & 1)) continue;
+      for (int w = 0; w <= (i >> 5); w++) {
+        unsigned m = s_col[w];
+        if (w == (i >> 5)) m &= ((i & 31) == 31) ? 0xffffffffu : ((2u << (i & 31)) - 1u);
+        bits[i * TS_WORDS + w] |= m;
+      }
     }
     __syncthreads();
   }
-  // slots in row-major lower order (single thread: nT^2/2 <= 131k steps, once per call)
-  if (tid == 0) {
-    int s = 0;
-    for (int i = 0; i < nT; i++)
-      for (int j = 0; j < nT; j++) p.tslot[i * nT + j] = (j <= i && tmask[i * nT + j]) ? s++ : -1;
-    s_cnt = s;
-    s_max = 0;
+  // slots: row-major over the lower triangle
+  for (int i = tid; i < nT; i += blockDim.x) {
+    int c = 0;
+    for (int w = 0; w < nW; w++) c += __popc(bits[i * TS_WORDS + w]);
+    s_start[i + 1] = c;
   }
   __syncthreads();
+  if (tid == 0) {
+    s_start[0] = 0;
+    for (int i = 0; i < nT; i++) s_start[i + 1] += s_start[i];
+    p.st->n_slots = s_start[nT];
+  }
+  __syncthreads();
+  for (int idx = tid; idx < nT * nT; idx += blockDim.x) {
+    const int i = idx / nT, j = idx % nT;
+    int slot = -1;
+    if (j <= i && ((bits[i * TS_WORDS + (j >> 5)] >> (j & 31)) & 1)) {
+      int c = 0;
+      for (int w = 0; w < (j >> 5); w++) c += __popc(bits[i * TS_WORDS + w]);
+      c += __popc(bits[i * TS_WORDS + (j >> 5)] & ((1u << (j & 31)) - 1u));
+      slot = s_start[i] + c;
+    }
+    p.tslot[idx] = slot;
+  }
   for (int kk = tid; kk < nT; kk += blockDim.x) {
     int c = 0;
     for (int i = kk + 1; i < nT; i++)
-      if (tmask[i * nT + kk]) colrows[kk * nT + c++] = i;
-    colcnt[kk] = c;
-    atomicMax(&s_max, c);
+      if ((bits[i * TS_WORDS + (kk >> 5)] >> (kk & 31)) & 1) sb.colrows[kk * nT + c++] = i;
+    sb.colcnt[kk] = c;
+    atomicMax(&s_maxc, c);
+    int r = 0;
+    for (int j = 0; j < kk; j++)
+      if ((bits[kk * TS_WORDS + (j >> 5)] >> (j & 31)) & 1) sb.rowcols[kk * nT + r++] = j;
+    sb.rowcnt[kk] = r;
+    atomicMax(&s_maxr, r);
   }
   __syncthreads();
   if (tid == 0) {
-    p.st->n_slots = s_cnt;
-    p.st->max_col = s_max;
+    p.st->max_col = s_maxc;
+    p.st->max_row = s_maxr;
   }
 }
 
@@ -77,224 +215,364 @@ __global__ void k_pad_diag(BaParams p) {
   if (i < p.ld) *sys_at(p, i, i) = 1.0;
 }
 
-// --------------------------------------------------------------------------------------------
-// Factorisation of one tile column kk: (1) Cholesky of the diagonal tile + its inverse,
-// (2) L[i,kk] = A[i,kk] * inv(L_kk)^T for the active tiles below, (3) trailing update of the
-// active tile pairs.  All fp64 (the reference solves in fp64, droid_kernels.cu:1133,1199).
-// --------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_potrf_diag(BaParams p, int kk, double *invL, int *fail) {
-  extern __shared__ double s_buf[];
-  double(*A)[GBA_NB + 1] = reinterpret_cast<double(*)[GBA_NB + 1]>(s_buf);
-  double(*X)[GBA_NB + 1] = reinterpret_cast<double(*)[GBA_NB + 1]>(s_buf + GBA_NB * (GBA_NB + 1));
+// ---------------------------------------------------------------------------------------------
+// Tile-column roles (256 threads; dynamic shared memory: 3 tiles of 64 x 65 doubles).
+// fp64 runs at 64 FMA/clk/SM on B200, so a 64^3 tile product pins one SM for ~9 us; the
+// trsm / syrk roles therefore work on SLAB-row slabs of a tile (SPLIT = 64 / SLAB CTAs per tile)
+// to spread a tile column over more SMs, and the potrf role keeps divisions and square roots off
+// its critical path (Newton rsqrt from an fp32 seed, blocked inverse without divisions).
+// ---------------------------------------------------------------------------------------------
+typedef double (*TilePtr)[GBA_NB + 1];
+#define TILE_STRIDE (GBA_NB * (GBA_NB + 1))
+
+__device__ __forceinline__ double *rhs_ptr(const BaParams &p) { return p.sys + (size_t)p.st->n_slots * GBA_NB2; }
+
+__device__ __forceinline__ double fast_rsqrt(double d) {
+  double y = (double)rsqrtf((float)d);
+  y = y * (1.5 - 0.5 * d * y * y);
+  y = y * (1.5 - 0.5 * d * y * y);
+  return y;
+}
+
+// Cholesky of the diagonal tile, its inverse, and the forward substitution y_kk = inv(L_kk) b_kk.
+// Right-looking with ONE barrier per pivot: the update reads the unscaled column j (which no
+// later step touches) and 1/d; the scaled column goes to a separate output array.
+__device__ void role_potrf(const BaParams &p, const SolverBufs &sb, int kk, double *s_buf) {
+  TilePtr A = reinterpret_cast<TilePtr>(s_buf);
+  TilePtr Lo = reinterpret_cast<TilePtr>(s_buf + TILE_STRIDE);
+  TilePtr X = reinterpret_cast<TilePtr>(s_buf + 2 * TILE_STRIDE);
   __shared__ int s_bad;
+  __shared__ double s_v[GBA_NB], s_rd[GBA_NB];
   const int tid = threadIdx.x;
   double *T = p.sys + (size_t)p.tslot[kk * p.nT + kk] * GBA_NB2;
-  if (*fail) return;  // an earlier tile column already failed
   if (tid == 0) s_bad = 0;
   for (int i = tid; i < GBA_NB2; i += 256) {
-    const int r = i / GBA_NB, c = i % GBA_NB;
-    A[r][c] = (c <= r) ? T[i] : 0.0;
+    const int r = i >> 6, c = i & 63;
+    A[r][c] = (c <= r) ? __ldcg(T + i) : 0.0;
+    Lo[r][c] = 0.0;
     X[r][c] = 0.0;
   }
   __syncthreads();
+  // thread -> 4x4 block of the tile: rows r0..r0+3, cols c0..c0+3
+  const int r0 = (tid >> 4) * 4, c0 = (tid & 15) * 4;
   for (int j = 0; j < GBA_NB; j++) {
     const double d = A[j][j];
     if (!(d > 0.0) || isinf(d)) {  // SimplicialLLT reports NumericalIssue on a non-positive pivot
       if (tid == 0) s_bad = 1;
       break;  // uniform: every thread reads the same d
     }
-    const double inv = 1.0 / sqrt(d);
-    __syncthreads();
-    for (int i = j + tid; i < GBA_NB; i += 256) A[i][j] = (i == j) ? sqrt(d) : A[i][j] * inv;
-    __syncthreads();
-    // trailing update of the lower triangle
-    const int m = GBA_NB - j - 1;
-    for (int idx = tid; idx < m * m; idx += 256) {
-      const int r = j + 1 + idx / m, c = j + 1 + idx % m;
-      if (c <= r) A[r][c] -= A[r][j] * A[c][j];
+    const double rs = fast_rsqrt(d), dinv = rs * rs;
+    if (tid < GBA_NB && tid >= j) Lo[tid][j] = A[tid][j] * rs;
+    if (tid == 0) s_rd[j] = rs;  // 1 / L[j][j]
+    if (r0 + 3 > j && c0 + 3 > j && r0 + 3 >= c0) {
+      double ar[4], ac[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        ar[u] = A[r0 + u][j];
+        ac[u] = A[c0 + u][j] * dinv;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; u++)
+#pragma unroll
+        for (int v = 0; v < 4; v++)
+          if (r0 + u > j && c0 + v > j && c0 + v <= r0 + u) A[r0 + u][c0 + v] -= ar[u] * ac[v];
     }
     __syncthreads();
   }
   __syncthreads();
   if (s_bad) {
-    if (tid == 0) *fail = 1;
+    if (tid == 0) *sb.fail = 1;
     return;
   }
-  // X = inv(L): row i of X from the rows above, X[i][c] = -(sum_{m=c}^{i-1} L[i][m] X[m][c]) / L[i][i]
-  for (int i = 0; i < GBA_NB; i++) {
-    if (tid < i) {
+  // ---- X = inv(L), blocked by 16 -----------------------------------------------------------
+  // level 0: the four 16x16 diagonal blocks, column c of block B by 4 lanes (64 columns total)
+  {
+    const int c = tid >> 2, part = tid & 3, base = (c >> 4) * 16;
+    for (int i = base; i < base + 16; i++) {
       double s = 0.0;
-      for (int m = tid; m < i; m++) s += A[i][m] * X[m][tid];
-      X[i][tid] = -s / A[i][i];
-    } else if (tid == i)
-      X[i][i] = 1.0 / A[i][i];
-    __syncthreads();
-  }
-  double *XI = invL + (size_t)kk * GBA_NB2;
-  for (int i = tid; i < GBA_NB2; i += 256) {
-    const int r = i / GBA_NB, c = i % GBA_NB;
-    T[i] = (c <= r) ? A[r][c] : 0.0;
-    XI[i] = X[r][c];
-  }
-}
-
-// L[i,kk] = A[i,kk] * inv(L_kk)^T ; one CTA per active tile of column kk
-__global__ void __launch_bounds__(256) k_trsm(BaParams p, int kk, const double *invL, const int *colrows,
-                                              const int *colcnt, const int *fail) {
-  extern __shared__ double s_buf[];
-  double(*A)[GBA_NB + 1] = reinterpret_cast<double(*)[GBA_NB + 1]>(s_buf);
-  double(*X)[GBA_NB + 1] = reinterpret_cast<double(*)[GBA_NB + 1]>(s_buf + GBA_NB * (GBA_NB + 1));
-  if (*fail) return;
-  if ((int)blockIdx.x >= colcnt[kk]) return;
-  const int i = colrows[kk * p.nT + blockIdx.x], tid = threadIdx.x;
-  double *T = p.sys + (size_t)p.tslot[i * p.nT + kk] * GBA_NB2;
-  const double *XI = invL + (size_t)kk * GBA_NB2;
-  for (int e = tid; e < GBA_NB2; e += 256) {
-    A[e / GBA_NB][e % GBA_NB] = T[e];
-    X[e / GBA_NB][e % GBA_NB] = XI[e];
+      for (int m = c + part; m < i; m += 4) s += Lo[i][m] * X[m][c];
+      s += __shfl_xor_sync(0xffffffffu, s, 1);
+      s += __shfl_xor_sync(0xffffffffu, s, 2);
+      if (part == 0 && i >= c) X[i][c] = ((i == c ? 1.0 : 0.0) - s) * s_rd[i];
+      __syncwarp();
+    }
   }
   __syncthreads();
-  // out[r][c] = sum_m A[r][m] * X[c][m], m <= c (X lower triangular); 4x4 outputs per thread
-  const int r0 = (tid / 16) * 4, c0 = (tid % 16) * 4;
-  double acc[4][4] = {};
-  for (int m = 0; m < GBA_NB; m++) {
-    double a[4], x[4];
-#pragma unroll
-    for (int u = 0; u < 4; u++) {
-      a[u] = A[r0 + u][m];
-      x[u] = X[c0 + u][m];
+  // block rows I = 1..3: T[I][J] = sum_{K=J}^{I-1} L[I][K] X[K][J];  X[I][J] = -X[I][I] T[I][J]
+  TilePtr Tm = A;  // A is dead now
+  for (int I = 1; I < 4; I++) {
+    const int ncol = 16 * I;  // columns 0 .. 16 I - 1
+    for (int e = tid; e < 16 * ncol; e += 256) {
+      const int r = 16 * I + e / ncol, c = e % ncol;
+      double s = 0.0;
+      for (int m = (c & ~15); m < 16 * I; m++) s += Lo[r][m] * X[m][c];
+      Tm[r][c] = s;
     }
-#pragma unroll
-    for (int u = 0; u < 4; u++)
-#pragma unroll
-      for (int v = 0; v < 4; v++) acc[u][v] += a[u] * x[v];
+    __syncthreads();
+    for (int e = tid; e < 16 * ncol; e += 256) {
+      const int r = 16 * I + e / ncol, c = e % ncol;
+      double s = 0.0;
+      for (int m = 16 * I; m <= r; m++) s += X[r][m] * Tm[m][c];
+      X[r][c] = -s;
+    }
+    __syncthreads();
   }
-#pragma unroll
-  for (int u = 0; u < 4; u++)
-#pragma unroll
-    for (int v = 0; v < 4; v++) T[(r0 + u) * GBA_NB + c0 + v] = acc[u][v];
+  double *XI = sb.invL + (size_t)kk * GBA_NB2;
+  for (int i = tid; i < GBA_NB2; i += 256) {
+    const int r = i >> 6, c = i & 63;
+    T[i] = Lo[r][c];
+    XI[i] = X[r][c];
+  }
+  // forward substitution of the rhs block
+  double *b = rhs_ptr(p) + kk * GBA_NB;
+  if (tid < GBA_NB) s_v[tid] = __ldcg(b + tid);
+  __syncthreads();
+  {
+    const int row = tid >> 2, part = tid & 3;
+    double s = 0.0;
+#pragma unroll 4
+    for (int m = part * 16; m < part * 16 + 16; m++) s += X[row][m] * s_v[m];
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    if (part == 0) b[row] = s;
+  }
 }
 
-// A[i,j] -= L[i,kk] * L[j,kk]^T for active i >= j of column kk
-__global__ void __launch_bounds__(256) k_syrk(BaParams p, int kk, const int *colrows, const int *colcnt,
-                                              const int *fail) {
+// Rows [q*SLAB, (q+1)*SLAB) of L[i,kk] = A[i,kk] * inv(L_kk)^T, then b_i -= L[i,kk] y_kk there.
+template <int SLAB>
+__device__ void role_trsm(const BaParams &p, const SolverBufs &sb, int kk, int a, int q, double *s_buf) {
+  TilePtr X = reinterpret_cast<TilePtr>(s_buf);
+  TilePtr A = reinterpret_cast<TilePtr>(s_buf + TILE_STRIDE);
+  __shared__ double s_y[GBA_NB];
+  constexpr int RPT = SLAB / 16;  // rows per thread (thread = RPT x 4 outputs)
+  const int i = sb.colrows[kk * p.nT + a], tid = threadIdx.x, rb = q * SLAB;
+  double *T = p.sys + (size_t)p.tslot[i * p.nT + kk] * GBA_NB2 + rb * GBA_NB;
+  const double *XI = sb.invL + (size_t)kk * GBA_NB2;
+  for (int e = tid; e < GBA_NB2; e += 256) X[e >> 6][e & 63] = __ldcg(XI + e);
+  for (int e = tid; e < SLAB * GBA_NB; e += 256) A[e >> 6][e & 63] = __ldcg(T + e);
+  if (tid < GBA_NB) s_y[tid] = __ldcg(rhs_ptr(p) + kk * GBA_NB + tid);
+  __syncthreads();
+  const int r0 = (tid >> 4) * RPT, c0 = (tid & 15) * 4;
+  double acc[RPT][4] = {};
+  for (int m = 0; m < GBA_NB; m++) {
+    double av[RPT], xv[4];
+#pragma unroll
+    for (int u = 0; u < RPT; u++) av[u] = A[r0 + u][m];
+#pragma unroll
+    for (int v = 0; v < 4; v++) xv[v] = X[c0 + v][m];
+#pragma unroll
+    for (int u = 0; u < RPT; u++)
+#pragma unroll
+      for (int v = 0; v < 4; v++) acc[u][v] += av[u] * xv[v];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int u = 0; u < RPT; u++)
+#pragma unroll
+    for (int v = 0; v < 4; v++) {
+      T[(r0 + u) * GBA_NB + c0 + v] = acc[u][v];
+      A[r0 + u][c0 + v] = acc[u][v];
+    }
+  __syncthreads();
+  if (tid < SLAB * 4) {
+    const int row = tid >> 2, part = tid & 3;
+    double s = 0.0;
+#pragma unroll 4
+    for (int m = part * 16; m < part * 16 + 16; m++) s += A[row][m] * s_y[m];
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    if (part == 0) rhs_ptr(p)[i * GBA_NB + rb + row] -= s;
+  }
+}
+
+// Rows [q*SLAB, (q+1)*SLAB) of A[i,j] -= L[i,kk] * L[j,kk]^T
+template <int SLAB>
+__device__ void role_syrk(const BaParams &p, const SolverBufs &sb, int kk, int a, int b, int q, double *s_buf) {
+  TilePtr B = reinterpret_cast<TilePtr>(s_buf);
+  TilePtr A = reinterpret_cast<TilePtr>(s_buf + TILE_STRIDE);
+  constexpr int RPT = SLAB / 16;
+  const int i = sb.colrows[kk * p.nT + a], j = sb.colrows[kk * p.nT + b], tid = threadIdx.x, rb = q * SLAB;
+  const double *Li = p.sys + (size_t)p.tslot[i * p.nT + kk] * GBA_NB2 + rb * GBA_NB;
+  const double *Lj = p.sys + (size_t)p.tslot[j * p.nT + kk] * GBA_NB2;
+  double *T = p.sys + (size_t)p.tslot[i * p.nT + j] * GBA_NB2 + rb * GBA_NB;
+  for (int e = tid; e < GBA_NB2; e += 256) B[e >> 6][e & 63] = __ldcg(Lj + e);
+  for (int e = tid; e < SLAB * GBA_NB; e += 256) A[e >> 6][e & 63] = __ldcg(Li + e);
+  __syncthreads();
+  const int r0 = (tid >> 4) * RPT, c0 = (tid & 15) * 4;
+  double acc[RPT][4] = {};
+  for (int m = 0; m < GBA_NB; m++) {
+    double x[RPT], y[4];
+#pragma unroll
+    for (int u = 0; u < RPT; u++) x[u] = A[r0 + u][m];
+#pragma unroll
+    for (int v = 0; v < 4; v++) y[v] = B[c0 + v][m];
+#pragma unroll
+    for (int u = 0; u < RPT; u++)
+#pragma unroll
+      for (int v = 0; v < 4; v++) acc[u][v] += x[u] * y[v];
+  }
+#pragma unroll
+  for (int u = 0; u < RPT; u++)
+#pragma unroll
+    for (int v = 0; v < 4; v++) T[(r0 + u) * GBA_NB + c0 + v] -= acc[u][v];
+}
+
+__device__ __forceinline__ unsigned ld_acquire(const unsigned *p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// Fused tile column kk.  Grid = 1 + SPLIT*max_col + SPLIT*max_col(max_col+1)/2 CTAs:
+//   CTA 0             potrf of the diagonal tile (skipped when the previous column's look-ahead
+//                     already did it), then raises flagA[kk];
+//   trsm CTAs         wait for flagA[kk], solve one slab of one tile below the diagonal, count
+//                     themselves into cntB[kk];
+//   syrk CTAs         wait until cntB[kk] == SPLIT*cnt, update one slab of one trailing tile.
+//   look-ahead        the syrk CTAs of tile (kk+1, kk+1) take a ticket; the last one factorises
+//                     that tile at once (potrf of column kk+1 overlaps the rest of this update).
+// Roles are handed out by an atomic ticket taken when a CTA starts running, not by blockIdx: a
+// CTA that waits therefore only ever waits for CTAs that started before it, so the kernel cannot
+// deadlock however the grid is dispatched and however much larger than the GPU it is.
+template <int SLAB>
+__global__ void __launch_bounds__(256) k_panel(BaParams p, SolverBufs sb, int kk, int max_col) {
   extern __shared__ double s_buf[];
-  double(*A)[GBA_NB + 1] = reinterpret_cast<double(*)[GBA_NB + 1]>(s_buf);
-  double(*B)[GBA_NB + 1] = reinterpret_cast<double(*)[GBA_NB + 1]>(s_buf + GBA_NB * (GBA_NB + 1));
-  if (*fail) return;
-  const int cnt = colcnt[kk];
-  // blockIdx.x -> (a >= b)
+  constexpr int SPLIT = GBA_NB / SLAB;
+  __shared__ int s_flag, s_bid;
+  const int tid = threadIdx.x;
+  if (tid == 0) s_bid = (int)atomicAdd(&sb.ticket[kk], 1u);
+  __syncthreads();
+  const int b = s_bid;
+  const int cnt = sb.colcnt[kk];
+  if (b == 0) {
+    if (ld_acquire(&sb.flagA[kk]) == 0u) {
+      if (!__ldcg(sb.fail)) role_potrf(p, sb, kk, s_buf);
+      __threadfence();
+      __syncthreads();
+      if (tid == 0) atomicExch(&sb.flagA[kk], 1u);
+    }
+    return;
+  }
+  if (b <= SPLIT * max_col) {
+    const int a = (b - 1) / SPLIT, q = (b - 1) % SPLIT;
+    if (a >= cnt) return;
+    if (tid == 0)
+      while (ld_acquire(&sb.flagA[kk]) == 0u) __nanosleep(20);
+    __syncthreads();
+    if (!__ldcg(sb.fail)) role_trsm<SLAB>(p, sb, kk, a, q, s_buf);
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) atomicAdd(&sb.cntB[kk], 1u);
+    return;
+  }
+  const int w = b - 1 - SPLIT * max_col, pair = w / SPLIT, q = w % SPLIT;
+  int a = 0, rem = pair;
+  while (rem > a) {
+    rem -= a + 1;
+    a++;
+  }
+  if (a >= cnt) return;
+  if (tid == 0)
+    while (ld_acquire(&sb.cntB[kk]) < (unsigned)(SPLIT * cnt)) __nanosleep(20);
+  __syncthreads();
+  const bool failed = __ldcg(sb.fail);
+  if (!failed) role_syrk<SLAB>(p, sb, kk, a, rem, q, s_buf);
+  // look-ahead: tile (kk+1, kk+1) is complete once its SPLIT slabs are updated
+  if (pair == 0 && sb.colrows[kk * p.nT] == kk + 1) {
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_flag = (atomicAdd(&sb.cntD[kk], 1u) == (unsigned)(SPLIT - 1));
+    __syncthreads();
+    if (s_flag) {
+      __threadfence();
+      if (!failed) role_potrf(p, sb, kk + 1, s_buf);
+      __threadfence();
+      __syncthreads();
+      if (tid == 0) atomicExch(&sb.flagA[kk + 1], 1u);
+    }
+  }
+}
+
+// the same three phases as separate launches (large, near-dense structures)
+__global__ void __launch_bounds__(256) k_potrf_diag(BaParams p, SolverBufs sb, int kk) {
+  extern __shared__ double s_buf[];
+  if (!*sb.fail) role_potrf(p, sb, kk, s_buf);
+}
+__global__ void __launch_bounds__(256) k_trsm(BaParams p, SolverBufs sb, int kk) {
+  extern __shared__ double s_buf[];
+  if (*sb.fail || (int)blockIdx.x >= sb.colcnt[kk]) return;
+  role_trsm<GBA_NB>(p, sb, kk, blockIdx.x, 0, s_buf);
+}
+__global__ void __launch_bounds__(256) k_syrk(BaParams p, SolverBufs sb, int kk) {
+  extern __shared__ double s_buf[];
+  if (*sb.fail) return;
   int a = 0, rem = blockIdx.x;
   while (rem > a) {
     rem -= a + 1;
     a++;
   }
-  const int b = rem;
-  if (a >= cnt) return;
-  const int i = colrows[kk * p.nT + a], j = colrows[kk * p.nT + b], tid = threadIdx.x;
-  const double *Li = p.sys + (size_t)p.tslot[i * p.nT + kk] * GBA_NB2;
-  const double *Lj = p.sys + (size_t)p.tslot[j * p.nT + kk] * GBA_NB2;
-  double *T = p.sys + (size_t)p.tslot[i * p.nT + j] * GBA_NB2;
-  for (int e = tid; e < GBA_NB2; e += 256) {
-    A[e / GBA_NB][e % GBA_NB] = Li[e];
-    B[e / GBA_NB][e % GBA_NB] = Lj[e];
-  }
-  __syncthreads();
-  const int r0 = (tid / 16) * 4, c0 = (tid % 16) * 4;
-  double acc[4][4] = {};
-  for (int m = 0; m < GBA_NB; m++) {
-    double x[4], y[4];
-#pragma unroll
-    for (int u = 0; u < 4; u++) {
-      x[u] = A[r0 + u][m];
-      y[u] = B[c0 + u][m];
-    }
-#pragma unroll
-    for (int u = 0; u < 4; u++)
-#pragma unroll
-      for (int v = 0; v < 4; v++) acc[u][v] += x[u] * y[v];
-  }
-#pragma unroll
-  for (int u = 0; u < 4; u++)
-#pragma unroll
-    for (int v = 0; v < 4; v++) T[(r0 + u) * GBA_NB + c0 + v] -= acc[u][v];
+  if (a >= sb.colcnt[kk]) return;
+  role_syrk<GBA_NB>(p, sb, kk, a, rem, 0, s_buf);
 }
 
-// --------------------------------------------------------------------------------------------
-// Triangular solves L y = b, L^T x = y over the tile structure; one CTA, 256 threads
-// (thread = (row, quarter)).  dx = (float) x, or zero when the factorisation failed
-// (droid_kernels.cu:1202-1210, chol.py:13-15).
-// --------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_tri_solve(BaParams p, const double *invL, const int *colrows,
-                                                   const int *colcnt, int *fail) {
-  extern __shared__ double s_x[];  // [ld]
-  __shared__ double s_y[GBA_NB];
-  const int tid = threadIdx.x, row = tid >> 2, part = tid & 3, nT = p.nT;
-  const double *rhs = p.sys + (size_t)p.st->n_slots * GBA_NB2;
-  if (*fail) {
-    for (int i = tid; i < 6 * p.P; i += 256) p.dx[i] = 0.f;
-    if (tid == 0) {
-      p.st->chol_fail += 1;
-      *fail = 0;
-    }
+// ---------------------------------------------------------------------------------------------
+// Backward substitution, one launch per tile row i (from the last to the first): CTA 0 computes
+// x_i = inv(L_i)^T y_i, the others push y_k -= L[i,k]^T x_i to the active tiles of row i.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_back_step(BaParams p, SolverBufs sb, int i) {
+  __shared__ double s_x[GBA_NB];
+  const int b = blockIdx.x, tid = threadIdx.x, col = tid >> 2, part = tid & 3;
+  double *rhs = rhs_ptr(p);
+  if (__ldcg(sb.fail)) return;
+  if (b == 0) {
+    if (tid < GBA_NB) s_x[tid] = __ldcg(rhs + i * GBA_NB + tid);
+    __syncthreads();
+    const double *XI = sb.invL + (size_t)i * GBA_NB2;
+    double s = 0.0;
+#pragma unroll 4
+    for (int m = part * 16; m < part * 16 + 16; m++) s += __ldcg(XI + m * GBA_NB + col) * s_x[m];
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    __syncthreads();
+    if (part == 0) rhs[i * GBA_NB + col] = s;
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) atomicExch(&sb.flagX[i], 1u);
     return;
   }
-  for (int i = tid; i < p.ld; i += 256) s_x[i] = rhs[i];
+  if (b - 1 >= sb.rowcnt[i]) return;
+  const int k = sb.rowcols[i * p.nT + b - 1];
+  const double *L = p.sys + (size_t)p.tslot[i * p.nT + k] * GBA_NB2;
+  // prefetch this thread's slice of the tile while waiting for x_i
+  double l[16];
+#pragma unroll
+  for (int m = 0; m < 16; m++) l[m] = __ldcg(L + (part * 16 + m) * GBA_NB + col);
+  if (tid == 0)
+    while (ld_acquire(&sb.flagX[i]) == 0u) __nanosleep(20);
   __syncthreads();
-  // forward
-  for (int kk = 0; kk < nT; kk++) {
-    const double *XI = invL + (size_t)kk * GBA_NB2 + row * GBA_NB + part * 16;
-    double s = 0.0;
+  if (tid < GBA_NB) s_x[tid] = __ldcg(rhs + i * GBA_NB + tid);
+  __syncthreads();
+  double s = 0.0;
 #pragma unroll
-    for (int m = 0; m < 16; m++) s += XI[m] * s_x[kk * GBA_NB + part * 16 + m];
-    s += __shfl_xor_sync(0xffffffffu, s, 1);
-    s += __shfl_xor_sync(0xffffffffu, s, 2);
-    __syncthreads();
-    if (part == 0) {
-      s_y[row] = s;
-      s_x[kk * GBA_NB + row] = s;
-    }
-    __syncthreads();
-    const int cnt = colcnt[kk];
-    for (int a = 0; a < cnt; a++) {
-      const int i = colrows[kk * nT + a];
-      const double *L = p.sys + (size_t)p.tslot[i * nT + kk] * GBA_NB2 + row * GBA_NB + part * 16;
-      double u = 0.0;
-#pragma unroll
-      for (int m = 0; m < 16; m++) u += L[m] * s_y[part * 16 + m];
-      u += __shfl_xor_sync(0xffffffffu, u, 1);
-      u += __shfl_xor_sync(0xffffffffu, u, 2);
-      if (part == 0) s_x[i * GBA_NB + row] -= u;
-    }
-    __syncthreads();
+  for (int m = 0; m < 16; m++) s += l[m] * s_x[part * 16 + m];
+  s += __shfl_xor_sync(0xffffffffu, s, 1);
+  s += __shfl_xor_sync(0xffffffffu, s, 2);
+  if (part == 0) rhs[k * GBA_NB + col] -= s;
+}
+
+// dx = (float) x in the caller's pose order, or zero when the factorisation failed
+// (droid_kernels.cu:1202-1210, chol.py:13-15; the reference hands dx back as fp32, :1204-1205)
+__global__ void k_dx_out(BaParams p, SolverBufs sb) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int failed = *sb.fail;
+  if (i < 6 * p.P) {
+    const int pose = i / 6, r = i - 6 * pose;
+    p.dx[i] = failed ? 0.f : (float)rhs_ptr(p)[6 * p.perm[pose] + r];
   }
-  // backward
-  for (int kk = nT - 1; kk >= 0; kk--) {
-    const int cnt = colcnt[kk];
-    // t = y_kk - sum_i L[i,kk]^T x_i : thread (col = row, part) sums a quarter of the rows
-    double t = 0.0;
-    for (int a = 0; a < cnt; a++) {
-      const int i = colrows[kk * nT + a];
-      const double *L = p.sys + (size_t)p.tslot[i * nT + kk] * GBA_NB2;
-#pragma unroll 4
-      for (int m = part * 16; m < part * 16 + 16; m++) t += L[m * GBA_NB + row] * s_x[i * GBA_NB + m];
-    }
-    t += __shfl_xor_sync(0xffffffffu, t, 1);
-    t += __shfl_xor_sync(0xffffffffu, t, 2);
-    __syncthreads();
-    if (part == 0) s_y[row] = s_x[kk * GBA_NB + row] - t;
-    __syncthreads();
-    // x_kk = inv(L_kk)^T * s_y
-    const double *XI = invL + (size_t)kk * GBA_NB2;
-    double s = 0.0;
-#pragma unroll 4
-    for (int m = part * 16; m < part * 16 + 16; m++) s += XI[m * GBA_NB + row] * s_y[m];
-    s += __shfl_xor_sync(0xffffffffu, s, 1);
-    s += __shfl_xor_sync(0xffffffffu, s, 2);
-    __syncthreads();
-    if (part == 0) s_x[kk * GBA_NB + row] = s;
-    __syncthreads();
+}
+__global__ void k_fail_account(BaParams p, SolverBufs sb) {
+  if (*sb.fail) {
+    p.st->chol_fail += 1;
+    *sb.fail = 0;
   }
-  // the reference hands dx back as fp32 (droid_kernels.cu:1204-1205)
-  for (int i = tid; i < 6 * p.P; i += 256) p.dx[i] = (float)s_x[i];
 }

@@ -295,7 +295,7 @@ def test_full_size_properties(name):
     np.testing.assert_allclose(np.linalg.norm(r.poses[:, 3:], axis=1), 1.0, atol=1e-4)
     # determinism of the state up to atomics-order noise, and edge-permutation invariance
     r2 = run_ba(g)
-    assert rel(r2.poses, r.poses) < 1e-6 and rel(r2.disps, r.disps) < 1e-6
+    assert rel(r2.poses, r.poses) < 1e-5 and rel(r2.disps, r.disps) < 1e-5
     perm = np.random.default_rng(1).permutation(g.n_edges)
     g.ii, g.jj, g.targets, g.weights = g.ii[perm], g.jj[perm], g.targets[perm], g.weights[perm]
     r3 = run_ba(g)
