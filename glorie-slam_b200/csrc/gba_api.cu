@@ -28,7 +28,8 @@ struct gba_ctx {
   float *hpart, *edge_hv, *Q, *W, *gram, *dx, *dzbuf, *dspo_part, *dwq;
   size_t gram_cap, sys_cap;
   double *sys;
-  int *tslot, *perm, *dspo_bad;
+  int *tslot, *perm, *iperm, *dspo_bad;
+  int pos_cap;
   SolverBufs sb;
   unsigned int *flags;  // flagA | cntB | cntD | flagX | ticket, nT_max each
   int nT_max, hpart_chunks, panel_capacity;
@@ -103,7 +104,7 @@ extern "C" void gba_destroy(gba_ctx *c) {
   if (!c) return;
   cudaSetDevice(c->device);
   void *ptrs[] = {c->kx, c->fmap, c->deg, c->eptr, c->eidx, c->ek, c->goff, c->st_d, c->geo, c->hpart, c->edge_hv,
-                  c->Q, c->W, c->gram, c->dx, c->dzbuf, c->dspo_part, c->dwq, c->sys, c->tslot, c->perm, c->dspo_bad,
+                  c->Q, c->W, c->gram, c->dx, c->dzbuf, c->dspo_part, c->dwq, c->sys, c->tslot, c->perm, c->iperm, c->dspo_bad,
                   c->sb.tbits, c->sb.colrows, c->sb.colcnt, c->sb.rowcols, c->sb.rowcnt, c->sb.invL, c->sb.fail,
                   c->flags};
   for (void *q : ptrs)
@@ -142,7 +143,8 @@ extern "C" int gba_create(gba_ctx **out, int device, int max_frames, int max_edg
   c->wd = wd;
   c->HW = ht * wd;
   const size_t N = max_frames, E = std::max(max_edges, 1), HW = c->HW;
-  c->nT_max = (6 * max_frames + GBA_NB - 1) / GBA_NB;
+  c->pos_cap = max_frames + 17 * ORD_ALIGN;  // room for the segment padding of the ordering
+  c->nT_max = (6 * c->pos_cap + GBA_NB - 1) / GBA_NB;
   const size_t nT = c->nT_max, ld = nT * GBA_NB;
   if (nT > TS_MAXT) {
     free(ctx);
@@ -185,6 +187,7 @@ extern "C" int gba_create(gba_ctx **out, int device, int max_frames, int max_edg
   CKC(dalloc(&c->sb.invL, nT * GBA_NB2));
   CKC(dalloc(&c->tslot, nT * nT));
   CKC(dalloc(&c->perm, N));
+  CKC(dalloc(&c->iperm, (size_t)c->pos_cap));
   CKC(dalloc(&c->sb.colrows, nT * nT));
   CKC(dalloc(&c->sb.colcnt, nT));
   CKC(dalloc(&c->sb.rowcols, nT * nT));
@@ -234,7 +237,7 @@ static int build_index(gba_ctx *c, const int64_t *kx_global, int n_kx, bool want
     LAUNCH_CHECK("k_prep_fill");
   }
   if (want_tiles) {
-    k_order<<<1, 1024, (size_t)((p.P + 3) / 4) * 4, s>>>(p);
+    k_order<<<1, 1024, (size_t)((p.P + 3) / 4) * 4, s>>>(p, c->pos_cap);
     LAUNCH_CHECK("k_order");
     CK(cudaMemsetAsync(c->sb.tbits, 0, (size_t)p.nT * TS_WORDS * sizeof(unsigned int), s));
     k_tile_mark<<<p.N, 128, 0, s>>>(p, c->sb.tbits);
@@ -280,14 +283,16 @@ extern "C" int gba_ba_begin(gba_ctx *c, float *poses, float *disps, const float 
   p.owned = owned; p.goff = c->goff; p.st = c->st_d; p.geo = c->geo; p.hpart = c->hpart; p.edge_hv = c->edge_hv;
   p.Q = c->Q; p.W = c->W; p.gram = c->gram; p.dx = c->dx; p.dz_out = c->dzbuf; p.sys = c->sys; p.tslot = c->tslot;
   p.perm = c->perm;
-  p.nT = (6 * p.P + GBA_NB - 1) / GBA_NB;
-  p.ld = p.nT * GBA_NB;
+  p.iperm = c->iperm;
+  p.nT = c->nT_max;  // stride of the tile tables; the actual tile count comes back in the status
+  p.ld = 0;
   c->last_P = p.P;
   int rc = build_index(c, kx_global, n_kx, true);
   if (rc) return rc;
   const Status &st = *c->st_h;
   if (!motion_only && eta_rows != st.K)
     return fail_msg(c, GBA_EINVAL, "eta has %d rows but the graph has K = %d depth keyframes", eta_rows, st.K);
+  p.ld = st.n_tiles * GBA_NB;
   if ((size_t)st.n_slots * GBA_NB2 + p.ld > c->sys_cap)
     return fail_msg(c, GBA_ECAPACITY, "reduced system needs %d tiles, capacity exceeded", st.n_slots);
   c->sys_count = (size_t)st.n_slots * GBA_NB2 + p.ld;
@@ -338,10 +343,8 @@ extern "C" int gba_ba_build(gba_ctx *c) {
   stage_end(c);
   stage_begin(c, GBA_STAGE_POSE);
   CK(cudaMemsetAsync(c->sys, 0, c->sys_count * sizeof(double), s));
-  if (p.ld > 6 * p.P) {
-    k_pad_diag<<<1, GBA_NB, 0, s>>>(p);
-    LAUNCH_CHECK("k_pad_diag");
-  }
+  k_pad_diag<<<(p.ld + 255) / 256, 256, 0, s>>>(p);
+  LAUNCH_CHECK("k_pad_diag");
   if (p.E > 0) {
     k_edge_finish<<<(p.E + 127) / 128, 128, 0, s>>>(p);
     LAUNCH_CHECK("k_edge_finish");
@@ -386,35 +389,52 @@ extern "C" int gba_ba_solve(gba_ctx *c) {
   }
   CK(cudaMemsetAsync(c->flags, 0, (size_t)5 * c->nT_max * sizeof(unsigned int), s));
   {
-    // fused tile-column kernel; 16-row slabs (4 CTAs per tile) spread the fp64 work over more
-    // SMs while the structure is sparse, whole tiles when a column already has plenty of tiles
+    // Tile columns of the n_seg band segments are independent: step t of every segment is one
+    // launch (grid.y = segment); the closure block follows column by column.  16-row slabs
+    // (4 CTAs per tile) spread the fp64 work over more SMs while the structure is sparse.
+    const int nT = st.n_tiles, nseg = st.n_seg, segT = st.seg_tiles, band = nseg > 1 ? nseg * segT : 0;
     const int mc = st.max_col, pairs = mc * (mc + 1) / 2;
     const bool split = (1 + mc + pairs) <= 4 * c->sm_count;
-    for (int kk = 0; kk < p.nT; kk++) {
-      const bool last = kk + 1 >= p.nT;
-      if (getenv("GBA_UNFUSED")) {  // diagnostic: the three phases as separate launches
-        k_potrf_diag<<<1, 256, kSolverSmem, s>>>(p, c->sb, kk);
+    const int atomic_from = nseg > 1 ? band : (1 << 30);
+    auto panel = [&](int kk0, int stride, int ny, bool last) -> int {
+      if (getenv("GBA_UNFUSED") && ny == 1) {  // diagnostic: the three phases as separate launches
+        k_potrf_diag<<<1, 256, kSolverSmem, s>>>(p, c->sb, kk0);
         LAUNCH_CHECK("k_potrf_diag");
         if (mc > 0 && !last) {
-          k_trsm<<<mc, 256, kSolverSmem, s>>>(p, c->sb, kk);
+          k_trsm<<<mc, 256, kSolverSmem, s>>>(p, c->sb, kk0);
           LAUNCH_CHECK("k_trsm");
-          k_syrk<<<pairs, 256, kSolverSmem, s>>>(p, c->sb, kk);
+          k_syrk<<<pairs, 256, kSolverSmem, s>>>(p, c->sb, kk0);
           LAUNCH_CHECK("k_syrk");
         }
       } else if (split) {
-        k_panel<16><<<last ? 1 : 1 + 4 * mc + 4 * pairs, 256, kSolverSmem, s>>>(p, c->sb, kk, mc);
+        k_panel<16><<<dim3(last ? 1 : 1 + 4 * mc + 4 * pairs, ny), 256, kSolverSmem, s>>>(p, c->sb, kk0, stride, mc,
+                                                                                      atomic_from);
         LAUNCH_CHECK("k_panel");
       } else {
-        k_panel<64><<<last ? 1 : 1 + mc + pairs, 256, kSolverSmem, s>>>(p, c->sb, kk, mc);
+        k_panel<64><<<dim3(last ? 1 : 1 + mc + pairs, ny), 256, kSolverSmem, s>>>(p, c->sb, kk0, stride, mc,
+                                                                              atomic_from);
         LAUNCH_CHECK("k_panel");
       }
+      return GBA_OK;
+    };
+    for (int t = 0; t < (nseg > 1 ? segT : 0); t++) {
+      const int rc = panel(t, segT, nseg, false);
+      if (rc) return rc;
     }
-  }
-  stage_end(c);
-  stage_begin(c, GBA_STAGE_SOLVE);
-  for (int i = p.nT - 1; i >= 0; i--) {
-    k_back_step<<<1 + (i > 0 ? st.max_row : 0), 256, 0, s>>>(p, c->sb, i);
-    LAUNCH_CHECK("k_back_step");
+    for (int kk = band; kk < nT; kk++) {
+      const int rc = panel(kk, 0, 1, kk + 1 >= nT);
+      if (rc) return rc;
+    }
+    stage_end(c);
+    stage_begin(c, GBA_STAGE_SOLVE);
+    for (int i = nT - 1; i >= band; i--) {
+      k_back_step<<<1 + (i > 0 ? st.max_row : 0), 256, 0, s>>>(p, c->sb, i, 0);
+      LAUNCH_CHECK("k_back_step");
+    }
+    for (int t = (nseg > 1 ? segT : 0) - 1; t >= 0; t--) {
+      k_back_step<<<dim3(1 + st.max_row, nseg), 256, 0, s>>>(p, c->sb, t, segT);
+      LAUNCH_CHECK("k_back_step");
+    }
   }
   k_dx_out<<<(6 * p.P + 255) / 256, 256, 0, s>>>(p, c->sb);
   LAUNCH_CHECK("k_dx_out");
@@ -559,7 +579,7 @@ extern "C" int gba_query(gba_ctx *c, gba_info *info) {
   info->n_poses = c->last_P;
   info->max_out_degree = st.max_deg;
   info->chol_failures = st.chol_fail;
-  info->n_tiles = c->p.nT;
+  info->n_tiles = st.n_tiles;
   info->n_active_tiles = st.n_slots;
   info->kernel_launches = c->launches;
   info->reserved = 0;
@@ -582,13 +602,14 @@ extern "C" int gba_get(gba_ctx *c, int what, void *dst, size_t bytes) {
     case GBA_GET_Q: src = c->Q; need = (size_t)st.K * p.HW * 4; break;
     case GBA_GET_W: src = c->W; need = (size_t)st.K * p.HW * 4; break;
     case GBA_GET_TILEMASK: {
-      need = (size_t)p.nT * p.nT;
+      const int nTa = st.n_tiles;
+      need = (size_t)nTa * nTa;
       if (bytes < need) return fail_msg(c, GBA_EINVAL, "gba_get: buffer too small (%zu < %zu)", bytes, need);
-      std::vector<unsigned int> bits((size_t)p.nT * TS_WORDS);
+      std::vector<unsigned int> bits((size_t)nTa * TS_WORDS);
       CK(cudaMemcpy(bits.data(), c->sb.tbits, bits.size() * sizeof(unsigned int), cudaMemcpyDeviceToHost));
       unsigned char *out = (unsigned char *)dst;
-      for (int i = 0; i < p.nT; i++)
-        for (int j = 0; j < p.nT; j++) out[(size_t)i * p.nT + j] = (bits[(size_t)i * TS_WORDS + (j >> 5)] >> (j & 31)) & 1;
+      for (int i = 0; i < nTa; i++)
+        for (int j = 0; j < nTa; j++) out[(size_t)i * nTa + j] = (bits[(size_t)i * TS_WORDS + (j >> 5)] >> (j & 31)) & 1;
       return GBA_OK;
     }
     case GBA_GET_SYSTEM: {

@@ -34,6 +34,10 @@ struct Status {          // device -> host after the index build
   int max_row;           // max active tiles left of the diagonal in a tile row
   int n_closure;         // poses moved to the end by the arrowhead ordering
   int band_w;            // chosen long-range threshold (-1: none)
+  int n_seg;             // independent band segments (nested dissection); 1 = plain band
+  int seg_tiles;         // tile columns per segment
+  int n_pos;             // pose positions of the reduced system incl. padding
+  int pad2;
   unsigned long long gram_floats;  // total size of the per-frame Gram buffers
 };
 
@@ -61,8 +65,10 @@ struct BaParams {
   // reduced system (tile packed, fp64)
   double *sys;    // [n_slots][NB*NB] then rhs [ld]
   int *tslot;     // [nT][nT]
-  int *perm;      // [P] pose -> position in the reduced system (arrowhead ordering)
-  int nT, ld;
+  int *perm;      // [P] pose -> position in the reduced system (ordering below)
+  int *iperm;     // [positions] position -> pose, -1 for padding positions
+  int nT;         // STRIDE of the tile tables (upper bound); the actual count is st->n_tiles
+  int ld;
 };
 
 __device__ __forceinline__ float ldg_stream(const float *p) { return __ldcs(p); }

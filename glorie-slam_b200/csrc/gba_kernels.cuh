@@ -690,8 +690,9 @@ __global__ void __launch_bounds__(SCHUR_NT) k_schur(BaParams p) {
 // Levenberg-Marquardt damping of the diagonal: d += ep + lm * d
 // (droid_kernels.cu:1197 after the Schur complement; chol.py:66-68 before it).
 __global__ void k_damp(BaParams p, float lm, float ep) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= 6 * p.P) return;
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= 6 * p.P) return;
+  const int i = 6 * p.perm[q / 6] + q % 6;
   double *d = sys_at(p, i, i);
   *d += (double)ep + (double)lm * (*d);
 }

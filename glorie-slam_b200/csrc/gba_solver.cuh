@@ -28,32 +28,46 @@ struct SolverBufs {
 };
 
 // ---------------------------------------------------------------------------------------------
-// Pose ordering.  Edges with |i - j| > W are "long range"; their destination poses form the
-// closure set C (through the Schur complement the destination couples with every neighbour of
-// the source, so it cannot stay inside a band).  W is chosen from a few candidates by a flop
-// model of the resulting band + arrow factorisation; perm puts non-C poses first (temporal
-// order), C poses last.  One CTA.
+// Pose ordering = arrowhead + nested dissection, chosen on the device (one CTA).
+//  1. Edges with |i - j| > W are "long range"; their destination poses form the closure set C
+//     (through the Schur complement the destination couples with every neighbour of the source, so
+//     it cannot stay inside a band).  W is picked from a few candidates by a flop model of the
+//     resulting band + arrow factorisation.
+//  2. The remaining poses form a band (temporal order) of half width hb = 2 * max short-range
+//     |i - j|.  The band is cut into n_seg segments by separators of hb consecutive band poses; the
+//     separators join the closure block.  Segments are independent of each other, so the same
+//     step of every segment is factorised by one launch: the sequential chain shrinks from
+//     all tile columns to seg_tiles + closure tile columns.
+//  3. Segments start on a multiple of 32 pose positions (= 3 tiles exactly) so that no tile is
+//     shared by two segments; the unused positions are padding (unit diagonal).
+// Layout of positions: [segment 0 | pad][segment 1 | pad] ... [separators and C, temporal order].
 // ---------------------------------------------------------------------------------------------
 #define ORD_NC 8
-__global__ void __launch_bounds__(1024) k_order(BaParams p) {
-  __shared__ int s_cnt[ORD_NC];
-  __shared__ int s_best, s_warp[32], s_carry;
-  extern __shared__ unsigned int s_flagw[];  // [ceil(P/4)] one byte per pose: bit c = in C for candidate c
+#define ORD_ALIGN 32  // pose positions; 32 * 6 rows = 3 tiles
+__global__ void __launch_bounds__(1024) k_order(BaParams p, int pos_cap) {
+  __shared__ int s_cnt[ORD_NC], s_reff[ORD_NC];
+  __shared__ int s_best, s_warp[32], s_nseg, s_seglen, s_hb, s_SL;
+  extern __shared__ unsigned int s_flagw[];  // one byte per pose: bit c = in C for candidate c
   unsigned char *s_flag = reinterpret_cast<unsigned char *>(s_flagw);
   const int tid = threadIdx.x, P = p.P;
   const int cand[ORD_NC] = {4, 8, 16, 32, 64, 128, 256, 1 << 30};
   for (int i = tid; i < (P + 3) / 4; i += blockDim.x) s_flagw[i] = 0;
-  if (tid < ORD_NC) s_cnt[tid] = 0;
+  if (tid < ORD_NC) {
+    s_cnt[tid] = 0;
+    s_reff[tid] = 0;
+  }
   __syncthreads();
   for (int n = tid; n < p.E; n += blockDim.x) {
     const long long i = p.ii[n], j = p.jj[n];
     const long long pj = j - p.t0;
     if (pj < 0 || pj >= P || i == j) continue;
-    const long long d = i > j ? i - j : j - i;
+    const int d = (int)(i > j ? i - j : j - i);
     unsigned m = 0;
 #pragma unroll
-    for (int c = 0; c < ORD_NC; c++)
+    for (int c = 0; c < ORD_NC; c++) {
       if (d > cand[c]) m |= 1u << c;
+      else atomicMax(&s_reff[c], d);
+    }
     if (m) atomicOr(&s_flagw[pj >> 2], m << (8 * (pj & 3)));
   }
   __syncthreads();
@@ -69,7 +83,7 @@ __global__ void __launch_bounds__(1024) k_order(BaParams p) {
     int bi = ORD_NC - 1;
     for (int c = 0; c < ORD_NC; c++) {
       const double nC = s_cnt[c], nB = P - nC;
-      const double b = fmin(2.0 * cand[c], nB);  // band half width in poses
+      const double b = fmin(2.0 * (double)max(s_reff[c], 1), nB);  // band half width in poses
       // band factor + arrow rows + arrow trailing update + dense tail (pose^3 units)
       const double cost = nB * b * b + nC * nB * b + nB * nC * nC * 0.5 + nC * nC * nC / 3.0;
       if (cost < best) {
@@ -78,18 +92,41 @@ __global__ void __launch_bounds__(1024) k_order(BaParams p) {
       }
     }
     s_best = bi;
-    s_carry = 0;
-    p.st->n_closure = s_cnt[bi];
-    p.st->band_w = cand[bi] > 1000000 ? -1 : cand[bi];
+    const int nC = s_cnt[bi], nB = P - nC, hb = min(2 * max(s_reff[bi], 1), nB);
+    // nested dissection: pick the segment count with the shortest sequential chain of tile columns
+    int best_seg = 1, best_chain = 1 << 30, best_len = nB;
+    for (int ns = 1; ns <= 16; ns *= 2) {
+      const int nsep = (ns - 1) * hb;
+      if (ns > 1 && (nB - nsep < ns * 2 * hb || nB - nsep < ns * ORD_ALIGN)) break;  // segments too short
+      const int len = (nB - nsep + ns - 1) / ns;                               // real poses per segment
+      const int SL = (ns == 1) ? len : (len + ORD_ALIGN - 1) / ORD_ALIGN * ORD_ALIGN;
+      if ((ns == 1 ? nB : ns * SL) + nC + nsep > pos_cap) break;
+      const int chain = (6 * SL + GBA_NB - 1) / GBA_NB + (6 * (nC + nsep) + GBA_NB - 1) / GBA_NB;
+      if (chain < best_chain) {
+        best_chain = chain;
+        best_seg = ns;
+        best_len = len;
+      }
+    }
+    s_nseg = best_seg;
+    s_seglen = best_len;
+    s_hb = hb;
+    s_SL = (best_seg == 1) ? best_len : (best_len + ORD_ALIGN - 1) / ORD_ALIGN * ORD_ALIGN;
   }
   __syncthreads();
-  const int bc = s_best, nB = P - s_cnt[bc];
-  // positions: inclusive scan of the "not in C" flags
+  const int bc = s_best, nseg = s_nseg, seglen = s_seglen, hb = s_hb, SL = s_SL;
+  const int band_end = nseg * SL;  // first position of the closure block (nseg == 1: == nB)
+  // band index b of a non-C pose = number of non-C poses before it.  With nseg > 1 the band is
+  // [seg 0: seglen][sep: hb][seg 1: seglen][sep: hb] ... ; separators go to the closure block.
+  // Closure positions are handed out in temporal order: a second scan counts closure members.
+  for (int i = tid; i < pos_cap; i += blockDim.x) p.iperm[i] = -1;
+  __syncthreads();
+  int carry_band = 0, carry_clo = 0;
   for (int base = 0; base < P; base += blockDim.x) {
     const int i = base + tid;
     const int inC = (i < P) ? ((s_flag[i] >> bc) & 1) : 0;
-    const int f = (i < P) ? 1 - inC : 0;
-    int v = f;
+    // pass 1: band index
+    int v = (i < P) ? 1 - inC : 0;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
       const int u = __shfl_up_sync(0xffffffffu, v, o);
@@ -107,11 +144,63 @@ __global__ void __launch_bounds__(1024) k_order(BaParams p) {
       s_warp[tid] = w;
     }
     __syncthreads();
-    const int incl = v + ((tid >> 5) ? s_warp[(tid >> 5) - 1] : 0) + s_carry;  // non-C poses among [0, i]
-    if (i < P) p.perm[i] = inC ? nB + (i - incl) : incl - 1;
+    const int bincl = v + ((tid >> 5) ? s_warp[(tid >> 5) - 1] : 0) + carry_band;
+    const int total_band = s_warp[31] + carry_band;
     __syncthreads();
-    if (tid == blockDim.x - 1) s_carry = incl;
+    // is this pose a closure member (C or separator)?
+    int seg = 0, off = 0, clo = inC;
+    if (i < P && !inC) {
+      const int bidx = bincl - 1;
+      if (nseg > 1) {
+        seg = bidx / (seglen + hb);
+        off = bidx - seg * (seglen + hb);
+        if (seg >= nseg) {  // tail beyond the last separator belongs to the last segment
+          seg = nseg - 1;
+          off = bidx - seg * (seglen + hb);
+        }
+        if (off >= seglen && seg < nseg - 1) clo = 1;      // separator
+        else if (off >= SL) clo = 1;                        // overflow of the last segment
+      } else
+        off = bidx;
+    }
+    // pass 2: closure index
+    int w2 = (i < P) ? clo : 0;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int u = __shfl_up_sync(0xffffffffu, w2, o);
+      if ((tid & 31) >= o) w2 += u;
+    }
+    if ((tid & 31) == 31) s_warp[tid >> 5] = w2;
     __syncthreads();
+    if (tid < 32) {
+      int w = s_warp[tid];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int u = __shfl_up_sync(0xffffffffu, w, o);
+        if (tid >= o) w += u;
+      }
+      s_warp[tid] = w;
+    }
+    __syncthreads();
+    const int cincl = w2 + ((tid >> 5) ? s_warp[(tid >> 5) - 1] : 0) + carry_clo;
+    const int total_clo = s_warp[31] + carry_clo;
+    __syncthreads();
+    if (i < P) {
+      const int pos = clo ? band_end + cincl - 1 : seg * SL + off;
+      p.perm[i] = pos;
+      p.iperm[pos] = i;
+    }
+    carry_band = total_band;
+    carry_clo = total_clo;
+  }
+  if (tid == 0) {
+    const int npos = band_end + carry_clo;
+    p.st->n_closure = carry_clo;
+    p.st->band_w = cand[bc] > 1000000 ? -1 : cand[bc];
+    p.st->n_seg = nseg;
+    p.st->seg_tiles = (nseg == 1) ? 0 : 6 * SL / GBA_NB;
+    p.st->n_pos = npos;
+    p.st->n_tiles = (6 * npos + GBA_NB - 1) / GBA_NB;
   }
 }
 
@@ -145,7 +234,7 @@ __global__ void __launch_bounds__(512) k_tile_fill(BaParams p, SolverBufs sb) {
   __shared__ int s_start[TS_MAXT + 1];
   __shared__ int s_maxc, s_maxr;
   unsigned int *bits = sb.tbits;
-  const int nT = p.nT, tid = threadIdx.x, nW = (nT + 31) / 32;
+  const int nT = p.st->n_tiles, nS = p.nT, tid = threadIdx.x, nW = (nT + 31) / 32;  // nS = table stride
   for (int i = tid; i < nT; i += blockDim.x) bits[i * TS_WORDS + (i >> 5)] |= 1u << (i & 31);
   if (tid == 0) s_maxc = s_maxr = 0;
   __syncthreads();
@@ -188,17 +277,17 @@ __global__ void __launch_bounds__(512) k_tile_fill(BaParams p, SolverBufs sb) {
       c += __popc(bits[i * TS_WORDS + (j >> 5)] & ((1u << (j & 31)) - 1u));
       slot = s_start[i] + c;
     }
-    p.tslot[idx] = slot;
+    p.tslot[i * nS + j] = slot;
   }
   for (int kk = tid; kk < nT; kk += blockDim.x) {
     int c = 0;
     for (int i = kk + 1; i < nT; i++)
-      if ((bits[i * TS_WORDS + (kk >> 5)] >> (kk & 31)) & 1) sb.colrows[kk * nT + c++] = i;
+      if ((bits[i * TS_WORDS + (kk >> 5)] >> (kk & 31)) & 1) sb.colrows[kk * nS + c++] = i;
     sb.colcnt[kk] = c;
     atomicMax(&s_maxc, c);
     int r = 0;
     for (int j = 0; j < kk; j++)
-      if ((bits[kk * TS_WORDS + (j >> 5)] >> (j & 31)) & 1) sb.rowcols[kk * nT + r++] = j;
+      if ((bits[kk * TS_WORDS + (j >> 5)] >> (j & 31)) & 1) sb.rowcols[kk * nS + r++] = j;
     sb.rowcnt[kk] = r;
     atomicMax(&s_maxr, r);
   }
@@ -209,10 +298,13 @@ __global__ void __launch_bounds__(512) k_tile_fill(BaParams p, SolverBufs sb) {
   }
 }
 
-// padded rows/cols of the last tile get a unit diagonal so the factorisation runs through
+// rows of padding positions (segment alignment, tail of the last tile) get a unit diagonal so the
+// factorisation runs through them
 __global__ void k_pad_diag(BaParams p) {
-  const int i = 6 * p.P + blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < p.ld) *sys_at(p, i, i) = 1.0;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= p.st->n_tiles * GBA_NB) return;
+  const int pos = i / 6;
+  if (pos >= p.st->n_pos || p.iperm[pos] < 0) *sys_at(p, i, i) = 1.0;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -234,56 +326,116 @@ __device__ __forceinline__ double fast_rsqrt(double d) {
   return y;
 }
 
-// Cholesky of the diagonal tile, its inverse, and the forward substitution y_kk = inv(L_kk) b_kk.
-// Right-looking with ONE barrier per pivot: the update reads the unscaled column j (which no
-// later step touches) and 1/d; the scaled column goes to a separate output array.
-__device__ void role_potrf(const BaParams &p, const SolverBufs &sb, int kk, double *s_buf) {
-  TilePtr A = reinterpret_cast<TilePtr>(s_buf);
-  TilePtr Lo = reinterpret_cast<TilePtr>(s_buf + TILE_STRIDE);
-  TilePtr X = reinterpret_cast<TilePtr>(s_buf + 2 * TILE_STRIDE);
-  __shared__ int s_bad;
-  __shared__ double s_v[GBA_NB], s_rd[GBA_NB];
+// Copy ROWS x 64 doubles from global (L2, row stride 64) into a padded shared tile; all the
+// 128-bit loads are issued before the first store so that their latencies overlap.
+template <int ROWS>
+__device__ __forceinline__ void load_rows(TilePtr dst, const double *src) {
+  constexpr int NV = ROWS * GBA_NB / 2 / 256;  // double2 per thread
+  static_assert(NV >= 1, "tile too small");
+  double2 v[NV];
   const int tid = threadIdx.x;
+#pragma unroll
+  for (int k = 0; k < NV; k++) v[k] = __ldcg(reinterpret_cast<const double2 *>(src) + tid + 256 * k);
+#pragma unroll
+  for (int k = 0; k < NV; k++) {
+    const int e = 2 * (tid + 256 * k);
+    dst[e >> 6][e & 63] = v[k].x;
+    dst[e >> 6][(e & 63) + 1] = v[k].y;
+  }
+}
+
+__device__ __forceinline__ double fast_rcp(double d) {
+  double r = (double)__frcp_rn((float)d);
+  double e = fma(-d, r, 1.0);
+  r = fma(r, e, r);
+  e = fma(-d, r, 1.0);
+  r = fma(r, e, r);
+  return r;
+}
+
+// Cholesky of the diagonal tile, its inverse, and the forward substitution y_kk = inv(L_kk) b_kk.
+// The tile lives in REGISTERS (thread (ty,tx) owns elements (ty+16u, tx+16v)); per pivot only
+// column j goes through shared memory (double buffered, one barrier per pivot).  The pivot loop is
+// latency bound, so its dependent chain is kept short: the update uses the UNSCALED column and
+// 1/d (Newton from an fp32 seed), is applied to all 16 owned elements without predicates (elements
+// of finished rows/columns are dead, updating them is harmless), the owner of the next column is
+// known at compile time, and the sqrt scaling of the columns happens after the loop.
+__device__ void role_potrf(const BaParams &p, const SolverBufs &sb, int kk, double *s_buf) {
+  TilePtr Lo = reinterpret_cast<TilePtr>(s_buf);
+  TilePtr X = reinterpret_cast<TilePtr>(s_buf + TILE_STRIDE);
+  TilePtr Tm = reinterpret_cast<TilePtr>(s_buf + 2 * TILE_STRIDE);
+  __shared__ int s_bad;
+  __shared__ double s_v[GBA_NB], s_rd[GBA_NB], s_dinv[GBA_NB], s_col[2][GBA_NB];
+  const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
   double *T = p.sys + (size_t)p.tslot[kk * p.nT + kk] * GBA_NB2;
   if (tid == 0) s_bad = 0;
-  for (int i = tid; i < GBA_NB2; i += 256) {
-    const int r = i >> 6, c = i & 63;
-    A[r][c] = (c <= r) ? __ldcg(T + i) : 0.0;
-    Lo[r][c] = 0.0;
-    X[r][c] = 0.0;
+  double a[4][4];
+#pragma unroll
+  for (int u = 0; u < 4; u++)
+#pragma unroll
+    for (int v = 0; v < 4; v++) {
+      const int r = ty + 16 * u, c = tx + 16 * v;
+      a[u][v] = (c <= r) ? __ldcg(T + r * GBA_NB + c) : 0.0;
+    }
+  for (int i = tid; i < GBA_NB * (GBA_NB + 1); i += 256) {
+    (&Lo[0][0])[i] = 0.0;
+    (&X[0][0])[i] = 0.0;
+  }
+  if (tx == 0) {  // column 0 -> buffer 0
+#pragma unroll
+    for (int u = 0; u < 4; u++) s_col[0][ty + 16 * u] = a[u][0];
   }
   __syncthreads();
-  // thread -> 4x4 block of the tile: rows r0..r0+3, cols c0..c0+3
-  const int r0 = (tid >> 4) * 4, c0 = (tid & 15) * 4;
-  for (int j = 0; j < GBA_NB; j++) {
-    const double d = A[j][j];
-    if (!(d > 0.0) || isinf(d)) {  // SimplicialLLT reports NumericalIssue on a non-positive pivot
-      if (tid == 0) s_bad = 1;
-      break;  // uniform: every thread reads the same d
-    }
-    const double rs = fast_rsqrt(d), dinv = rs * rs;
-    if (tid < GBA_NB && tid >= j) Lo[tid][j] = A[tid][j] * rs;
-    if (tid == 0) s_rd[j] = rs;  // 1 / L[j][j]
-    if (r0 + 3 > j && c0 + 3 > j && r0 + 3 >= c0) {
+  bool bad = false;
+#pragma unroll
+  for (int v0 = 0; v0 < 4; v0++) {  // columns 16 v0 .. 16 v0 + 15
+    for (int jj = 0; jj < 16; jj++) {
+      const int j = 16 * v0 + jj;
+      const double *col = s_col[j & 1];
+      const double d = col[j];
+      if (!(d > 0.0) || isinf(d)) bad = true;  // SimplicialLLT: NumericalIssue on a non-positive pivot
+      const double dinv = fast_rcp(d);
+      if (tid < GBA_NB) Lo[tid][j] = (tid >= j) ? col[tid] : 0.0;  // unscaled, scaled after the loop
+      if (tid == 0) s_dinv[j] = dinv;
       double ar[4], ac[4];
 #pragma unroll
       for (int u = 0; u < 4; u++) {
-        ar[u] = A[r0 + u][j];
-        ac[u] = A[c0 + u][j] * dinv;
+        ar[u] = col[ty + 16 * u];
+        ac[u] = col[tx + 16 * u] * dinv;
       }
 #pragma unroll
       for (int u = 0; u < 4; u++)
 #pragma unroll
-        for (int v = 0; v < 4; v++)
-          if (r0 + u > j && c0 + v > j && c0 + v <= r0 + u) A[r0 + u][c0 + v] -= ar[u] * ac[v];
+        for (int v = 0; v < 4; v++) a[u][v] -= ar[u] * ac[v];
+      // owners of column j+1 publish it into the other buffer
+      if (jj < 15) {
+        if (tx == jj + 1) {
+#pragma unroll
+          for (int u = 0; u < 4; u++) s_col[(j + 1) & 1][ty + 16 * u] = a[u][v0];
+        }
+      } else if (v0 < 3) {
+        if (tx == 0) {
+#pragma unroll
+          for (int u = 0; u < 4; u++) s_col[(j + 1) & 1][ty + 16 * u] = a[u][(v0 + 1) & 3];
+        }
+      }
+      __syncthreads();
     }
-    __syncthreads();
   }
+  if (bad && tid == 0) s_bad = 1;
   __syncthreads();
   if (s_bad) {
     if (tid == 0) *sb.fail = 1;
     return;
   }
+  // scale the columns: L[:,j] = col_j / sqrt(d_j);  s_rd[j] = 1 / L[j][j] = sqrt(dinv_j)
+  if (tid < GBA_NB) s_rd[tid] = sqrt(s_dinv[tid]);
+  __syncthreads();
+  for (int i = tid; i < GBA_NB2; i += 256) {
+    const int r = i >> 6, c = i & 63;
+    Lo[r][c] *= s_rd[c];
+  }
+  __syncthreads();
   // ---- X = inv(L), blocked by 16 -----------------------------------------------------------
   // level 0: the four 16x16 diagonal blocks, column c of block B by 4 lanes (64 columns total)
   {
@@ -299,21 +451,33 @@ __device__ void role_potrf(const BaParams &p, const SolverBufs &sb, int kk, doub
   }
   __syncthreads();
   // block rows I = 1..3: T[I][J] = sum_{K=J}^{I-1} L[I][K] X[K][J];  X[I][J] = -X[I][I] T[I][J]
-  TilePtr Tm = A;  // A is dead now
+#pragma unroll
   for (int I = 1; I < 4; I++) {
+    constexpr int dummy = 0;
+    (void)dummy;
     const int ncol = 16 * I;  // columns 0 .. 16 I - 1
     for (int e = tid; e < 16 * ncol; e += 256) {
       const int r = 16 * I + e / ncol, c = e % ncol;
-      double s = 0.0;
-      for (int m = (c & ~15); m < 16 * I; m++) s += Lo[r][m] * X[m][c];
-      Tm[r][c] = s;
+      double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+      for (int m = (c & ~15); m < 16 * I; m += 4) {
+        s0 += Lo[r][m] * X[m][c];
+        s1 += Lo[r][m + 1] * X[m + 1][c];
+        s2 += Lo[r][m + 2] * X[m + 2][c];
+        s3 += Lo[r][m + 3] * X[m + 3][c];
+      }
+      Tm[r][c] = (s0 + s1) + (s2 + s3);
     }
     __syncthreads();
     for (int e = tid; e < 16 * ncol; e += 256) {
       const int r = 16 * I + e / ncol, c = e % ncol;
-      double s = 0.0;
-      for (int m = 16 * I; m <= r; m++) s += X[r][m] * Tm[m][c];
-      X[r][c] = -s;
+      double s0 = 0.0, s1 = 0.0;
+      int m = 16 * I;
+      for (; m + 1 <= r; m += 2) {
+        s0 += X[r][m] * Tm[m][c];
+        s1 += X[r][m + 1] * Tm[m + 1][c];
+      }
+      if (m <= r) s0 += X[r][m] * Tm[m][c];
+      X[r][c] = -(s0 + s1);
     }
     __syncthreads();
   }
@@ -339,27 +503,29 @@ __device__ void role_potrf(const BaParams &p, const SolverBufs &sb, int kk, doub
 }
 
 // Rows [q*SLAB, (q+1)*SLAB) of L[i,kk] = A[i,kk] * inv(L_kk)^T, then b_i -= L[i,kk] y_kk there.
+// Thread (ty, tx) computes outputs (ty + 16u, tx + 16v): a warp then reads 16 consecutive rows of
+// the 65-double-pitch tile per operand, which is bank-conflict free for 8-byte words.
 template <int SLAB>
-__device__ void role_trsm(const BaParams &p, const SolverBufs &sb, int kk, int a, int q, double *s_buf) {
+__device__ void role_trsm(const BaParams &p, const SolverBufs &sb, int kk, int a, int q, int atomic_from,
+                          double *s_buf) {
   TilePtr X = reinterpret_cast<TilePtr>(s_buf);
   TilePtr A = reinterpret_cast<TilePtr>(s_buf + TILE_STRIDE);
   __shared__ double s_y[GBA_NB];
-  constexpr int RPT = SLAB / 16;  // rows per thread (thread = RPT x 4 outputs)
-  const int i = sb.colrows[kk * p.nT + a], tid = threadIdx.x, rb = q * SLAB;
+  constexpr int RPT = SLAB / 16;  // rows per thread
+  const int i = sb.colrows[kk * p.nT + a], tid = threadIdx.x, rb = q * SLAB, ty = tid >> 4, tx = tid & 15;
   double *T = p.sys + (size_t)p.tslot[i * p.nT + kk] * GBA_NB2 + rb * GBA_NB;
-  const double *XI = sb.invL + (size_t)kk * GBA_NB2;
-  for (int e = tid; e < GBA_NB2; e += 256) X[e >> 6][e & 63] = __ldcg(XI + e);
-  for (int e = tid; e < SLAB * GBA_NB; e += 256) A[e >> 6][e & 63] = __ldcg(T + e);
+  load_rows<GBA_NB>(X, sb.invL + (size_t)kk * GBA_NB2);
+  load_rows<SLAB>(A, T);
   if (tid < GBA_NB) s_y[tid] = __ldcg(rhs_ptr(p) + kk * GBA_NB + tid);
   __syncthreads();
-  const int r0 = (tid >> 4) * RPT, c0 = (tid & 15) * 4;
   double acc[RPT][4] = {};
+#pragma unroll 8
   for (int m = 0; m < GBA_NB; m++) {
     double av[RPT], xv[4];
 #pragma unroll
-    for (int u = 0; u < RPT; u++) av[u] = A[r0 + u][m];
+    for (int u = 0; u < RPT; u++) av[u] = A[ty + 16 * u][m];
 #pragma unroll
-    for (int v = 0; v < 4; v++) xv[v] = X[c0 + v][m];
+    for (int v = 0; v < 4; v++) xv[v] = X[tx + 16 * v][m];
 #pragma unroll
     for (int u = 0; u < RPT; u++)
 #pragma unroll
@@ -370,8 +536,8 @@ __device__ void role_trsm(const BaParams &p, const SolverBufs &sb, int kk, int a
   for (int u = 0; u < RPT; u++)
 #pragma unroll
     for (int v = 0; v < 4; v++) {
-      T[(r0 + u) * GBA_NB + c0 + v] = acc[u][v];
-      A[r0 + u][c0 + v] = acc[u][v];
+      T[(ty + 16 * u) * GBA_NB + tx + 16 * v] = acc[u][v];
+      A[ty + 16 * u][tx + 16 * v] = acc[u][v];
     }
   __syncthreads();
   if (tid < SLAB * 4) {
@@ -381,31 +547,45 @@ __device__ void role_trsm(const BaParams &p, const SolverBufs &sb, int kk, int a
     for (int m = part * 16; m < part * 16 + 16; m++) s += A[row][m] * s_y[m];
     s += __shfl_xor_sync(0xffffffffu, s, 1);
     s += __shfl_xor_sync(0xffffffffu, s, 2);
-    if (part == 0) rhs_ptr(p)[i * GBA_NB + rb + row] -= s;
+    if (part == 0) {
+      // closure rows are updated by several band segments at once
+      if (i >= atomic_from) atomicAdd(&rhs_ptr(p)[i * GBA_NB + rb + row], -s);
+      else rhs_ptr(p)[i * GBA_NB + rb + row] -= s;
+    }
   }
 }
 
 // Rows [q*SLAB, (q+1)*SLAB) of A[i,j] -= L[i,kk] * L[j,kk]^T
 template <int SLAB>
-__device__ void role_syrk(const BaParams &p, const SolverBufs &sb, int kk, int a, int b, int q, double *s_buf) {
+__device__ void role_syrk(const BaParams &p, const SolverBufs &sb, int kk, int a, int b, int q, int atomic_from,
+                          double *s_buf) {
   TilePtr B = reinterpret_cast<TilePtr>(s_buf);
   TilePtr A = reinterpret_cast<TilePtr>(s_buf + TILE_STRIDE);
   constexpr int RPT = SLAB / 16;
   const int i = sb.colrows[kk * p.nT + a], j = sb.colrows[kk * p.nT + b], tid = threadIdx.x, rb = q * SLAB;
+  const int ty = tid >> 4, tx = tid & 15;
   const double *Li = p.sys + (size_t)p.tslot[i * p.nT + kk] * GBA_NB2 + rb * GBA_NB;
   const double *Lj = p.sys + (size_t)p.tslot[j * p.nT + kk] * GBA_NB2;
   double *T = p.sys + (size_t)p.tslot[i * p.nT + j] * GBA_NB2 + rb * GBA_NB;
-  for (int e = tid; e < GBA_NB2; e += 256) B[e >> 6][e & 63] = __ldcg(Lj + e);
-  for (int e = tid; e < SLAB * GBA_NB; e += 256) A[e >> 6][e & 63] = __ldcg(Li + e);
+  load_rows<GBA_NB>(B, Lj);
+  load_rows<SLAB>(A, Li);
+  // the target values are fetched now so that their latency hides behind the product; tiles of
+  // the closure block are shared by concurrently factorised band segments -> atomic adds instead
+  const bool shared_tile = j >= atomic_from;
+  double t[RPT][4];
+#pragma unroll
+  for (int u = 0; u < RPT; u++)
+#pragma unroll
+    for (int v = 0; v < 4; v++) t[u][v] = shared_tile ? 0.0 : __ldcg(T + (ty + 16 * u) * GBA_NB + tx + 16 * v);
   __syncthreads();
-  const int r0 = (tid >> 4) * RPT, c0 = (tid & 15) * 4;
   double acc[RPT][4] = {};
+#pragma unroll 8
   for (int m = 0; m < GBA_NB; m++) {
     double x[RPT], y[4];
 #pragma unroll
-    for (int u = 0; u < RPT; u++) x[u] = A[r0 + u][m];
+    for (int u = 0; u < RPT; u++) x[u] = A[ty + 16 * u][m];
 #pragma unroll
-    for (int v = 0; v < 4; v++) y[v] = B[c0 + v][m];
+    for (int v = 0; v < 4; v++) y[v] = B[tx + 16 * v][m];
 #pragma unroll
     for (int u = 0; u < RPT; u++)
 #pragma unroll
@@ -414,7 +594,10 @@ __device__ void role_syrk(const BaParams &p, const SolverBufs &sb, int kk, int a
 #pragma unroll
   for (int u = 0; u < RPT; u++)
 #pragma unroll
-    for (int v = 0; v < 4; v++) T[(r0 + u) * GBA_NB + c0 + v] -= acc[u][v];
+    for (int v = 0; v < 4; v++) {
+      if (shared_tile) atomicAdd(&T[(ty + 16 * u) * GBA_NB + tx + 16 * v], -acc[u][v]);
+      else T[(ty + 16 * u) * GBA_NB + tx + 16 * v] = t[u][v] - acc[u][v];
+    }
 }
 
 __device__ __forceinline__ unsigned ld_acquire(const unsigned *p) {
@@ -434,12 +617,14 @@ __device__ __forceinline__ unsigned ld_acquire(const unsigned *p) {
 // Roles are handed out by an atomic ticket taken when a CTA starts running, not by blockIdx: a
 // CTA that waits therefore only ever waits for CTAs that started before it, so the kernel cannot
 // deadlock however the grid is dispatched and however much larger than the GPU it is.
+// blockIdx.y selects the band segment: tile column kk = kk0 + y * kk_stride (independent columns).
 template <int SLAB>
-__global__ void __launch_bounds__(256) k_panel(BaParams p, SolverBufs sb, int kk, int max_col) {
+__global__ void __launch_bounds__(256) k_panel(BaParams p, SolverBufs sb, int kk0, int kk_stride, int max_col,
+                                               int atomic_from) {
   extern __shared__ double s_buf[];
   constexpr int SPLIT = GBA_NB / SLAB;
   __shared__ int s_flag, s_bid;
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, kk = kk0 + blockIdx.y * kk_stride;
   if (tid == 0) s_bid = (int)atomicAdd(&sb.ticket[kk], 1u);
   __syncthreads();
   const int b = s_bid;
@@ -459,7 +644,7 @@ __global__ void __launch_bounds__(256) k_panel(BaParams p, SolverBufs sb, int kk
     if (tid == 0)
       while (ld_acquire(&sb.flagA[kk]) == 0u) __nanosleep(20);
     __syncthreads();
-    if (!__ldcg(sb.fail)) role_trsm<SLAB>(p, sb, kk, a, q, s_buf);
+    if (!__ldcg(sb.fail)) role_trsm<SLAB>(p, sb, kk, a, q, atomic_from, s_buf);
     __threadfence();
     __syncthreads();
     if (tid == 0) atomicAdd(&sb.cntB[kk], 1u);
@@ -476,7 +661,7 @@ __global__ void __launch_bounds__(256) k_panel(BaParams p, SolverBufs sb, int kk
     while (ld_acquire(&sb.cntB[kk]) < (unsigned)(SPLIT * cnt)) __nanosleep(20);
   __syncthreads();
   const bool failed = __ldcg(sb.fail);
-  if (!failed) role_syrk<SLAB>(p, sb, kk, a, rem, q, s_buf);
+  if (!failed) role_syrk<SLAB>(p, sb, kk, a, rem, q, atomic_from, s_buf);
   // look-ahead: tile (kk+1, kk+1) is complete once its SPLIT slabs are updated
   if (pair == 0 && sb.colrows[kk * p.nT] == kk + 1) {
     __threadfence();
@@ -501,7 +686,7 @@ __global__ void __launch_bounds__(256) k_potrf_diag(BaParams p, SolverBufs sb, i
 __global__ void __launch_bounds__(256) k_trsm(BaParams p, SolverBufs sb, int kk) {
   extern __shared__ double s_buf[];
   if (*sb.fail || (int)blockIdx.x >= sb.colcnt[kk]) return;
-  role_trsm<GBA_NB>(p, sb, kk, blockIdx.x, 0, s_buf);
+  role_trsm<GBA_NB>(p, sb, kk, blockIdx.x, 0, 1 << 30, s_buf);
 }
 __global__ void __launch_bounds__(256) k_syrk(BaParams p, SolverBufs sb, int kk) {
   extern __shared__ double s_buf[];
@@ -512,29 +697,33 @@ __global__ void __launch_bounds__(256) k_syrk(BaParams p, SolverBufs sb, int kk)
     a++;
   }
   if (a >= sb.colcnt[kk]) return;
-  role_syrk<GBA_NB>(p, sb, kk, a, rem, 0, s_buf);
+  role_syrk<GBA_NB>(p, sb, kk, a, rem, 0, 1 << 30, s_buf);
 }
 
 // ---------------------------------------------------------------------------------------------
 // Backward substitution, one launch per tile row i (from the last to the first): CTA 0 computes
 // x_i = inv(L_i)^T y_i, the others push y_k -= L[i,k]^T x_i to the active tiles of row i.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_back_step(BaParams p, SolverBufs sb, int i) {
-  __shared__ double s_x[GBA_NB];
-  const int b = blockIdx.x, tid = threadIdx.x, col = tid >> 2, part = tid & 3;
+__global__ void __launch_bounds__(256) k_back_step(BaParams p, SolverBufs sb, int i0, int i_stride) {
+  __shared__ double s_x[GBA_NB], s_part[4][GBA_NB];
+  // thread = (column of the tile, quarter of its rows): lanes run over columns -> coalesced
+  const int b = blockIdx.x, tid = threadIdx.x, col = tid & 63, part = tid >> 6;
+  const int i = i0 + blockIdx.y * i_stride;  // blockIdx.y = band segment
   double *rhs = rhs_ptr(p);
   if (__ldcg(sb.fail)) return;
   if (b == 0) {
+    const double *XI = sb.invL + (size_t)i * GBA_NB2;
+    double l[16];
+#pragma unroll
+    for (int m = 0; m < 16; m++) l[m] = __ldcg(XI + (part * 16 + m) * GBA_NB + col);
     if (tid < GBA_NB) s_x[tid] = __ldcg(rhs + i * GBA_NB + tid);
     __syncthreads();
-    const double *XI = sb.invL + (size_t)i * GBA_NB2;
     double s = 0.0;
-#pragma unroll 4
-    for (int m = part * 16; m < part * 16 + 16; m++) s += __ldcg(XI + m * GBA_NB + col) * s_x[m];
-    s += __shfl_xor_sync(0xffffffffu, s, 1);
-    s += __shfl_xor_sync(0xffffffffu, s, 2);
+#pragma unroll
+    for (int m = 0; m < 16; m++) s += l[m] * s_x[part * 16 + m];
+    s_part[part][col] = s;
     __syncthreads();
-    if (part == 0) rhs[i * GBA_NB + col] = s;
+    if (tid < GBA_NB) rhs[i * GBA_NB + tid] = s_part[0][tid] + s_part[1][tid] + s_part[2][tid] + s_part[3][tid];
     __threadfence();
     __syncthreads();
     if (tid == 0) atomicExch(&sb.flagX[i], 1u);
@@ -555,9 +744,9 @@ __global__ void __launch_bounds__(256) k_back_step(BaParams p, SolverBufs sb, in
   double s = 0.0;
 #pragma unroll
   for (int m = 0; m < 16; m++) s += l[m] * s_x[part * 16 + m];
-  s += __shfl_xor_sync(0xffffffffu, s, 1);
-  s += __shfl_xor_sync(0xffffffffu, s, 2);
-  if (part == 0) rhs[k * GBA_NB + col] -= s;
+  s_part[part][col] = s;
+  __syncthreads();
+  if (tid < GBA_NB) rhs[k * GBA_NB + tid] -= s_part[0][tid] + s_part[1][tid] + s_part[2][tid] + s_part[3][tid];
 }
 
 // dx = (float) x in the caller's pose order, or zero when the factorisation failed
