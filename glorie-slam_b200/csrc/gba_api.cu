@@ -29,6 +29,7 @@ struct gba_ctx {
   size_t gram_cap, sys_cap;
   double *sys;
   int *tslot, *perm, *iperm, *dspo_bad;
+  int *h_cnt;  // pinned: colcnt[nT_max] | rowcnt[nT_max], read back with the status
   int pos_cap;
   SolverBufs sb;
   unsigned int *flags;  // flagA | cntB | cntD | flagX | ticket, nT_max each
@@ -110,6 +111,7 @@ extern "C" void gba_destroy(gba_ctx *c) {
   for (void *q : ptrs)
     if (q) cudaFree(q);
   if (c->st_h) cudaFreeHost(c->st_h);
+  if (c->h_cnt) cudaFreeHost(c->h_cnt);
   if (c->ev_pool) {
     for (cudaEvent_t e : *c->ev_pool) cudaEventDestroy(e);
     delete c->ev_pool;
@@ -125,7 +127,7 @@ extern "C" int gba_create(gba_ctx **out, int device, int max_frames, int max_edg
   *out = nullptr;
   if (max_frames < 2 || max_edges < 0 || ht < 1 || wd < 1)
     return fail_msg(c, GBA_EINVAL, "bad sizes: frames %d edges %d grid %dx%d", max_frames, max_edges, ht, wd);
-  if ((ht * wd) % 4 != 0) return fail_msg(c, GBA_EINVAL, "ht*wd must be a multiple of 4 (got %d)", ht * wd);
+  if (wd % 4 != 0) return fail_msg(c, GBA_EINVAL, "wd must be a multiple of 4 (got %d)", wd);
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || device < 0 || device >= ndev) {
     cudaGetLastError();
@@ -173,6 +175,7 @@ extern "C" int gba_create(gba_ctx **out, int device, int max_frames, int max_edg
   CKC(dalloc(&c->goff, N));
   CKC(dalloc(&c->st_d, 1));
   CKC(cudaMallocHost((void **)&c->st_h, sizeof(Status)));
+  CKC(cudaMallocHost((void **)&c->h_cnt, 2 * nT * sizeof(int)));
   CKC(dalloc(&c->geo, E));
   CKC(dalloc(&c->hpart, E * c->hpart_chunks * 32));
   CKC(dalloc(&c->edge_hv, E * 32));
@@ -247,6 +250,10 @@ static int build_index(gba_ctx *c, const int64_t *kx_global, int n_kx, bool want
   }
   stage_end(c);
   CK(cudaMemcpyAsync(c->st_h, c->st_d, sizeof(Status), cudaMemcpyDeviceToHost, s));
+  if (want_tiles) {
+    CK(cudaMemcpyAsync(c->h_cnt, c->sb.colcnt, (size_t)c->nT_max * sizeof(int), cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(c->h_cnt + c->nT_max, c->sb.rowcnt, (size_t)c->nT_max * sizeof(int), cudaMemcpyDeviceToHost, s));
+  }
   CK(cudaStreamSynchronize(s));
   const Status &st = *c->st_h;
   if (st.err & 1) return fail_msg(c, GBA_EINVAL, "ii/jj (or kx) contain keyframe indices outside [0,%d)", p.N);
@@ -301,7 +308,7 @@ extern "C" int gba_ba_begin(gba_ctx *c, float *poses, float *disps, const float 
       return fail_msg(c, GBA_ECAPACITY, "Schur Gram buffers need %llu floats (capacity %zu); max out-degree %d",
                       st.gram_floats, c->gram_cap, st.max_deg);
     const int nb = (6 * st.max_deg + 1 + 7) / 8, RS = ((2 * nb + 7) & ~7) * 4;
-    if ((size_t)GRAM_T * RS * sizeof(float) > (size_t)kGramSmemMax)
+    if ((size_t)2 * GRAM_T * RS * sizeof(float) > (size_t)kGramSmemMax)
       return fail_msg(c, GBA_ECAPACITY, "out-degree %d too large for the shared-memory Gram tile", st.max_deg);
   }
   // launch shape of the streaming passes: largest CTA footprint that still gives >= 2 CTAs per SM
@@ -335,9 +342,15 @@ extern "C" int gba_ba_build(gba_ctx *c) {
   stage_begin(c, GBA_STAGE_LINEARIZE);  // brackets k_linearize alone (roofline kernel)
   if (st.K > 0) {
     dim3 grid(p.nchunk, st.K);
-    if (c->variant == 0) k_linearize<256, 2><<<grid, 256, 0, s>>>(p);
-    else if (c->variant == 1) k_linearize<128, 2><<<grid, 128, 0, s>>>(p);
-    else k_linearize<128, 1><<<grid, 128, 0, s>>>(p);
+    if (p.mode == 0) {
+      if (c->variant == 0) k_linearize<256, 2, 0><<<grid, 256, 0, s>>>(p);
+      else if (c->variant == 1) k_linearize<128, 2, 0><<<grid, 128, 0, s>>>(p);
+      else k_linearize<128, 1, 0><<<grid, 128, 0, s>>>(p);
+    } else {
+      if (c->variant == 0) k_linearize<256, 2, 1><<<grid, 256, 0, s>>>(p);
+      else if (c->variant == 1) k_linearize<128, 2, 1><<<grid, 128, 0, s>>>(p);
+      else k_linearize<128, 1, 1><<<grid, 128, 0, s>>>(p);
+    }
     LAUNCH_CHECK("k_linearize");
   }
   stage_end(c);
@@ -358,7 +371,7 @@ extern "C" int gba_ba_build(gba_ctx *c) {
     stage_begin(c, GBA_STAGE_GRAM);
     if (c->gsplit > 1) CK(cudaMemsetAsync(c->gram, 0, (size_t)st.gram_floats * sizeof(float), s));
     const int nb = (6 * st.max_deg + 1 + 7) / 8, RS = ((2 * nb + 7) & ~7) * 4;
-    k_gram<<<dim3(c->gsplit, st.K), GRAM_NT, (size_t)GRAM_T * RS * sizeof(float), s>>>(p);
+    k_gram<<<dim3(c->gsplit, st.K), GRAM_NT, (size_t)2 * GRAM_T * RS * sizeof(float), s>>>(p);
     LAUNCH_CHECK("k_gram");
     stage_end(c);
     stage_begin(c, GBA_STAGE_SCHUR);
@@ -393,10 +406,13 @@ extern "C" int gba_ba_solve(gba_ctx *c) {
     // launch (grid.y = segment); the closure block follows column by column.  16-row slabs
     // (4 CTAs per tile) spread the fp64 work over more SMs while the structure is sparse.
     const int nT = st.n_tiles, nseg = st.n_seg, segT = st.seg_tiles, band = nseg > 1 ? nseg * segT : 0;
-    const int mc = st.max_col, pairs = mc * (mc + 1) / 2;
-    const bool split = (1 + mc + pairs) <= 4 * c->sm_count;
+    const int *colcnt = c->h_cnt, *rowcnt = c->h_cnt + c->nT_max;
     const int atomic_from = nseg > 1 ? band : (1 << 30);
     auto panel = [&](int kk0, int stride, int ny, bool last) -> int {
+      int mc = 0;  // the launch is sized by the fullest of its tile columns (counts known on the host)
+      for (int y = 0; y < ny; y++) mc = std::max(mc, colcnt[kk0 + y * stride]);
+      const int pairs = mc * (mc + 1) / 2;
+      const bool split = (1 + mc + pairs) * ny <= 4 * c->sm_count;
       if (getenv("GBA_UNFUSED") && ny == 1) {  // diagnostic: the three phases as separate launches
         k_potrf_diag<<<1, 256, kSolverSmem, s>>>(p, c->sb, kk0);
         LAUNCH_CHECK("k_potrf_diag");
@@ -428,11 +444,13 @@ extern "C" int gba_ba_solve(gba_ctx *c) {
     stage_end(c);
     stage_begin(c, GBA_STAGE_SOLVE);
     for (int i = nT - 1; i >= band; i--) {
-      k_back_step<<<1 + (i > 0 ? st.max_row : 0), 256, 0, s>>>(p, c->sb, i, 0);
+      k_back_step<<<1 + rowcnt[i], 256, 0, s>>>(p, c->sb, i, 0);
       LAUNCH_CHECK("k_back_step");
     }
     for (int t = (nseg > 1 ? segT : 0) - 1; t >= 0; t--) {
-      k_back_step<<<dim3(1 + st.max_row, nseg), 256, 0, s>>>(p, c->sb, t, segT);
+      int mr = 0;
+      for (int y = 0; y < nseg; y++) mr = std::max(mr, rowcnt[t + y * segT]);
+      k_back_step<<<dim3(1 + mr, nseg), 256, 0, s>>>(p, c->sb, t, segT);
       LAUNCH_CHECK("k_back_step");
     }
   }
@@ -444,9 +462,15 @@ extern "C" int gba_ba_solve(gba_ctx *c) {
   if (!p.motion_only && st.K > 0) {
     stage_begin(c, GBA_STAGE_BACKSUB);
     dim3 grid(p.nchunk, st.K);
-    if (c->variant == 0) k_backsub<256, 2><<<grid, 256, 0, s>>>(p);
-    else if (c->variant == 1) k_backsub<128, 2><<<grid, 128, 0, s>>>(p);
-    else k_backsub<128, 1><<<grid, 128, 0, s>>>(p);
+    if (p.mode == 0) {
+      if (c->variant == 0) k_backsub<256, 2, 0><<<grid, 256, 0, s>>>(p);
+      else if (c->variant == 1) k_backsub<128, 2, 0><<<grid, 128, 0, s>>>(p);
+      else k_backsub<128, 1, 0><<<grid, 128, 0, s>>>(p);
+    } else {
+      if (c->variant == 0) k_backsub<256, 2, 1><<<grid, 256, 0, s>>>(p);
+      else if (c->variant == 1) k_backsub<128, 2, 1><<<grid, 128, 0, s>>>(p);
+      else k_backsub<128, 1, 1><<<grid, 128, 0, s>>>(p);
+    }
     LAUNCH_CHECK("k_backsub");
     stage_end(c);
   }

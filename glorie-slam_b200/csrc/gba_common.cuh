@@ -158,6 +158,65 @@ __device__ __forceinline__ void pix_linearize(const float *__restrict__ R, const
   o.jzv = fyd * t[1] - fyd2 * Y * t[2];
 }
 
+// ---------------------------------------------------------------------------------------------
+// Lean form of the same linearisation for the hot kernels.  The focal lengths are folded into the
+// weights (wu' = 0.001 fx^2 weight_u, wv' likewise) and the residuals (ru' = ru / fx), so that the
+// Jacobian rows become  ju' = (e, 0, -a e, -a b, 1 + a^2, -b),  jv' = (0, e, -b e, -(1 + b^2), a b, a)
+// with a = X/Z, b = Y/Z, e = z/Z, and  jz' = ((tx - tz a)/Z, (ty - tz b)/Z).  Every product of the
+// normal equations keeps its value:  w J J^T = w' j' j'^T,  w r J = w' r' j',  w Jz J = w' jz' j'.
+// ---------------------------------------------------------------------------------------------
+struct PixConst {  // per launch
+  float ifx, ify, cxf, cyf, kwu, kwv;
+};
+__device__ __forceinline__ PixConst make_pix_const(const float *intr) {
+  PixConst k;
+  k.ifx = 1.0f / intr[0];
+  k.ify = 1.0f / intr[1];
+  k.cxf = intr[2] * k.ifx;
+  k.cyf = intr[3] * k.ify;
+  k.kwu = 0.001f * intr[0] * intr[0];
+  k.kwv = 0.001f * intr[1] * intr[1];
+  return k;
+}
+struct PixHat {
+  float ru, rv, wu, wv, jzu, jzv;  // residuals / fx, fy; folded weights; jz'
+  float e, nae, nab, opa, nb;      // ju' = (e, 0, nae, nab, opa, nb)
+  float nbe, nopb, ab, a;          // jv' = (0, e, nbe, nopb, ab, a)
+};
+template <int MODE>
+__device__ __forceinline__ void pix_hat(const float *__restrict__ R, const float *__restrict__ t, const PixConst &k,
+                                        float x0, float y0, float z, float tu, float tv, float wgu, float wgv,
+                                        PixHat &o) {
+  const float X = fmaf(R[0], x0, fmaf(R[1], y0, fmaf(t[0], z, R[2])));
+  const float Y = fmaf(R[3], x0, fmaf(R[4], y0, fmaf(t[1], z, R[5])));
+  const float Z = fmaf(R[6], x0, fmaf(R[7], y0, fmaf(t[2], z, R[8])));
+  bool invalid;
+  float d;
+  if (MODE == 0) {  // droid_kernels.cu:26,302-306
+    invalid = Z < 0.25f;
+    d = invalid ? 0.0f : __fdividef(1.0f, Z);
+  } else {  // projective_ops.py:44,112
+    invalid = !(Z > 0.2f);
+    d = (Z < 0.1f) ? 1.0f : __fdividef(1.0f, Z);
+  }
+  const float a = X * d, b = Y * d, e = z * d;
+  o.wu = invalid ? 0.0f : k.kwu * wgu;
+  o.wv = invalid ? 0.0f : k.kwv * wgv;
+  o.ru = fmaf(tu, k.ifx, -k.cxf) - a;
+  o.rv = fmaf(tv, k.ify, -k.cyf) - b;
+  o.e = e;
+  o.a = a;
+  o.nb = -b;
+  o.ab = a * b;
+  o.nab = -o.ab;
+  o.nae = -(a * e);
+  o.nbe = -(b * e);
+  o.opa = fmaf(a, a, 1.0f);
+  o.nopb = -fmaf(b, b, 1.0f);
+  o.jzu = d * fmaf(-t[2], a, t[0]);
+  o.jzv = d * fmaf(-t[2], b, t[1]);
+}
+
 // Sum NV (<= 32) per-lane values across the warp so that lane l ends up holding the total of
 // v[l]: 31 shuffles instead of 5 per value (butterfly that halves the live values per stage).
 __device__ __forceinline__ float warp_transpose_reduce32(float (&v)[32], int lane) {

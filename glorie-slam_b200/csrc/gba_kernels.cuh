@@ -253,8 +253,8 @@ __global__ void k_edge_geo(BaParams p) {
 // --------------------------------------------------------------------------------------------
 #define LIN_EB 8  // edges per shared-memory batch
 
-template <int NT, int NV>
-__global__ void __launch_bounds__(NT) k_linearize(BaParams p) {
+template <int NT, int NV, int MODE>
+__global__ void __launch_bounds__(NT, (NT >= 256) ? 2 : 3) k_linearize(BaParams p) {
   constexpr int NW = NT / 32;
   __shared__ EdgeGeo s_geo[LIN_EB];
   __shared__ int s_eid[LIN_EB];
@@ -267,26 +267,25 @@ __global__ void __launch_bounds__(NT) k_linearize(BaParams p) {
   const int frame = p.kx[k];
   const int HW = p.HW;
   const float fx = p.intr[0], fy = p.intr[1], cx = p.intr[2], cy = p.intr[3];
-  const float ifx = 1.0f / fx, ify = 1.0f / fy;
+  const PixConst pk = make_pix_const(p.intr);
 
+  // wd is a multiple of 4 (checked in gba_create): the 4 pixels of a group share one image row
   int px[NV];
-  float x0[NV][4], y0[NV][4], z[NV][4], cacc[NV][4], wacc[NV][4];
+  float x0[NV], y0[NV], z[NV][4], cacc[NV][4], wacc[NV][4];
 #pragma unroll
   for (int g = 0; g < NV; g++) {
     px[g] = (chunk * NV + g) * (NT * 4) + tid * 4;
     float4 zz = make_float4(0.f, 0.f, 0.f, 0.f);
     if (px[g] < HW) zz = *reinterpret_cast<const float4 *>(p.disps + (size_t)frame * HW + px[g]);
     z[g][0] = zz.x; z[g][1] = zz.y; z[g][2] = zz.z; z[g][3] = zz.w;
+    x0[g] = ((float)(px[g] % p.wd) - cx) / fx;  // droid_kernels.cu:290-291
+    y0[g] = ((float)(px[g] / p.wd) - cy) / fy;
 #pragma unroll
     for (int i = 0; i < 4; i++) {
-      const int q = px[g] + i;
-      x0[g][i] = ((float)(q % p.wd) - cx) / fx;  // droid_kernels.cu:290-291
-      y0[g][i] = ((float)(q / p.wd) - cy) / fy;
       cacc[g][i] = 0.f;
       wacc[g][i] = 0.f;
     }
   }
-  (void)ifx; (void)ify;
 
   const int e0 = p.eptr[k], e1 = p.eptr[k + 1];
   for (int eb = e0; eb < e1; eb += LIN_EB) {
@@ -324,43 +323,43 @@ __global__ void __launch_bounds__(NT) k_linearize(BaParams p) {
         const float wua[4] = {wu[g].x, wu[g].y, wu[g].z, wu[g].w}, wva[4] = {wv[g].x, wv[g].y, wv[g].z, wv[g].w};
 #pragma unroll
         for (int i = 0; i < 4; i++) {
-          PixLin L;
-          pix_linearize(R, t, fx, fy, cx, cy, p.mode, x0[g][i], y0[g][i], z[g][i], tua[i], tva[i], wua[i], wva[i],
-                        L);
+          PixHat L;
+          pix_hat<MODE>(R, t, pk, fmaf((float)i, pk.ifx, x0[g]), y0[g], z[g][i], tua[i], tva[i], wua[i], wva[i], L);
           // depth diagonal keeps the un-zeroed weight even for stereo pairs (droid_kernels.cu:320-323)
-          cacc[g][i] += L.wu * L.jzu * L.jzu + L.wv * L.jzv * L.jzv;
-          wacc[g][i] += L.wu * L.ru * L.jzu + L.wv * L.rv * L.jzv;
-          const float wu_ = stereo ? 0.f : L.wu, wv_ = stereo ? 0.f : L.wv;
-          const float a0 = wu_ * L.ju0, a2 = wu_ * L.ju2, a3 = wu_ * L.ju3, a4 = wu_ * L.ju4, a5 = wu_ * L.ju5;
-          const float b1 = wv_ * L.jv1, b2 = wv_ * L.jv2, b3 = wv_ * L.jv3, b4 = wv_ * L.jv4, b5 = wv_ * L.jv5;
+          const float qu = L.wu * L.jzu, qv = L.wv * L.jzv;
+          cacc[g][i] = fmaf(qv, L.jzv, fmaf(qu, L.jzu, cacc[g][i]));
+          wacc[g][i] = fmaf(qv, L.rv, fmaf(qu, L.ru, wacc[g][i]));
+          if (stereo) continue;  // block-uniform: self edges carry no pose terms (droid_kernels.cu:323,356)
+          const float a0 = L.wu * L.e, a2 = L.wu * L.nae, a3 = L.wu * L.nab, a4 = L.wu * L.opa, a5 = L.wu * L.nb;
+          const float b1 = L.wv * L.e, b2 = L.wv * L.nbe, b3 = L.wv * L.nopb, b4 = L.wv * L.ab, b5 = L.wv * L.a;
           // upper triangle of H_jj, row major: (0,0..5) (1,1..5) (2,2..5) (3,3..5) (4,4..5) (5,5)
-          acc[0] += a0 * L.ju0;
-          acc[2] += a0 * L.ju2;
-          acc[3] += a0 * L.ju3;
-          acc[4] += a0 * L.ju4;
-          acc[5] += a0 * L.ju5;
-          acc[6] += b1 * L.jv1;
-          acc[7] += b1 * L.jv2;
-          acc[8] += b1 * L.jv3;
-          acc[9] += b1 * L.jv4;
-          acc[10] += b1 * L.jv5;
-          acc[11] += a2 * L.ju2 + b2 * L.jv2;
-          acc[12] += a2 * L.ju3 + b2 * L.jv3;
-          acc[13] += a2 * L.ju4 + b2 * L.jv4;
-          acc[14] += a2 * L.ju5 + b2 * L.jv5;
-          acc[15] += a3 * L.ju3 + b3 * L.jv3;
-          acc[16] += a3 * L.ju4 + b3 * L.jv4;
-          acc[17] += a3 * L.ju5 + b3 * L.jv5;
-          acc[18] += a4 * L.ju4 + b4 * L.jv4;
-          acc[19] += a4 * L.ju5 + b4 * L.jv5;
-          acc[20] += a5 * L.ju5 + b5 * L.jv5;
-          // v_j
-          acc[21] += a0 * L.ru;
-          acc[22] += b1 * L.rv;
-          acc[23] += a2 * L.ru + b2 * L.rv;
-          acc[24] += a3 * L.ru + b3 * L.rv;
-          acc[25] += a4 * L.ru + b4 * L.rv;
-          acc[26] += a5 * L.ru + b5 * L.rv;
+          acc[0] = fmaf(a0, L.e, acc[0]);
+          acc[2] = fmaf(a0, L.nae, acc[2]);
+          acc[3] = fmaf(a0, L.nab, acc[3]);
+          acc[4] = fmaf(a0, L.opa, acc[4]);
+          acc[5] = fmaf(a0, L.nb, acc[5]);
+          acc[6] = fmaf(b1, L.e, acc[6]);
+          acc[7] = fmaf(b1, L.nbe, acc[7]);
+          acc[8] = fmaf(b1, L.nopb, acc[8]);
+          acc[9] = fmaf(b1, L.ab, acc[9]);
+          acc[10] = fmaf(b1, L.a, acc[10]);
+          acc[11] = fmaf(b2, L.nbe, fmaf(a2, L.nae, acc[11]));
+          acc[12] = fmaf(b2, L.nopb, fmaf(a2, L.nab, acc[12]));
+          acc[13] = fmaf(b2, L.ab, fmaf(a2, L.opa, acc[13]));
+          acc[14] = fmaf(b2, L.a, fmaf(a2, L.nb, acc[14]));
+          acc[15] = fmaf(b3, L.nopb, fmaf(a3, L.nab, acc[15]));
+          acc[16] = fmaf(b3, L.ab, fmaf(a3, L.opa, acc[16]));
+          acc[17] = fmaf(b3, L.a, fmaf(a3, L.nb, acc[17]));
+          acc[18] = fmaf(b4, L.ab, fmaf(a4, L.opa, acc[18]));
+          acc[19] = fmaf(b4, L.a, fmaf(a4, L.nb, acc[19]));
+          acc[20] = fmaf(b5, L.a, fmaf(a5, L.nb, acc[20]));
+          // v_j (in units of 1/fx, 1/fy folded into the weights: w r J = w' r' j')
+          acc[21] = fmaf(a0, L.ru, acc[21]);
+          acc[22] = fmaf(b1, L.rv, acc[22]);
+          acc[23] = fmaf(b2, L.rv, fmaf(a2, L.ru, acc[23]));
+          acc[24] = fmaf(b3, L.rv, fmaf(a3, L.ru, acc[24]));
+          acc[25] = fmaf(b4, L.rv, fmaf(a4, L.ru, acc[25]));
+          acc[26] = fmaf(b5, L.rv, fmaf(a5, L.ru, acc[26]));
         }
       }
       const float tot = warp_transpose_reduce32(acc, lane);
@@ -481,13 +480,21 @@ __global__ void k_edge_finish(BaParams p) {
 // --------------------------------------------------------------------------------------------
 #define GRAM_T 32   // pixels per shared-memory tile
 #define GRAM_NT 256
+#define GRAM_MAXCW 6  // at most 6 consumer warps (192 register blocks per pass), at least 2 producers
 
-__device__ __forceinline__ int gram_off(int p, int col, int nb, int RS) {
-  const int chunk = (col >> 3) + (((col >> 2) & 1) ? nb : 0);
+__device__ __forceinline__ int gram_off(int p, int col, int nbs, int RS) {
+  const int chunk = (col >> 3) + (((col >> 2) & 1) ? nbs : 0);
   return p * RS + (((chunk ^ (p & 7)) << 2) | (col & 3));
 }
+__device__ __forceinline__ void named_bar_sync(int id) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(GRAM_NT) : "memory"); }
+__device__ __forceinline__ void named_bar_arrive(int id) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(GRAM_NT) : "memory"); }
 
-__global__ void __launch_bounds__(GRAM_NT) k_gram(BaParams p) {
+// Warp-specialised: producer warps rebuild the sqrt(Q)-scaled E rows of a 32-pixel tile into one
+// of two shared-memory buffers while consumer warps accumulate the previous tile into their 8x8
+// register blocks (block-upper triangle of G = A A^T).  FULL/EMPTY named barriers (ids 1-4) hand
+// the buffers over; nobody waits at a CTA-wide barrier inside the pixel loop.  The extra column
+// G[:, 6 deg] = sum_pix E Q w is accumulated by the threads that own the diagonal blocks.
+__global__ void __launch_bounds__(GRAM_NT, 2) k_gram(BaParams p) {
   extern __shared__ float s_tile[];
   const int k = blockIdx.y;
   if (k >= p.st->K) return;
@@ -495,105 +502,141 @@ __global__ void __launch_bounds__(GRAM_NT) k_gram(BaParams p) {
   const int e0 = p.eptr[k], deg = p.eptr[k + 1] - e0;
   if (deg == 0) return;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int Rw = 6 * deg;  // column of the w row
-  const int nb = (Rw + 1 + 7) / 8, Rp = nb * 8;
-  const int RS = ((2 * nb + 7) & ~7) * 4;
+  const int Rw = 6 * deg;              // rows of E; shared-memory column Rw holds sqrt(Q) * w
+  const int nb = (Rw + 7) / 8;         // 8-row blocks of G proper
+  const int nbs = (Rw + 1 + 7) / 8;    // 8-column chunks of a shared-memory row (incl. the w column)
+  const int Rp = nbs * 8;              // pitch of G in the gram buffer (k_prep_scan uses the same)
+  const int RS = ((2 * nbs + 7) & ~7) * 4;
   const int nblk = nb * (nb + 1) / 2;
-  const int npass = (nblk + GRAM_NT - 1) / GRAM_NT;
+  const int ncw = min(GRAM_MAXCW, (nblk + 31) / 32);  // consumer warps
+  const int npw = GRAM_NT / 32 - ncw;                 // producer warps
+  const int npass = (nblk + ncw * 32 - 1) / (ncw * 32);
   const int HW = p.HW, frame = p.kx[k];
   const float fx = p.intr[0], fy = p.intr[1], cx = p.intr[2], cy = p.intr[3];
+  const PixConst pk = make_pix_const(p.intr);
   const int ntile = (HW + GRAM_T - 1) / GRAM_T;
+  const int nloc = (ntile - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // tiles of this CTA
   float *G = p.gram + p.goff[k];
-  const float4 *tile4 = reinterpret_cast<const float4 *>(s_tile);
   const int RS4 = RS >> 2;
+  const bool producer = warp >= ncw;
+
+  // padding columns of both buffers stay zero; data columns are rewritten for every tile
+  for (int i = tid; i < 2 * GRAM_T * RS; i += GRAM_NT) s_tile[i] = 0.f;
+  __syncthreads();
 
   for (int pass = 0; pass < npass; pass++) {
-    const int blk = pass * GRAM_NT + tid;
-    int bi = 0, bj = 0;
-    const bool active = blk < nblk;
-    if (active) {  // blk -> (bi <= bj), row major over the block-upper triangle
-      int rem = blk;
-      while (rem >= nb - bi) {
-        rem -= nb - bi;
-        bi++;
-      }
-      bj = bi + rem;
-    }
-    float acc[8][8];
+    if (producer) {
+      const int pw = warp - ncw;
+      for (int it = 0; it < nloc; it++) {
+        const int b = it & 1;
+        float *buf = s_tile + b * GRAM_T * RS;
+        if (it >= 2) named_bar_sync(3 + b);  // consumers are done with this buffer (tile it-2)
+        const int tt = blockIdx.x + it * gridDim.x;
+        const int pix = tt * GRAM_T + lane;
+        const bool pv = pix < HW;
+        const float zq = pv ? p.disps[(size_t)frame * HW + pix] : 1.f;
+        const float sq = pv ? sqrtf(p.Q[(size_t)k * HW + pix]) : 0.f;
+        const float x0 = ((float)(pix % p.wd) - cx) / fx, y0 = ((float)(pix / p.wd) - cy) / fy;
+        if (pw == 0) buf[gram_off(lane, Rw, nbs, RS)] = pv ? sq * p.W[(size_t)k * HW + pix] : 0.f;
+        for (int q = pw; q < deg; q += npw) {
+          const int n = p.eidx[e0 + q];
+          const EdgeGeo *g = p.geo + n;
+          float R[9], t[3];
+          {
+            const float4 g0 = __ldg(reinterpret_cast<const float4 *>(g)), g1 = __ldg(reinterpret_cast<const float4 *>(g) + 1),
+                         g2 = __ldg(reinterpret_cast<const float4 *>(g) + 2);
+            R[0] = g0.x; R[1] = g0.y; R[2] = g0.z; R[3] = g0.w;
+            R[4] = g1.x; R[5] = g1.y; R[6] = g1.z; R[7] = g1.w;
+            R[8] = g2.x; t[0] = g2.y; t[1] = g2.z; t[2] = g2.w;
+          }
+          const bool stereo = __ldg(&g->flags) & 1;
+          float e[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+          if (pv && !stereo) {
+            const float *tg = p.targets + (size_t)n * 2 * HW, *wg = p.weights + (size_t)n * 2 * HW;
+            PixHat L;
+            const float tu_ = ldg_stream(tg + pix), tv_ = ldg_stream(tg + HW + pix);
+            const float wu_ = ldg_stream(wg + pix), wv_ = ldg_stream(wg + HW + pix);
+            if (p.mode == 0) pix_hat<0>(R, t, pk, x0, y0, zq, tu_, tv_, wu_, wv_, L);
+            else pix_hat<1>(R, t, pk, x0, y0, zq, tu_, tv_, wu_, wv_, L);
+            const float su = sq * L.wu * L.jzu, sv = sq * L.wv * L.jzv;
+            e[0] = su * L.e;
+            e[1] = sv * L.e;
+            e[2] = fmaf(su, L.nae, sv * L.nbe);
+            e[3] = fmaf(su, L.nab, sv * L.nopb);
+            e[4] = fmaf(su, L.opa, sv * L.ab);
+            e[5] = fmaf(su, L.nb, sv * L.a);
+          }
 #pragma unroll
-    for (int r = 0; r < 8; r++)
-#pragma unroll
-      for (int c = 0; c < 8; c++) acc[r][c] = 0.f;
-
-    // zero the tile once (padding columns stay zero; data columns are rewritten per tile)
-    __syncthreads();
-    for (int i = tid; i < GRAM_T * RS; i += GRAM_NT) s_tile[i] = 0.f;
-
-    for (int tt = blockIdx.x; tt < ntile; tt += gridDim.x) {
-      __syncthreads();
-      // ---- phase 1: rebuild the rows of this pixel tile --------------------------------------
-      const int pix = tt * GRAM_T + lane;
-      const bool pv = pix < HW;
-      const float zq = pv ? p.disps[(size_t)frame * HW + pix] : 1.f;
-      const float sq = pv ? sqrtf(p.Q[(size_t)k * HW + pix]) : 0.f;
-      const float x0 = ((float)(pix % p.wd) - cx) / fx, y0 = ((float)(pix / p.wd) - cy) / fy;
-      if (warp == 0) s_tile[gram_off(lane, Rw, nb, RS)] = pv ? sq * p.W[(size_t)k * HW + pix] : 0.f;
-      for (int q = warp; q < deg; q += GRAM_NT / 32) {
-        const int n = p.eidx[e0 + q];
-        const EdgeGeo *g = p.geo + n;
-        float R[9], t[3];
-        {
-          const float4 g0 = __ldg(reinterpret_cast<const float4 *>(g)), g1 = __ldg(reinterpret_cast<const float4 *>(g) + 1),
-                       g2 = __ldg(reinterpret_cast<const float4 *>(g) + 2);
-          R[0] = g0.x; R[1] = g0.y; R[2] = g0.z; R[3] = g0.w;
-          R[4] = g1.x; R[5] = g1.y; R[6] = g1.z; R[7] = g1.w;
-          R[8] = g2.x; t[0] = g2.y; t[1] = g2.z; t[2] = g2.w;
+          for (int c = 0; c < 6; c++) buf[gram_off(lane, 6 * q + c, nbs, RS)] = e[c];
         }
-        const bool stereo = __ldg(&g->flags) & 1;
-        float e[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        if (pv && !stereo) {
-          const float *tg = p.targets + (size_t)n * 2 * HW, *wg = p.weights + (size_t)n * 2 * HW;
-          PixLin L;
-          pix_linearize(R, t, fx, fy, cx, cy, p.mode, x0, y0, zq, ldg_stream(tg + pix), ldg_stream(tg + HW + pix),
-                        ldg_stream(wg + pix), ldg_stream(wg + HW + pix), L);
-          const float su = sq * L.wu * L.jzu, sv = sq * L.wv * L.jzv;
-          e[0] = su * L.ju0;
-          e[1] = sv * L.jv1;
-          e[2] = su * L.ju2 + sv * L.jv2;
-          e[3] = su * L.ju3 + sv * L.jv3;
-          e[4] = su * L.ju4 + sv * L.jv4;
-          e[5] = su * L.ju5 + sv * L.jv5;
-        }
-#pragma unroll
-        for (int c = 0; c < 6; c++) s_tile[gram_off(lane, 6 * q + c, nb, RS)] = e[c];
+        __threadfence_block();
+        named_bar_arrive(1 + b);  // buffer b is full
       }
-      __syncthreads();
-      // ---- phase 2: rank-GRAM_T update of the 8x8 register block --------------------------
-      if (active) {
+    } else {
+      const int blk = pass * ncw * 32 + tid;
+      int bi = 0, bj = 0;
+      const bool active = blk < nblk;
+      if (active) {  // blk -> (bi <= bj), row major over the block-upper triangle
+        int rem = blk;
+        while (rem >= nb - bi) {
+          rem -= nb - bi;
+          bi++;
+        }
+        bj = bi + rem;
+      }
+      const bool diag = active && bi == bj;
+      float acc[8][8], accw[8];
+#pragma unroll
+      for (int r = 0; r < 8; r++) {
+        accw[r] = 0.f;
+#pragma unroll
+        for (int c = 0; c < 8; c++) acc[r][c] = 0.f;
+      }
+      const int wchunk = (Rw >> 3) + (((Rw >> 2) & 1) ? nbs : 0), wsub = Rw & 3;
+      for (int it = 0; it < nloc; it++) {
+        const int b = it & 1;
+        const float4 *tile4 = reinterpret_cast<const float4 *>(s_tile + b * GRAM_T * RS);
+        named_bar_sync(1 + b);  // wait until the producers filled buffer b
+        if (active) {
 #pragma unroll 4
-        for (int pp = 0; pp < GRAM_T; pp++) {
-          const int s = pp & 7;
-          const float4 a0 = tile4[pp * RS4 + (bi ^ s)], a1 = tile4[pp * RS4 + ((nb + bi) ^ s)];
-          const float4 b0 = tile4[pp * RS4 + (bj ^ s)], b1 = tile4[pp * RS4 + ((nb + bj) ^ s)];
-          const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-          const float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+          for (int pp = 0; pp < GRAM_T; pp++) {
+            const int s = pp & 7;
+            const float4 a0 = tile4[pp * RS4 + (bi ^ s)], a1 = tile4[pp * RS4 + ((nbs + bi) ^ s)];
+            const float4 b0 = tile4[pp * RS4 + (bj ^ s)], b1 = tile4[pp * RS4 + ((nbs + bj) ^ s)];
+            const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
-          for (int r = 0; r < 8; r++)
+            for (int r = 0; r < 8; r++)
 #pragma unroll
-            for (int c = 0; c < 8; c++) acc[r][c] = fmaf(a[r], b[c], acc[r][c]);
+              for (int c = 0; c < 8; c++) acc[r][c] = fmaf(a[r], bb[c], acc[r][c]);
+            if (diag) {
+              const float wq = reinterpret_cast<const float *>(tile4)[(pp * RS4 + (wchunk ^ s)) * 4 + wsub];
+#pragma unroll
+              for (int r = 0; r < 8; r++) accw[r] = fmaf(a[r], wq, accw[r]);
+            }
+          }
+        }
+        if (it + 2 < nloc) named_bar_arrive(3 + b);  // buffer b may be refilled
+      }
+      if (active) {
+#pragma unroll
+        for (int r = 0; r < 8; r++) {
+#pragma unroll
+          for (int c = 0; c < 8; c++) {
+            float *dst = G + (size_t)(8 * bi + r) * Rp + 8 * bj + c;
+            if (8 * bj + c == Rw) continue;  // that column belongs to the E Q w sums below
+            if (gridDim.x == 1) *dst = acc[r][c];
+            else atomicAdd(dst, acc[r][c]);
+          }
+          if (diag && 8 * bi + r < Rw) {
+            float *dst = G + (size_t)(8 * bi + r) * Rp + Rw;
+            if (gridDim.x == 1) *dst = accw[r];
+            else atomicAdd(dst, accw[r]);
+          }
         }
       }
     }
-    if (active) {
-#pragma unroll
-      for (int r = 0; r < 8; r++)
-#pragma unroll
-        for (int c = 0; c < 8; c++) {
-          float *dst = G + (size_t)(8 * bi + r) * Rp + 8 * bj + c;
-          if (gridDim.x == 1) *dst = acc[r][c];
-          else atomicAdd(dst, acc[r][c]);
-        }
-    }
+    __syncthreads();  // both roles: all tiles of this pass consumed before the buffers are reused
   }
 }
 
@@ -703,7 +746,7 @@ __global__ void k_damp(BaParams p, float lm, float ep) {
 // with one 6-vector per edge, delta_n = dx[jj] + B_n^T dx[k]; disps is updated in place.
 // Replaces EvT6x1 + accum + disp_retr (droid_kernels.cu:1095-1115,1409-1418,933-946,1428-1431).
 // --------------------------------------------------------------------------------------------
-template <int NT, int NV>
+template <int NT, int NV, int MODE>
 __global__ void __launch_bounds__(NT) k_backsub(BaParams p) {
   __shared__ EdgeGeo s_geo[LIN_EB];
   __shared__ float s_delta[LIN_EB][8];
@@ -714,26 +757,24 @@ __global__ void __launch_bounds__(NT) k_backsub(BaParams p) {
   const int chunk = blockIdx.x, tid = threadIdx.x;
   const int frame = p.kx[k], HW = p.HW;
   const float fx = p.intr[0], fy = p.intr[1], cx = p.intr[2], cy = p.intr[3];
+  const PixConst pk = make_pix_const(p.intr);
   const int pcr = frame - p.t0;
   // EvT6x1 skips pose index <= 0 (droid_kernels.cu:1105); chol.py:81 does not
-  const int lo = (p.mode == 0) ? 1 : 0;
+  const int lo = (MODE == 0) ? 1 : 0;
   const bool kvalid = (pcr >= lo && pcr < p.P);
 
   int px[NV];
-  float x0[NV][4], y0[NV][4], z[NV][4], dw[NV][4];
+  float x0[NV], y0[NV], z[NV][4], dw[NV][4];
 #pragma unroll
   for (int g = 0; g < NV; g++) {
     px[g] = (chunk * NV + g) * (NT * 4) + tid * 4;
     float4 zz = make_float4(0.f, 0.f, 0.f, 0.f);
     if (px[g] < HW) zz = *reinterpret_cast<const float4 *>(p.disps + (size_t)frame * HW + px[g]);
     z[g][0] = zz.x; z[g][1] = zz.y; z[g][2] = zz.z; z[g][3] = zz.w;
+    x0[g] = ((float)(px[g] % p.wd) - cx) / fx;
+    y0[g] = ((float)(px[g] / p.wd) - cy) / fy;
 #pragma unroll
-    for (int i = 0; i < 4; i++) {
-      const int q = px[g] + i;
-      x0[g][i] = ((float)(q % p.wd) - cx) / fx;
-      y0[g][i] = ((float)(q / p.wd) - cy) / fy;
-      dw[g][i] = 0.f;
-    }
+    for (int i = 0; i < 4; i++) dw[g][i] = 0.f;
   }
   const int e0 = p.eptr[k], e1 = p.eptr[k + 1];
   for (int eb = e0; eb < e1; eb += LIN_EB) {
@@ -781,12 +822,11 @@ __global__ void __launch_bounds__(NT) k_backsub(BaParams p) {
         const float wua[4] = {wu[g].x, wu[g].y, wu[g].z, wu[g].w}, wva[4] = {wv[g].x, wv[g].y, wv[g].z, wv[g].w};
 #pragma unroll
         for (int i = 0; i < 4; i++) {
-          PixLin L;
-          pix_linearize(R, t, fx, fy, cx, cy, p.mode, x0[g][i], y0[g][i], z[g][i], tua[i], tva[i], wua[i], wva[i],
-                        L);
-          const float du = L.ju0 * dl[0] + L.ju2 * dl[2] + L.ju3 * dl[3] + L.ju4 * dl[4] + L.ju5 * dl[5];
-          const float dv = L.jv1 * dl[1] + L.jv2 * dl[2] + L.jv3 * dl[3] + L.jv4 * dl[4] + L.jv5 * dl[5];
-          dw[g][i] += L.wu * L.jzu * du + L.wv * L.jzv * dv;
+          PixHat L;
+          pix_hat<MODE>(R, t, pk, fmaf((float)i, pk.ifx, x0[g]), y0[g], z[g][i], tua[i], tva[i], wua[i], wva[i], L);
+          const float du = fmaf(L.e, dl[0], fmaf(L.nae, dl[2], fmaf(L.nab, dl[3], fmaf(L.opa, dl[4], L.nb * dl[5]))));
+          const float dv = fmaf(L.e, dl[1], fmaf(L.nbe, dl[2], fmaf(L.nopb, dl[3], fmaf(L.ab, dl[4], L.a * dl[5]))));
+          dw[g][i] = fmaf(L.wv * L.jzv, dv, fmaf(L.wu * L.jzu, du, dw[g][i]));
         }
       }
     }
@@ -802,7 +842,7 @@ __global__ void __launch_bounds__(NT) k_backsub(BaParams p) {
     for (int i = 0; i < 4; i++) {
       dzv[i] = qa[i] * (wa[i] - dw[g][i]);
       zn[i] = z[g][i] + dzv[i];
-      if (p.mode == 1 && zn[i] < 0.f) zn[i] = 0.f;  // ba.py:119
+      if (MODE == 1 && zn[i] < 0.f) zn[i] = 0.f;  // ba.py:119
     }
     *reinterpret_cast<float4 *>(p.disps + (size_t)frame * HW + px[g]) = make_float4(zn[0], zn[1], zn[2], zn[3]);
     if (p.dz_out)
