@@ -307,7 +307,7 @@ extern "C" int gba_ba_begin(gba_ctx *c, float *poses, float *disps, const float 
     if (st.gram_floats > c->gram_cap)
       return fail_msg(c, GBA_ECAPACITY, "Schur Gram buffers need %llu floats (capacity %zu); max out-degree %d",
                       st.gram_floats, c->gram_cap, st.max_deg);
-    const int nb = (6 * st.max_deg + 1 + 7) / 8, RS = ((2 * nb + 7) & ~7) * 4;
+    const int RS = gram_pitch((6 * st.max_deg + 1 + 7) / 8);
     if ((size_t)2 * GRAM_T * RS * sizeof(float) > (size_t)kGramSmemMax)
       return fail_msg(c, GBA_ECAPACITY, "out-degree %d too large for the shared-memory Gram tile", st.max_deg);
   }
@@ -370,7 +370,7 @@ extern "C" int gba_ba_build(gba_ctx *c) {
   if (!p.motion_only && p.E > 0 && st.K > 0) {
     stage_begin(c, GBA_STAGE_GRAM);
     if (c->gsplit > 1) CK(cudaMemsetAsync(c->gram, 0, (size_t)st.gram_floats * sizeof(float), s));
-    const int nb = (6 * st.max_deg + 1 + 7) / 8, RS = ((2 * nb + 7) & ~7) * 4;
+    const int RS = gram_pitch((6 * st.max_deg + 1 + 7) / 8);
     k_gram<<<dim3(c->gsplit, st.K), GRAM_NT, (size_t)2 * GRAM_T * RS * sizeof(float), s>>>(p);
     LAUNCH_CHECK("k_gram");
     stage_end(c);

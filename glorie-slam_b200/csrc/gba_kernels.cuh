@@ -481,19 +481,33 @@ __global__ void k_edge_finish(BaParams p) {
 #define GRAM_T 32   // pixels per shared-memory tile
 #define GRAM_NT 256
 #define GRAM_MAXCW 6  // at most 6 consumer warps (192 register blocks per pass), at least 2 producers
+#define GRAM_PB 5     // edges whose inputs a producer lane keeps in flight
 
-__device__ __forceinline__ int gram_off(int p, int col, int nbs, int RS) {
-  const int chunk = (col >> 3) + (((col >> 2) & 1) ? nbs : 0);
-  return p * RS + (((chunk ^ (p & 7)) << 2) | (col & 3));
-}
+// pitch (floats) of one pixel row of the shared tile: >= 8 * nbs, a multiple of 4 (float4 reads)
+// and == 4 (mod 32) so that the 32 producer lanes of a column store spread over 8 banks
+__host__ __device__ __forceinline__ int gram_pitch(int nbs) { return ((8 * nbs + 27) / 32) * 32 + 4; }
+
 __device__ __forceinline__ void named_bar_sync(int id) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(GRAM_NT) : "memory"); }
 __device__ __forceinline__ void named_bar_arrive(int id) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(GRAM_NT) : "memory"); }
+// packed fp32x2 FMA (Blackwell FFMA2): d.lo += a.lo * b.lo, d.hi += a.hi * b.hi in ONE issue slot
+__device__ __forceinline__ unsigned long long pack2(float lo, float hi) {
+  unsigned long long r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(unsigned long long v, float &lo, float &hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ void fma2(unsigned long long &d, unsigned long long a, unsigned long long b) {
+  asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b));
+}
 
 // Warp-specialised: producer warps rebuild the sqrt(Q)-scaled E rows of a 32-pixel tile into one
 // of two shared-memory buffers while consumer warps accumulate the previous tile into their 8x8
-// register blocks (block-upper triangle of G = A A^T).  FULL/EMPTY named barriers (ids 1-4) hand
-// the buffers over; nobody waits at a CTA-wide barrier inside the pixel loop.  The extra column
-// G[:, 6 deg] = sum_pix E Q w is accumulated by the threads that own the diagonal blocks.
+// register blocks (block-upper triangle of G = A A^T) with packed FFMA2.  FULL/EMPTY named
+// barriers (ids 1-4) hand the buffers over; nobody waits at a CTA-wide barrier inside the pixel
+// loop.  Diagonal blocks are enumerated first, so only the first consumer warp(s) also carry the
+// extra column G[:, 6 deg] = sum_pix E Q w.
 __global__ void __launch_bounds__(GRAM_NT, 2) k_gram(BaParams p) {
   extern __shared__ float s_tile[];
   const int k = blockIdx.y;
@@ -506,7 +520,7 @@ __global__ void __launch_bounds__(GRAM_NT, 2) k_gram(BaParams p) {
   const int nb = (Rw + 7) / 8;         // 8-row blocks of G proper
   const int nbs = (Rw + 1 + 7) / 8;    // 8-column chunks of a shared-memory row (incl. the w column)
   const int Rp = nbs * 8;              // pitch of G in the gram buffer (k_prep_scan uses the same)
-  const int RS = ((2 * nbs + 7) & ~7) * 4;
+  const int RS = gram_pitch(nbs);
   const int nblk = nb * (nb + 1) / 2;
   const int ncw = min(GRAM_MAXCW, (nblk + 31) / 32);  // consumer warps
   const int npw = GRAM_NT / 32 - ncw;                 // producer warps
@@ -517,7 +531,6 @@ __global__ void __launch_bounds__(GRAM_NT, 2) k_gram(BaParams p) {
   const int ntile = (HW + GRAM_T - 1) / GRAM_T;
   const int nloc = (ntile - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // tiles of this CTA
   float *G = p.gram + p.goff[k];
-  const int RS4 = RS >> 2;
   const bool producer = warp >= ncw;
 
   // padding columns of both buffers stay zero; data columns are rewritten for every tile
@@ -529,7 +542,7 @@ __global__ void __launch_bounds__(GRAM_NT, 2) k_gram(BaParams p) {
       const int pw = warp - ncw;
       for (int it = 0; it < nloc; it++) {
         const int b = it & 1;
-        float *buf = s_tile + b * GRAM_T * RS;
+        float *row = s_tile + b * GRAM_T * RS + lane * RS;
         if (it >= 2) named_bar_sync(3 + b);  // consumers are done with this buffer (tile it-2)
         const int tt = blockIdx.x + it * gridDim.x;
         const int pix = tt * GRAM_T + lane;
@@ -537,83 +550,114 @@ __global__ void __launch_bounds__(GRAM_NT, 2) k_gram(BaParams p) {
         const float zq = pv ? p.disps[(size_t)frame * HW + pix] : 1.f;
         const float sq = pv ? sqrtf(p.Q[(size_t)k * HW + pix]) : 0.f;
         const float x0 = ((float)(pix % p.wd) - cx) / fx, y0 = ((float)(pix / p.wd) - cy) / fy;
-        if (pw == 0) buf[gram_off(lane, Rw, nbs, RS)] = pv ? sq * p.W[(size_t)k * HW + pix] : 0.f;
-        for (int q = pw; q < deg; q += npw) {
-          const int n = p.eidx[e0 + q];
-          const EdgeGeo *g = p.geo + n;
-          float R[9], t[3];
-          {
-            const float4 g0 = __ldg(reinterpret_cast<const float4 *>(g)), g1 = __ldg(reinterpret_cast<const float4 *>(g) + 1),
-                         g2 = __ldg(reinterpret_cast<const float4 *>(g) + 2);
-            R[0] = g0.x; R[1] = g0.y; R[2] = g0.z; R[3] = g0.w;
-            R[4] = g1.x; R[5] = g1.y; R[6] = g1.z; R[7] = g1.w;
-            R[8] = g2.x; t[0] = g2.y; t[1] = g2.z; t[2] = g2.w;
-          }
-          const bool stereo = __ldg(&g->flags) & 1;
-          float e[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-          if (pv && !stereo) {
-            const float *tg = p.targets + (size_t)n * 2 * HW, *wg = p.weights + (size_t)n * 2 * HW;
-            PixHat L;
-            const float tu_ = ldg_stream(tg + pix), tv_ = ldg_stream(tg + HW + pix);
-            const float wu_ = ldg_stream(wg + pix), wv_ = ldg_stream(wg + HW + pix);
-            if (p.mode == 0) pix_hat<0>(R, t, pk, x0, y0, zq, tu_, tv_, wu_, wv_, L);
-            else pix_hat<1>(R, t, pk, x0, y0, zq, tu_, tv_, wu_, wv_, L);
-            const float su = sq * L.wu * L.jzu, sv = sq * L.wv * L.jzv;
-            e[0] = su * L.e;
-            e[1] = sv * L.e;
-            e[2] = fmaf(su, L.nae, sv * L.nbe);
-            e[3] = fmaf(su, L.nab, sv * L.nopb);
-            e[4] = fmaf(su, L.opa, sv * L.ab);
-            e[5] = fmaf(su, L.nb, sv * L.a);
+        const float wk = (pw == 0 && pv) ? p.W[(size_t)k * HW + pix] : 0.f;
+        // the producer is latency bound: fetch target/weight of up to GRAM_PB edges before using any
+        const int nq = (deg - pw + npw - 1) / npw;  // edges of this warp: q = pw + j * npw
+        for (int j0 = 0; j0 < nq; j0 += GRAM_PB) {
+          int nn[GRAM_PB];
+          float tu_[GRAM_PB], tv_[GRAM_PB], wu_[GRAM_PB], wv_[GRAM_PB];
+#pragma unroll
+          for (int u = 0; u < GRAM_PB; u++) nn[u] = (j0 + u < nq) ? p.eidx[e0 + pw + (j0 + u) * npw] : -1;
+#pragma unroll
+          for (int u = 0; u < GRAM_PB; u++) {
+            tu_[u] = tv_[u] = wu_[u] = wv_[u] = 0.f;
+            if (nn[u] >= 0 && pv) {
+              const float *tg = p.targets + (size_t)nn[u] * 2 * HW, *wg = p.weights + (size_t)nn[u] * 2 * HW;
+              tu_[u] = ldg_stream(tg + pix);
+              tv_[u] = ldg_stream(tg + HW + pix);
+              wu_[u] = ldg_stream(wg + pix);
+              wv_[u] = ldg_stream(wg + HW + pix);
+            }
           }
 #pragma unroll
-          for (int c = 0; c < 6; c++) buf[gram_off(lane, 6 * q + c, nbs, RS)] = e[c];
+          for (int u = 0; u < GRAM_PB; u++) {
+            if (nn[u] < 0) continue;
+            const int q = pw + (j0 + u) * npw;
+            const EdgeGeo *g = p.geo + nn[u];
+            float R[9], t[3];
+            {
+              const float4 g0 = __ldg(reinterpret_cast<const float4 *>(g)), g1 = __ldg(reinterpret_cast<const float4 *>(g) + 1),
+                           g2 = __ldg(reinterpret_cast<const float4 *>(g) + 2);
+              R[0] = g0.x; R[1] = g0.y; R[2] = g0.z; R[3] = g0.w;
+              R[4] = g1.x; R[5] = g1.y; R[6] = g1.z; R[7] = g1.w;
+              R[8] = g2.x; t[0] = g2.y; t[1] = g2.z; t[2] = g2.w;
+            }
+            const bool stereo = __ldg(&g->flags) & 1;
+            float e[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            if (pv && !stereo) {
+              PixHat L;
+              if (p.mode == 0) pix_hat<0>(R, t, pk, x0, y0, zq, tu_[u], tv_[u], wu_[u], wv_[u], L);
+              else pix_hat<1>(R, t, pk, x0, y0, zq, tu_[u], tv_[u], wu_[u], wv_[u], L);
+              const float su = sq * L.wu * L.jzu, sv = sq * L.wv * L.jzv;
+              e[0] = su * L.e;
+              e[1] = sv * L.e;
+              e[2] = fmaf(su, L.nae, sv * L.nbe);
+              e[3] = fmaf(su, L.nab, sv * L.nopb);
+              e[4] = fmaf(su, L.opa, sv * L.ab);
+              e[5] = fmaf(su, L.nb, sv * L.a);
+            }
+            // 6 q is even: three aligned 8-byte stores
+            float2 *dst = reinterpret_cast<float2 *>(row + 6 * q);
+            dst[0] = make_float2(e[0], e[1]);
+            dst[1] = make_float2(e[2], e[3]);
+            dst[2] = make_float2(e[4], e[5]);
+          }
         }
+        if (pw == 0) row[Rw] = sq * wk;
         __threadfence_block();
         named_bar_arrive(1 + b);  // buffer b is full
       }
     } else {
+      // block enumeration: the nb diagonal blocks first, then bi < bj row major
       const int blk = pass * ncw * 32 + tid;
       int bi = 0, bj = 0;
       const bool active = blk < nblk;
-      if (active) {  // blk -> (bi <= bj), row major over the block-upper triangle
-        int rem = blk;
-        while (rem >= nb - bi) {
-          rem -= nb - bi;
+      const bool diag = blk < nb;
+      if (diag) bi = bj = blk;
+      else if (active) {
+        int rem = blk - nb;
+        while (rem >= nb - 1 - bi) {
+          rem -= nb - 1 - bi;
           bi++;
         }
-        bj = bi + rem;
+        bj = bi + 1 + rem;
       }
-      const bool diag = active && bi == bj;
-      float acc[8][8], accw[8];
+      const bool wdiag = (pass * ncw * 32 + warp * 32) < nb;  // warp-uniform: this warp owns diagonal blocks
+      unsigned long long acc[8][4];
+      float accw[8];
 #pragma unroll
       for (int r = 0; r < 8; r++) {
         accw[r] = 0.f;
 #pragma unroll
-        for (int c = 0; c < 8; c++) acc[r][c] = 0.f;
+        for (int c = 0; c < 4; c++) acc[r][c] = 0ull;
       }
-      const int wchunk = (Rw >> 3) + (((Rw >> 2) & 1) ? nbs : 0), wsub = Rw & 3;
       for (int it = 0; it < nloc; it++) {
         const int b = it & 1;
-        const float4 *tile4 = reinterpret_cast<const float4 *>(s_tile + b * GRAM_T * RS);
+        const float *pa = s_tile + b * GRAM_T * RS + 8 * bi;
+        const float *pb = s_tile + b * GRAM_T * RS + 8 * bj;
+        const float *pw_ = s_tile + b * GRAM_T * RS + Rw;
         named_bar_sync(1 + b);  // wait until the producers filled buffer b
         if (active) {
-#pragma unroll 4
+#pragma unroll 8
           for (int pp = 0; pp < GRAM_T; pp++) {
-            const int s = pp & 7;
-            const float4 a0 = tile4[pp * RS4 + (bi ^ s)], a1 = tile4[pp * RS4 + ((nbs + bi) ^ s)];
-            const float4 b0 = tile4[pp * RS4 + (bj ^ s)], b1 = tile4[pp * RS4 + ((nbs + bj) ^ s)];
+            const float4 a0 = *reinterpret_cast<const float4 *>(pa), a1 = *reinterpret_cast<const float4 *>(pa + 4);
+            const float4 b0 = *reinterpret_cast<const float4 *>(pb), b1 = *reinterpret_cast<const float4 *>(pb + 4);
             const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-            const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+            const unsigned long long bp[4] = {pack2(b0.x, b0.y), pack2(b0.z, b0.w), pack2(b1.x, b1.y), pack2(b1.z, b1.w)};
 #pragma unroll
-            for (int r = 0; r < 8; r++)
+            for (int r = 0; r < 8; r++) {
+              const unsigned long long ap = pack2(a[r], a[r]);
 #pragma unroll
-              for (int c = 0; c < 8; c++) acc[r][c] = fmaf(a[r], bb[c], acc[r][c]);
-            if (diag) {
-              const float wq = reinterpret_cast<const float *>(tile4)[(pp * RS4 + (wchunk ^ s)) * 4 + wsub];
+              for (int c = 0; c < 4; c++) fma2(acc[r][c], ap, bp[c]);
+            }
+            if (wdiag) {
+              const float wq = *pw_;
 #pragma unroll
               for (int r = 0; r < 8; r++) accw[r] = fmaf(a[r], wq, accw[r]);
             }
+            pa += RS;
+            pb += RS;
+            pw_ += RS;
           }
         }
         if (it + 2 < nloc) named_bar_arrive(3 + b);  // buffer b may be refilled
@@ -622,11 +666,18 @@ __global__ void __launch_bounds__(GRAM_NT, 2) k_gram(BaParams p) {
 #pragma unroll
         for (int r = 0; r < 8; r++) {
 #pragma unroll
-          for (int c = 0; c < 8; c++) {
-            float *dst = G + (size_t)(8 * bi + r) * Rp + 8 * bj + c;
-            if (8 * bj + c == Rw) continue;  // that column belongs to the E Q w sums below
-            if (gridDim.x == 1) *dst = acc[r][c];
-            else atomicAdd(dst, acc[r][c]);
+          for (int c = 0; c < 4; c++) {
+            float v0, v1;
+            unpack2(acc[r][c], v0, v1);
+            float *dst = G + (size_t)(8 * bi + r) * Rp + 8 * bj + 2 * c;
+            if (8 * bj + 2 * c != Rw) {  // column Rw belongs to the E Q w sums below
+              if (gridDim.x == 1) dst[0] = v0;
+              else atomicAdd(dst, v0);
+            }
+            if (8 * bj + 2 * c + 1 != Rw) {
+              if (gridDim.x == 1) dst[1] = v1;
+              else atomicAdd(dst + 1, v1);
+            }
           }
           if (diag && 8 * bi + r < Rw) {
             float *dst = G + (size_t)(8 * bi + r) * Rp + Rw;
