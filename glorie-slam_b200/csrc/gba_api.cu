@@ -308,7 +308,7 @@ extern "C" int gba_ba_begin(gba_ctx *c, float *poses, float *disps, const float 
       return fail_msg(c, GBA_ECAPACITY, "Schur Gram buffers need %llu floats (capacity %zu); max out-degree %d",
                       st.gram_floats, c->gram_cap, st.max_deg);
     const int RS = gram_pitch((6 * st.max_deg + 1 + 7) / 8);
-    if ((size_t)2 * GRAM_T * RS * sizeof(float) > (size_t)kGramSmemMax)
+    if ((size_t)2 * GRAM_T * RS * sizeof(float) + (size_t)st.max_deg * 68 > (size_t)kGramSmemMax)
       return fail_msg(c, GBA_ECAPACITY, "out-degree %d too large for the shared-memory Gram tile", st.max_deg);
   }
   // launch shape of the streaming passes: largest CTA footprint that still gives >= 2 CTAs per SM
@@ -371,7 +371,7 @@ extern "C" int gba_ba_build(gba_ctx *c) {
     stage_begin(c, GBA_STAGE_GRAM);
     if (c->gsplit > 1) CK(cudaMemsetAsync(c->gram, 0, (size_t)st.gram_floats * sizeof(float), s));
     const int RS = gram_pitch((6 * st.max_deg + 1 + 7) / 8);
-    k_gram<<<dim3(c->gsplit, st.K), GRAM_NT, (size_t)2 * GRAM_T * RS * sizeof(float), s>>>(p);
+    k_gram<<<dim3(c->gsplit, st.K), GRAM_NT, (size_t)2 * GRAM_T * RS * sizeof(float) + (size_t)st.max_deg * 68, s>>>(p);
     LAUNCH_CHECK("k_gram");
     stage_end(c);
     stage_begin(c, GBA_STAGE_SCHUR);

@@ -520,7 +520,7 @@ __global__ void __launch_bounds__(GRAM_NT, 2) k_gram(BaParams p) {
   const int nb = (Rw + 7) / 8;         // 8-row blocks of G proper
   const int nbs = (Rw + 1 + 7) / 8;    // 8-column chunks of a shared-memory row (incl. the w column)
   const int Rp = nbs * 8;              // pitch of G in the gram buffer (k_prep_scan uses the same)
-  const int RS = gram_pitch(nbs);
+  const int RS = gram_pitch(nbs), half = 4 * nbs;  // row = [cols 0-3 of all blocks | cols 4-7 of all blocks]
   const int nblk = nb * (nb + 1) / 2;
   const int ncw = min(GRAM_MAXCW, (nblk + 31) / 32);  // consumer warps
   const int npw = GRAM_NT / 32 - ncw;                 // producer warps
@@ -535,77 +535,129 @@ __global__ void __launch_bounds__(GRAM_NT, 2) k_gram(BaParams p) {
 
   // padding columns of both buffers stay zero; data columns are rewritten for every tile
   for (int i = tid; i < 2 * GRAM_T * RS; i += GRAM_NT) s_tile[i] = 0.f;
+  // per-edge geometry and edge ids of this keyframe, staged once behind the two tile buffers
+  EdgeGeo *s_geo = reinterpret_cast<EdgeGeo *>(s_tile + 2 * GRAM_T * RS);
+  int *s_eid = reinterpret_cast<int *>(s_geo + deg);
+  for (int i = tid; i < deg; i += GRAM_NT) s_eid[i] = p.eidx[e0 + i];
+  for (int i = tid; i < deg * 16; i += GRAM_NT)
+    reinterpret_cast<float *>(s_geo)[i] = reinterpret_cast<const float *>(p.geo + p.eidx[e0 + (i >> 4)])[i & 15];
   __syncthreads();
 
   for (int pass = 0; pass < npass; pass++) {
     if (producer) {
       const int pw = warp - ncw;
-      for (int it = 0; it < nloc; it++) {
-        const int b = it & 1;
-        float *row = s_tile + b * GRAM_T * RS + lane * RS;
-        if (it >= 2) named_bar_sync(3 + b);  // consumers are done with this buffer (tile it-2)
-        const int tt = blockIdx.x + it * gridDim.x;
-        const int pix = tt * GRAM_T + lane;
-        const bool pv = pix < HW;
-        const float zq = pv ? p.disps[(size_t)frame * HW + pix] : 1.f;
-        const float sq = pv ? sqrtf(p.Q[(size_t)k * HW + pix]) : 0.f;
-        const float x0 = ((float)(pix % p.wd) - cx) / fx, y0 = ((float)(pix / p.wd) - cy) / fy;
-        const float wk = (pw == 0 && pv) ? p.W[(size_t)k * HW + pix] : 0.f;
-        // the producer is latency bound: fetch target/weight of up to GRAM_PB edges before using any
-        const int nq = (deg - pw + npw - 1) / npw;  // edges of this warp: q = pw + j * npw
-        for (int j0 = 0; j0 < nq; j0 += GRAM_PB) {
-          int nn[GRAM_PB];
-          float tu_[GRAM_PB], tv_[GRAM_PB], wu_[GRAM_PB], wv_[GRAM_PB];
-#pragma unroll
-          for (int u = 0; u < GRAM_PB; u++) nn[u] = (j0 + u < nq) ? p.eidx[e0 + pw + (j0 + u) * npw] : -1;
-#pragma unroll
-          for (int u = 0; u < GRAM_PB; u++) {
-            tu_[u] = tv_[u] = wu_[u] = wv_[u] = 0.f;
-            if (nn[u] >= 0 && pv) {
-              const float *tg = p.targets + (size_t)nn[u] * 2 * HW, *wg = p.weights + (size_t)nn[u] * 2 * HW;
-              tu_[u] = ldg_stream(tg + pix);
-              tv_[u] = ldg_stream(tg + HW + pix);
-              wu_[u] = ldg_stream(wg + pix);
-              wv_[u] = ldg_stream(wg + HW + pix);
-            }
-          }
-#pragma unroll
-          for (int u = 0; u < GRAM_PB; u++) {
-            if (nn[u] < 0) continue;
-            const int q = pw + (j0 + u) * npw;
-            const EdgeGeo *g = p.geo + nn[u];
-            float R[9], t[3];
-            {
-              const float4 g0 = __ldg(reinterpret_cast<const float4 *>(g)), g1 = __ldg(reinterpret_cast<const float4 *>(g) + 1),
-                           g2 = __ldg(reinterpret_cast<const float4 *>(g) + 2);
-              R[0] = g0.x; R[1] = g0.y; R[2] = g0.z; R[3] = g0.w;
-              R[4] = g1.x; R[5] = g1.y; R[6] = g1.z; R[7] = g1.w;
-              R[8] = g2.x; t[0] = g2.y; t[1] = g2.z; t[2] = g2.w;
-            }
-            const bool stereo = __ldg(&g->flags) & 1;
-            float e[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-            if (pv && !stereo) {
-              PixHat L;
-              if (p.mode == 0) pix_hat<0>(R, t, pk, x0, y0, zq, tu_[u], tv_[u], wu_[u], wv_[u], L);
-              else pix_hat<1>(R, t, pk, x0, y0, zq, tu_[u], tv_[u], wu_[u], wv_[u], L);
-              const float su = sq * L.wu * L.jzu, sv = sq * L.wv * L.jzv;
-              e[0] = su * L.e;
-              e[1] = sv * L.e;
-              e[2] = fmaf(su, L.nae, sv * L.nbe);
-              e[3] = fmaf(su, L.nab, sv * L.nopb);
-              e[4] = fmaf(su, L.opa, sv * L.ab);
-              e[5] = fmaf(su, L.nb, sv * L.a);
-            }
-            // 6 q is even: three aligned 8-byte stores
-            float2 *dst = reinterpret_cast<float2 *>(row + 6 * q);
-            dst[0] = make_float2(e[0], e[1]);
-            dst[1] = make_float2(e[2], e[3]);
-            dst[2] = make_float2(e[4], e[5]);
-          }
+      const int nq = (deg - pw + npw - 1) / npw;  // edges of this warp: q = pw + j * npw
+      const size_t fo = (size_t)frame * HW, ko = (size_t)k * HW;
+      // one (edge, pixel) item: E row sqrt(Q) w' jz' j' into the half-split shared row
+      auto emit = [&](float *row, int q, bool pv, float x0, float y0, float zq, float sq, float tu_, float tv_,
+                      float wu_, float wv_) {
+        const EdgeGeo &g = s_geo[q];
+        float e[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        if (pv && !(g.flags & 1)) {
+          PixHat L;
+          if (p.mode == 0) pix_hat<0>(g.R, g.t, pk, x0, y0, zq, tu_, tv_, wu_, wv_, L);
+          else pix_hat<1>(g.R, g.t, pk, x0, y0, zq, tu_, tv_, wu_, wv_, L);
+          const float su = sq * L.wu * L.jzu, sv = sq * L.wv * L.jzv;
+          e[0] = su * L.e;
+          e[1] = sv * L.e;
+          e[2] = fmaf(su, L.nae, sv * L.nbe);
+          e[3] = fmaf(su, L.nab, sv * L.nopb);
+          e[4] = fmaf(su, L.opa, sv * L.ab);
+          e[5] = fmaf(su, L.nb, sv * L.a);
         }
-        if (pw == 0) row[Rw] = sq * wk;
-        __threadfence_block();
-        named_bar_arrive(1 + b);  // buffer b is full
+        // half-split row: columns [0..3] of every 8-block first, then columns [4..7]; the three
+        // column pairs (6q, 6q+2, 6q+4 are even) never straddle a half
+#pragma unroll
+        for (int c = 0; c < 6; c += 2) {
+          const int col = 6 * q + c;
+          *reinterpret_cast<float2 *>(row + ((col >> 2) & 1) * half + ((col >> 3) << 2) + (col & 3)) =
+              make_float2(e[c], e[c + 1]);
+        }
+      };
+      const int woff = ((Rw >> 2) & 1) * half + ((Rw >> 3) << 2) + (Rw & 3);
+      if (nq <= GRAM_PB) {
+        // common case: all edges of this warp fit one batch.  The producer is latency bound, so the
+        // inputs of tile it+1 are requested before tile it is computed (register double buffer).
+        const float *tgp[GRAM_PB];
+        const float *wgp[GRAM_PB];
+#pragma unroll
+        for (int u = 0; u < GRAM_PB; u++) {
+          const int n = (u < nq) ? s_eid[pw + u * npw] : 0;
+          tgp[u] = p.targets + (size_t)n * 2 * HW;
+          wgp[u] = p.weights + (size_t)n * 2 * HW;
+        }
+        float tu_[GRAM_PB], tv_[GRAM_PB], wu_[GRAM_PB], wv_[GRAM_PB], zq = 1.f, qv = 0.f, wk = 0.f;
+        auto fetch = [&](int it) {
+          const int pix = (blockIdx.x + it * gridDim.x) * GRAM_T + lane;
+          const bool pv = pix < HW;
+          zq = pv ? p.disps[fo + pix] : 1.f;
+          qv = pv ? p.Q[ko + pix] : 0.f;
+          wk = (pw == 0 && pv) ? p.W[ko + pix] : 0.f;
+#pragma unroll
+          for (int u = 0; u < GRAM_PB; u++) {
+            const bool ok = pv && u < nq;
+            tu_[u] = ok ? ldg_stream(tgp[u] + pix) : 0.f;
+            tv_[u] = ok ? ldg_stream(tgp[u] + HW + pix) : 0.f;
+            wu_[u] = ok ? ldg_stream(wgp[u] + pix) : 0.f;
+            wv_[u] = ok ? ldg_stream(wgp[u] + HW + pix) : 0.f;
+          }
+        };
+        if (nloc > 0) fetch(0);
+        for (int it = 0; it < nloc; it++) {
+          const int b = it & 1;
+          float *row = s_tile + b * GRAM_T * RS + lane * RS;
+          const int pix = (blockIdx.x + it * gridDim.x) * GRAM_T + lane;
+          const bool pv = pix < HW;
+          const float x0 = ((float)(pix % p.wd) - cx) / fx, y0 = ((float)(pix / p.wd) - cy) / fy;
+          // move the current inputs out of the way, then request the next tile's
+          float ctu[GRAM_PB], ctv[GRAM_PB], cwu[GRAM_PB], cwv[GRAM_PB];
+#pragma unroll
+          for (int u = 0; u < GRAM_PB; u++) {
+            ctu[u] = tu_[u]; ctv[u] = tv_[u]; cwu[u] = wu_[u]; cwv[u] = wv_[u];
+          }
+          const float czq = zq, csq = sqrtf(qv), cwk = wk;
+          if (it + 1 < nloc) fetch(it + 1);
+          if (it >= 2) named_bar_sync(3 + b);  // consumers are done with this buffer (tile it-2)
+#pragma unroll
+          for (int u = 0; u < GRAM_PB; u++)
+            if (u < nq) emit(row, pw + u * npw, pv, x0, y0, czq, csq, ctu[u], ctv[u], cwu[u], cwv[u]);
+          if (pw == 0) row[woff] = csq * cwk;
+          __threadfence_block();
+          named_bar_arrive(1 + b);  // buffer b is full
+        }
+      } else {
+        for (int it = 0; it < nloc; it++) {
+          const int b = it & 1;
+          float *row = s_tile + b * GRAM_T * RS + lane * RS;
+          if (it >= 2) named_bar_sync(3 + b);
+          const int pix = (blockIdx.x + it * gridDim.x) * GRAM_T + lane;
+          const bool pv = pix < HW;
+          const float zq = pv ? p.disps[fo + pix] : 1.f;
+          const float sq = pv ? sqrtf(p.Q[ko + pix]) : 0.f;
+          const float x0 = ((float)(pix % p.wd) - cx) / fx, y0 = ((float)(pix / p.wd) - cy) / fy;
+          const float wk = (pw == 0 && pv) ? p.W[ko + pix] : 0.f;
+          for (int j0 = 0; j0 < nq; j0 += GRAM_PB) {
+            float tu_[GRAM_PB], tv_[GRAM_PB], wu_[GRAM_PB], wv_[GRAM_PB];
+#pragma unroll
+            for (int u = 0; u < GRAM_PB; u++) {
+              tu_[u] = tv_[u] = wu_[u] = wv_[u] = 0.f;
+              if (j0 + u < nq && pv) {
+                const int n = s_eid[pw + (j0 + u) * npw];
+                const float *tg = p.targets + (size_t)n * 2 * HW, *wg = p.weights + (size_t)n * 2 * HW;
+                tu_[u] = ldg_stream(tg + pix);
+                tv_[u] = ldg_stream(tg + HW + pix);
+                wu_[u] = ldg_stream(wg + pix);
+                wv_[u] = ldg_stream(wg + HW + pix);
+              }
+            }
+#pragma unroll
+            for (int u = 0; u < GRAM_PB; u++)
+              if (j0 + u < nq) emit(row, pw + (j0 + u) * npw, pv, x0, y0, zq, sq, tu_[u], tv_[u], wu_[u], wv_[u]);
+          }
+          if (pw == 0) row[woff] = sq * wk;
+          __threadfence_block();
+          named_bar_arrive(1 + b);
+        }
       }
     } else {
       // block enumeration: the nb diagonal blocks first, then bi < bj row major
@@ -633,15 +685,15 @@ __global__ void __launch_bounds__(GRAM_NT, 2) k_gram(BaParams p) {
       }
       for (int it = 0; it < nloc; it++) {
         const int b = it & 1;
-        const float *pa = s_tile + b * GRAM_T * RS + 8 * bi;
-        const float *pb = s_tile + b * GRAM_T * RS + 8 * bj;
-        const float *pw_ = s_tile + b * GRAM_T * RS + Rw;
+        const float *pa = s_tile + b * GRAM_T * RS + 4 * bi;
+        const float *pb = s_tile + b * GRAM_T * RS + 4 * bj;
+        const float *pw_ = s_tile + b * GRAM_T * RS + ((Rw >> 2) & 1) * half + ((Rw >> 3) << 2) + (Rw & 3);
         named_bar_sync(1 + b);  // wait until the producers filled buffer b
         if (active) {
 #pragma unroll 8
           for (int pp = 0; pp < GRAM_T; pp++) {
-            const float4 a0 = *reinterpret_cast<const float4 *>(pa), a1 = *reinterpret_cast<const float4 *>(pa + 4);
-            const float4 b0 = *reinterpret_cast<const float4 *>(pb), b1 = *reinterpret_cast<const float4 *>(pb + 4);
+            const float4 a0 = *reinterpret_cast<const float4 *>(pa), a1 = *reinterpret_cast<const float4 *>(pa + half);
+            const float4 b0 = *reinterpret_cast<const float4 *>(pb), b1 = *reinterpret_cast<const float4 *>(pb + half);
             const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
             const unsigned long long bp[4] = {pack2(b0.x, b0.y), pack2(b0.z, b0.w), pack2(b1.x, b1.y), pack2(b1.z, b1.w)};
 #pragma unroll
