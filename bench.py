@@ -190,6 +190,7 @@ def main():
     poses0, disps0 = d["poses"].clone(), d["disps"].clone()
     kx_t = torch.from_numpy(kx).to(dev)
     owned_t = torch.from_numpy((owner == rank).astype(np.uint8)).to(dev)
+    ii_all, jj_all = torch.from_numpy(g.ii).to(dev), torch.from_numpy(g.jj).to(dev)
     droid_backends.RETURN_UPDATES = False  # GlORIE-SLAM discards [dx, dz]; skip the extra sync
     input_bytes = sum(v.numel() * v.element_size() for k, v in host.items())
     l2_flush = None
@@ -206,7 +207,7 @@ def main():
                               d["ii"], d["jj"], g.t0, g.t1, iters, g.lm, g.ep, False, False)
         else:
             sharded.ba_sharded(d["poses"], d["disps"], d["intr"], d["sens"], d["targets"], d["weights"], d["eta"],
-                               d["ii"], d["jj"], g.t0, g.t1, iters, g.lm, g.ep, kx_t, owned_t)
+                               d["ii"], d["jj"], g.t0, g.t1, iters, g.lm, g.ep, kx_t, owned_t, ii_all, jj_all)
 
     def barrier():
         if world > 1:
@@ -238,7 +239,7 @@ def main():
         reset()
         step()
     barrier()
-    ctx = _gba.context(local_rank, N, max(E_local, 1), ht, wd)
+    ctx = _gba.context(local_rank, N, max(E_local, E_total if world > 1 else 1, 1), ht, wd)
     info = _gba.query(ctx)
     launches_per_step = info.kernel_launches
     sampler = ClockSampler(local_rank)

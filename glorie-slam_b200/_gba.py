@@ -43,7 +43,7 @@ def lib():
         L.gba_last_error.restype = ctypes.c_char_p
         L.gba_ba.argtypes = [vp] + [vp] * 9 + [ci] * 6 + [cf, cf, ci, ci, ci, vp, vp, vp]
         L.gba_dspo.argtypes = [vp] + [vp] * 12 + [ci] * 4 + [cf, cf, cf, ci, vp]
-        L.gba_ba_begin.argtypes = [vp] + [vp] * 9 + [ci] * 5 + [cf, cf, ci, ci, ci, vp, ci, vp, vp]
+        L.gba_ba_begin.argtypes = [vp] + [vp] * 9 + [ci] * 5 + [cf, cf, ci, ci, ci, vp, ci, vp, vp, vp, ci, vp]
         L.gba_ba_build.argtypes = [vp]
         L.gba_ba_system.argtypes = [vp, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]
         L.gba_ba_solve.argtypes = [vp]

@@ -223,10 +223,10 @@ extern "C" int gba_create(gba_ctx **out, int device, int max_frames, int max_edg
 }
 
 // ---- index build shared by BA and DSPO ---------------------------------------------------------
-static int build_index(gba_ctx *c, const int64_t *kx_global, int n_kx, bool want_tiles) {
+// CSR of the edges in p.ii / p.jj by source keyframe
+static int build_csr(gba_ctx *c, const int64_t *kx_global, int n_kx) {
   BaParams &p = c->p;
   cudaStream_t s = c->stream;
-  stage_begin(c, GBA_STAGE_INDEX);
   k_prep_frames<<<1, 1024, 0, s>>>(p, kx_global, n_kx);
   LAUNCH_CHECK("k_prep_frames");
   if (p.E > 0) {
@@ -239,6 +239,26 @@ static int build_index(gba_ctx *c, const int64_t *kx_global, int n_kx, bool want
     k_prep_fill<<<(p.N * 32 + 255) / 256, 256, 0, s>>>(p);
     LAUNCH_CHECK("k_prep_fill");
   }
+  return GBA_OK;
+}
+
+// ii_all/jj_all (optional): the whole graph, when p.ii/p.jj hold only this rank's shard; the pose
+// ordering and the tile structure must be identical on all ranks, so they come from the whole graph
+static int build_index(gba_ctx *c, const int64_t *kx_global, int n_kx, bool want_tiles,
+                       const int64_t *ii_all = nullptr, const int64_t *jj_all = nullptr, int n_all = 0) {
+  BaParams &p = c->p;
+  cudaStream_t s = c->stream;
+  stage_begin(c, GBA_STAGE_INDEX);
+  const bool sharded = want_tiles && ii_all && jj_all;
+  const int64_t *ii_loc = p.ii, *jj_loc = p.jj;
+  const int E_loc = p.E;
+  if (sharded) {
+    p.ii = ii_all;
+    p.jj = jj_all;
+    p.E = n_all;
+  }
+  int rc = build_csr(c, kx_global, n_kx);
+  if (rc) return rc;
   if (want_tiles) {
     k_order<<<1, 1024, (size_t)((p.P + 3) / 4) * 4, s>>>(p, c->pos_cap);
     LAUNCH_CHECK("k_order");
@@ -247,6 +267,13 @@ static int build_index(gba_ctx *c, const int64_t *kx_global, int n_kx, bool want
     LAUNCH_CHECK("k_tile_mark");
     k_tile_fill<<<1, 512, 0, s>>>(p, c->sb);
     LAUNCH_CHECK("k_tile_fill");
+  }
+  if (sharded) {  // now the CSR of this rank's own edges
+    p.ii = ii_loc;
+    p.jj = jj_loc;
+    p.E = E_loc;
+    rc = build_csr(c, kx_global, n_kx);
+    if (rc) return rc;
   }
   stage_end(c);
   CK(cudaMemcpyAsync(c->st_h, c->st_d, sizeof(Status), cudaMemcpyDeviceToHost, s));
@@ -265,7 +292,8 @@ extern "C" int gba_ba_begin(gba_ctx *c, float *poses, float *disps, const float 
                             const float *targets, const float *weights, const float *eta, const int64_t *ii,
                             const int64_t *jj, int n_frames, int n_edges, int eta_rows, int t0, int t1, float lm,
                             float ep, int motion_only, int depth_only, int mode, const int64_t *kx_global, int n_kx,
-                            const uint8_t *owned, void *stream) {
+                            const uint8_t *owned, const int64_t *ii_all, const int64_t *jj_all, int n_all,
+                            void *stream) {
   if (!c) return GBA_EINVAL;
   c->begun = 0;
   if (!poses || !disps || !intrinsics || !disps_sens || !eta || (n_edges > 0 && (!targets || !weights || !ii || !jj)))
@@ -273,6 +301,8 @@ extern "C" int gba_ba_begin(gba_ctx *c, float *poses, float *disps, const float 
   if (n_frames < 1 || n_frames > c->N_max)
     return fail_msg(c, GBA_ECAPACITY, "n_frames %d outside [1,%d]", n_frames, c->N_max);
   if (n_edges < 0 || n_edges > c->E_max) return fail_msg(c, GBA_ECAPACITY, "n_edges %d outside [0,%d]", n_edges, c->E_max);
+  if (ii_all && jj_all && (n_all < n_edges || n_all > c->E_max))
+    return fail_msg(c, GBA_ECAPACITY, "n_all %d outside [n_edges,%d]", n_all, c->E_max);
   if (t0 < 0 || t1 <= t0 || t1 > n_frames)
     return fail_msg(c, GBA_EINVAL, "optimised window [%d,%d) not inside [0,%d)", t0, t1, n_frames);
   if (mode != GBA_MODE_DROID_CUDA && mode != GBA_MODE_GEOM_PY) return fail_msg(c, GBA_EINVAL, "unknown mode %d", mode);
@@ -294,7 +324,7 @@ extern "C" int gba_ba_begin(gba_ctx *c, float *poses, float *disps, const float 
   p.nT = c->nT_max;  // stride of the tile tables; the actual tile count comes back in the status
   p.ld = 0;
   c->last_P = p.P;
-  int rc = build_index(c, kx_global, n_kx, true);
+  int rc = build_index(c, kx_global, n_kx, true, ii_all, jj_all, n_all);
   if (rc) return rc;
   const Status &st = *c->st_h;
   if (!motion_only && eta_rows != st.K)
@@ -498,7 +528,8 @@ extern "C" int gba_ba(gba_ctx *c, float *poses, float *disps, const float *intri
                       const int64_t *jj, int n_frames, int n_edges, int eta_rows, int t0, int t1, int iters, float lm,
                       float ep, int motion_only, int depth_only, int mode, float *dx_out, float *dz_out, void *stream) {
   int rc = gba_ba_begin(c, poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, n_frames, n_edges,
-                        eta_rows, t0, t1, lm, ep, motion_only, depth_only, mode, nullptr, 0, nullptr, stream);
+                        eta_rows, t0, t1, lm, ep, motion_only, depth_only, mode, nullptr, 0, nullptr, nullptr, nullptr,
+                        0, stream);
   if (rc) return rc;
   for (int it = 0; it < iters; it++) {
     if ((rc = gba_ba_build(c))) return rc;

@@ -72,26 +72,28 @@ def allreduce_system(view, group=None):
 
 
 def ba_sharded(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1, iterations, lm, ep,
-               kx_t, owned_t, group=None, merge=True):
+               kx_t, owned_t, ii_all, jj_all, group=None, merge=True):
     """`droid_backends.ba` for one rank of an edge-sharded run.
 
     poses / disps / intrinsics / disps_sens / eta: the full (replicated) tensors on this rank's GPU;
     targets / weights / ii / jj: THIS RANK's edges only; kx_t [K] int64 = frame_list(global ii),
-    owned_t [K] uint8 = (owner == rank).  poses and the owned rows of disps are updated in place;
+    owned_t [K] uint8 = (owner == rank), ii_all / jj_all: the edge indices of the WHOLE graph
+    (replicated; the pose ordering and the tile layout of the reduced system are derived from them
+    so that all ranks pack the system identically).  poses and the owned rows of disps are updated in place;
     with merge=True all rows of disps are consistent on return.  Returns the kernel-launch count."""
     dev = poses.device
     N, ht, wd = disps.shape
     E = int(ii.shape[0])
     L = _gba.lib()
     with torch.cuda.device(dev):
-        ctx = _gba.context(dev.index, N, max(E, 1), ht, wd)
+        ctx = _gba.context(dev.index, N, max(E, int(ii_all.shape[0]), 1), ht, wd)
         stream = torch.cuda.current_stream(dev).cuda_stream
         nul = lambda t: t.data_ptr() if t.numel() else None
         _gba.check(ctx, L.gba_ba_begin(ctx, poses.data_ptr(), disps.data_ptr(), intrinsics.data_ptr(),
                                        disps_sens.data_ptr(), nul(targets), nul(weights), eta.data_ptr(), nul(ii),
                                        nul(jj), N, E, int(eta.shape[0]), int(t0), int(t1), float(lm), float(ep), 0, 0,
                                        _gba.MODE_DROID_CUDA, kx_t.data_ptr(), int(kx_t.shape[0]), owned_t.data_ptr(),
-                                       stream))
+                                       ii_all.data_ptr(), jj_all.data_ptr(), int(ii_all.shape[0]), stream))
         view = _gba.system_view(ctx, dev)
         for _ in range(int(iterations)):
             _gba.check(ctx, L.gba_ba_build(ctx))

@@ -82,10 +82,15 @@ int gba_dspo(gba_ctx *ctx, const float *poses, float *disps, const float *intrin
              int ignore_frames, float lm, float ep, float alpha, int interleaved, void *stream);
 
 /* ---- split-phase form of gba_ba for edge-sharded multi-GPU runs --------
- * Every rank calls begin with ITS edges (all edges of a source keyframe live on one rank),
- * `kx_global` = the global sorted list of depth keyframes (so eta rows and dz rows are the
- * same on every rank; NULL = derive from the local edges) and `owned` (one byte per kx entry,
- * NULL = all) marking whose disparities this rank updates.  Per iteration:
+ * Every rank calls begin with ITS edges (all edges of a source keyframe live on one rank) plus
+ *   kx_global [n_kx]      the global sorted list of depth keyframes, so that eta rows and dz rows
+ *                         mean the same on every rank (NULL = derive from the local edges),
+ *   owned [n_kx]          one byte per kx entry: whose disparities this rank updates (NULL = all),
+ *   ii_all, jj_all [n_all] the edge list of the WHOLE graph (indices only, replicated): the pose
+ *                         ordering and the tile structure of the reduced camera system are
+ *                         derived from it, so that the packed system has the same layout on
+ *                         every rank (NULL = the local edges are the whole graph).
+ * Per iteration:
  *   gba_ba_build  -> local contribution to the reduced camera system, packed in a buffer
  *   (caller sums the buffer over ranks, e.g. ncclAllReduce / torch.distributed.all_reduce)
  *   gba_ba_solve  -> damping, factorisation, solve, back-substitution, retraction
@@ -93,7 +98,8 @@ int gba_dspo(gba_ctx *ctx, const float *poses, float *disps, const float *intrin
 int gba_ba_begin(gba_ctx *ctx, float *poses, float *disps, const float *intrinsics, const float *disps_sens,
                  const float *targets, const float *weights, const float *eta, const int64_t *ii, const int64_t *jj,
                  int n_frames, int n_edges, int eta_rows, int t0, int t1, float lm, float ep, int motion_only,
-                 int depth_only, int mode, const int64_t *kx_global, int n_kx, const uint8_t *owned, void *stream);
+                 int depth_only, int mode, const int64_t *kx_global, int n_kx, const uint8_t *owned,
+                 const int64_t *ii_all, const int64_t *jj_all, int n_all, void *stream);
 int gba_ba_build(gba_ctx *ctx);
 /* device pointer + element count (doubles) of the packed reduced system of the last build */
 int gba_ba_system(gba_ctx *ctx, double **buf, size_t *count);

@@ -55,7 +55,7 @@ def split_phase(g, mode=0, owned_masks=None, iters=1):
     for m in masks:
         sel = np.isin(g.ii, kx[m.astype(bool)])
         h = ctypes.c_void_p()
-        rc = L.gba_create(ctypes.byref(h), 0, N, max(int(sel.sum()), 1), ht, wd)
+        rc = L.gba_create(ctypes.byref(h), 0, N, g.n_edges, ht, wd)
         assert rc == 0, L.gba_last_error(None)
         d = SimpleNamespace(
             h=h, sel=sel, mask=torch.from_numpy(m.astype(np.uint8)).cuda(),
@@ -64,11 +64,13 @@ def split_phase(g, mode=0, owned_masks=None, iters=1):
             targets=torch.from_numpy(np.ascontiguousarray(g.targets[sel])).cuda(),
             weights=torch.from_numpy(np.ascontiguousarray(g.weights[sel])).cuda(),
             eta=torch.from_numpy(g.eta).cuda(), ii=torch.from_numpy(np.ascontiguousarray(g.ii[sel])).cuda(),
-            jj=torch.from_numpy(np.ascontiguousarray(g.jj[sel])).cuda(), kx=torch.from_numpy(kx).cuda())
+            jj=torch.from_numpy(np.ascontiguousarray(g.jj[sel])).cuda(), kx=torch.from_numpy(kx).cuda(),
+            ii_all=torch.from_numpy(g.ii).cuda(), jj_all=torch.from_numpy(g.jj).cuda())
         _gba.check(h, L.gba_ba_begin(h, d.poses.data_ptr(), d.disps.data_ptr(), d.intr.data_ptr(), d.sens.data_ptr(),
                                      d.targets.data_ptr(), d.weights.data_ptr(), d.eta.data_ptr(), d.ii.data_ptr(),
                                      d.jj.data_ptr(), N, int(sel.sum()), g.eta.shape[0], g.t0, g.t1, g.lm, g.ep, 0, 0,
-                                     mode, d.kx.data_ptr(), len(kx), d.mask.data_ptr(), None))
+                                     mode, d.kx.data_ptr(), len(kx), d.mask.data_ptr(), d.ii_all.data_ptr(),
+                                     d.jj_all.data_ptr(), g.n_edges, None))
         ranks.append(d)
     systems = None
     for _ in range(iters):
