@@ -96,7 +96,7 @@ static cudaError_t dalloc(T **p, size_t n) {
   return cudaMalloc((void **)p, std::max<size_t>(n, 1) * sizeof(T));
 }
 
-static const int kSolverSmem = 3 * GBA_NB * (GBA_NB + 1) * (int)sizeof(double);
+static const int kSolverSmem = (2 * GBA_NB + 16) * (GBA_NB + 1) * (int)sizeof(double);
 static const int kGramSmemMax = 200 * 1024;
 
 extern "C" const char *gba_last_error(const gba_ctx *c) { return c ? c->err : g_create_err; }
@@ -352,7 +352,20 @@ extern "C" int gba_ba_begin(gba_ctx *c, float *poses, float *disps, const float 
     }
   p.nchunk = (c->HW + foot[c->variant] - 1) / foot[c->variant];
   const int ntile = (c->HW + GRAM_T - 1) / GRAM_T;
+  // Gram CTAs per keyframe: enough CTAs to fill the GPU (2 resident per SM), and among the small
+  // factors the one with the least tail in the last wave of CTAs
   c->gsplit = std::max(1, std::min(ntile, (3 * c->sm_count + K - 1) / K));
+  if (c->gsplit <= 4) {
+    const int slots = 2 * c->sm_count;
+    double best = 1e30;
+    for (int g = 1; g <= std::min(4, ntile); g++) {
+      const double waves = (double)((K * g + slots - 1) / slots) / g;
+      if (waves < best - 0.05) {
+        best = waves;
+        c->gsplit = g;
+      }
+    }
+  }
   c->begun = 1;
   return GBA_OK;
 }

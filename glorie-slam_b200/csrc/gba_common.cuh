@@ -217,6 +217,24 @@ __device__ __forceinline__ void pix_hat(const float *__restrict__ R, const float
   o.jzv = d * fmaf(-t[2], b, t[1]);
 }
 
+// packed fp32x2 arithmetic (Blackwell FFMA2 / FMUL2): two lanes of work in ONE issue slot
+__device__ __forceinline__ unsigned long long pack2(float lo, float hi) {
+  unsigned long long r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(unsigned long long v, float &lo, float &hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ void fma2(unsigned long long &d, unsigned long long a, unsigned long long b) {
+  asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b));
+}
+__device__ __forceinline__ unsigned long long mul2(unsigned long long a, unsigned long long b) {
+  unsigned long long r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+
 // Sum NV (<= 32) per-lane values across the warp so that lane l ends up holding the total of
 // v[l]: 31 shuffles instead of 5 per value (butterfly that halves the live values per stage).
 __device__ __forceinline__ float warp_transpose_reduce32(float (&v)[32], int lane) {

@@ -314,9 +314,11 @@ __global__ void __launch_bounds__(NT, (NT >= 256) ? 2 : 3) k_linearize(BaParams 
           tu[g] = tv[g] = wu[g] = wv[g] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
       }
-      float acc[32];
+      // 27 sums of (H_jj, v_j), kept as 10 packed pairs + 7 scalars (FFMA2: two sums per issue slot)
+      unsigned long long P[10];
+      float s0 = 0.f, s6 = 0.f, s17 = 0.f, s20 = 0.f, s21 = 0.f, s22 = 0.f;
 #pragma unroll
-      for (int i = 0; i < 32; i++) acc[i] = 0.f;
+      for (int i = 0; i < 10; i++) P[i] = 0ull;
 #pragma unroll
       for (int g = 0; g < NV; g++) {
         const float tua[4] = {tu[g].x, tu[g].y, tu[g].z, tu[g].w}, tva[4] = {tv[g].x, tv[g].y, tv[g].z, tv[g].w};
@@ -330,38 +332,60 @@ __global__ void __launch_bounds__(NT, (NT >= 256) ? 2 : 3) k_linearize(BaParams 
           cacc[g][i] = fmaf(qv, L.jzv, fmaf(qu, L.jzu, cacc[g][i]));
           wacc[g][i] = fmaf(qv, L.rv, fmaf(qu, L.ru, wacc[g][i]));
           if (stereo) continue;  // block-uniform: self edges carry no pose terms (droid_kernels.cu:323,356)
-          const float a0 = L.wu * L.e, a2 = L.wu * L.nae, a3 = L.wu * L.nab, a4 = L.wu * L.opa, a5 = L.wu * L.nb;
-          const float b1 = L.wv * L.e, b2 = L.wv * L.nbe, b3 = L.wv * L.nopb, b4 = L.wv * L.ab, b5 = L.wv * L.a;
-          // upper triangle of H_jj, row major: (0,0..5) (1,1..5) (2,2..5) (3,3..5) (4,4..5) (5,5)
-          acc[0] = fmaf(a0, L.e, acc[0]);
-          acc[2] = fmaf(a0, L.nae, acc[2]);
-          acc[3] = fmaf(a0, L.nab, acc[3]);
-          acc[4] = fmaf(a0, L.opa, acc[4]);
-          acc[5] = fmaf(a0, L.nb, acc[5]);
-          acc[6] = fmaf(b1, L.e, acc[6]);
-          acc[7] = fmaf(b1, L.nbe, acc[7]);
-          acc[8] = fmaf(b1, L.nopb, acc[8]);
-          acc[9] = fmaf(b1, L.ab, acc[9]);
-          acc[10] = fmaf(b1, L.a, acc[10]);
-          acc[11] = fmaf(b2, L.nbe, fmaf(a2, L.nae, acc[11]));
-          acc[12] = fmaf(b2, L.nopb, fmaf(a2, L.nab, acc[12]));
-          acc[13] = fmaf(b2, L.ab, fmaf(a2, L.opa, acc[13]));
-          acc[14] = fmaf(b2, L.a, fmaf(a2, L.nb, acc[14]));
-          acc[15] = fmaf(b3, L.nopb, fmaf(a3, L.nab, acc[15]));
-          acc[16] = fmaf(b3, L.ab, fmaf(a3, L.opa, acc[16]));
-          acc[17] = fmaf(b3, L.a, fmaf(a3, L.nb, acc[17]));
-          acc[18] = fmaf(b4, L.ab, fmaf(a4, L.opa, acc[18]));
-          acc[19] = fmaf(b4, L.a, fmaf(a4, L.nb, acc[19]));
-          acc[20] = fmaf(b5, L.a, fmaf(a5, L.nb, acc[20]));
-          // v_j (in units of 1/fx, 1/fy folded into the weights: w r J = w' r' j')
-          acc[21] = fmaf(a0, L.ru, acc[21]);
-          acc[22] = fmaf(b1, L.rv, acc[22]);
-          acc[23] = fmaf(b2, L.rv, fmaf(a2, L.ru, acc[23]));
-          acc[24] = fmaf(b3, L.rv, fmaf(a3, L.ru, acc[24]));
-          acc[25] = fmaf(b4, L.rv, fmaf(a4, L.ru, acc[25]));
-          acc[26] = fmaf(b5, L.rv, fmaf(a5, L.ru, acc[26]));
+          // ju' = (e, 0, nae, nab, opa, nb), jv' = (0, e, nbe, nopb, ab, a)
+          const unsigned long long U1 = pack2(L.nae, L.nab), U2 = pack2(L.opa, L.nb), U3 = pack2(L.nab, L.opa);
+          const unsigned long long V1 = pack2(L.nbe, L.nopb), V2 = pack2(L.ab, L.a), V3 = pack2(L.nopb, L.ab);
+          const unsigned long long WU = pack2(L.wu, L.wu), WV = pack2(L.wv, L.wv);
+          const unsigned long long A23 = mul2(WU, U1), A45 = mul2(WU, U2), B23 = mul2(WV, V1), B45 = mul2(WV, V2);
+          float a2, a3, a4, a5, b2, b3, b4, b5;
+          unpack2(A23, a2, a3);
+          unpack2(A45, a4, a5);
+          unpack2(B23, b2, b3);
+          unpack2(B45, b4, b5);
+          const float a0 = L.wu * L.e, b1 = L.wv * L.e;
+          const unsigned long long A0 = pack2(a0, a0), B1 = pack2(b1, b1);
+          // H_jj upper triangle, row major: 0:(0,0) 1:(0,1)=0 2..5:(0,2..5) 6:(1,1) 7..10:(1,2..5)
+          // 11..14:(2,2..5) 15..17:(3,3..5) 18,19:(4,4..5) 20:(5,5); v_j: 21..26
+          s0 = fmaf(a0, L.e, s0);
+          fma2(P[0], A0, U1);  // (0,2),(0,3)
+          fma2(P[1], A0, U2);  // (0,4),(0,5)
+          s6 = fmaf(b1, L.e, s6);
+          fma2(P[2], B1, V1);  // (1,2),(1,3)
+          fma2(P[3], B1, V2);  // (1,4),(1,5)
+          fma2(P[4], pack2(a2, a2), U1);  // (2,2),(2,3)
+          fma2(P[4], pack2(b2, b2), V1);
+          fma2(P[5], pack2(a2, a2), U2);  // (2,4),(2,5)
+          fma2(P[5], pack2(b2, b2), V2);
+          fma2(P[6], pack2(a3, a3), U3);  // (3,3),(3,4)
+          fma2(P[6], pack2(b3, b3), V3);
+          s17 = fmaf(b3, L.a, fmaf(a3, L.nb, s17));  // (3,5)
+          fma2(P[7], pack2(a4, a4), U2);  // (4,4),(4,5)
+          fma2(P[7], pack2(b4, b4), V2);
+          s20 = fmaf(b5, L.a, fmaf(a5, L.nb, s20));  // (5,5)
+          // v_j (w r J = w' r' j')
+          s21 = fmaf(a0, L.ru, s21);
+          s22 = fmaf(b1, L.rv, s22);
+          const unsigned long long RU = pack2(L.ru, L.ru), RV = pack2(L.rv, L.rv);
+          fma2(P[8], RU, A23);
+          fma2(P[8], RV, B23);
+          fma2(P[9], RU, A45);
+          fma2(P[9], RV, B45);
         }
       }
+      float acc[32];
+#pragma unroll
+      for (int i = 27; i < 32; i++) acc[i] = 0.f;
+      acc[0] = s0; acc[1] = 0.f; acc[6] = s6; acc[17] = s17; acc[20] = s20; acc[21] = s21; acc[22] = s22;
+      unpack2(P[0], acc[2], acc[3]);
+      unpack2(P[1], acc[4], acc[5]);
+      unpack2(P[2], acc[7], acc[8]);
+      unpack2(P[3], acc[9], acc[10]);
+      unpack2(P[4], acc[11], acc[12]);
+      unpack2(P[5], acc[13], acc[14]);
+      unpack2(P[6], acc[15], acc[16]);
+      unpack2(P[7], acc[18], acc[19]);
+      unpack2(P[8], acc[23], acc[24]);
+      unpack2(P[9], acc[25], acc[26]);
       const float tot = warp_transpose_reduce32(acc, lane);
       if (lane < 28) s_red[warp][q][lane] = tot;
     }
@@ -489,19 +513,6 @@ __host__ __device__ __forceinline__ int gram_pitch(int nbs) { return ((8 * nbs +
 
 __device__ __forceinline__ void named_bar_sync(int id) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(GRAM_NT) : "memory"); }
 __device__ __forceinline__ void named_bar_arrive(int id) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(GRAM_NT) : "memory"); }
-// packed fp32x2 FMA (Blackwell FFMA2): d.lo += a.lo * b.lo, d.hi += a.hi * b.hi in ONE issue slot
-__device__ __forceinline__ unsigned long long pack2(float lo, float hi) {
-  unsigned long long r;
-  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
-  return r;
-}
-__device__ __forceinline__ void unpack2(unsigned long long v, float &lo, float &hi) {
-  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
-}
-__device__ __forceinline__ void fma2(unsigned long long &d, unsigned long long a, unsigned long long b) {
-  asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b));
-}
-
 // Warp-specialised: producer warps rebuild the sqrt(Q)-scaled E rows of a 32-pixel tile into one
 // of two shared-memory buffers while consumer warps accumulate the previous tile into their 8x8
 // register blocks (block-upper triangle of G = A A^T) with packed FFMA2.  FULL/EMPTY named

@@ -308,7 +308,7 @@ __global__ void k_pad_diag(BaParams p) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// Tile-column roles (256 threads; dynamic shared memory: 3 tiles of 64 x 65 doubles).
+// Tile-column roles (256 threads; dynamic shared memory: 2 tiles of 64 x 65 doubles + 16 rows).
 // fp64 runs at 64 FMA/clk/SM on B200, so a 64^3 tile product pins one SM for ~9 us; the
 // trsm / syrk roles therefore work on SLAB-row slabs of a tile (SPLIT = 64 / SLAB CTAs per tile)
 // to spread a tile column over more SMs, and the potrf role keeps divisions and square roots off
@@ -465,7 +465,7 @@ __device__ void role_potrf(const BaParams &p, const SolverBufs &sb, int kk, doub
         s2 += Lo[r][m + 2] * X[m + 2][c];
         s3 += Lo[r][m + 3] * X[m + 3][c];
       }
-      Tm[r][c] = (s0 + s1) + (s2 + s3);
+      Tm[r - 16 * I][c] = (s0 + s1) + (s2 + s3);
     }
     __syncthreads();
     for (int e = tid; e < 16 * ncol; e += 256) {
@@ -473,10 +473,10 @@ __device__ void role_potrf(const BaParams &p, const SolverBufs &sb, int kk, doub
       double s0 = 0.0, s1 = 0.0;
       int m = 16 * I;
       for (; m + 1 <= r; m += 2) {
-        s0 += X[r][m] * Tm[m][c];
-        s1 += X[r][m + 1] * Tm[m + 1][c];
+        s0 += X[r][m] * Tm[m - 16 * I][c];
+        s1 += X[r][m + 1] * Tm[m + 1 - 16 * I][c];
       }
-      if (m <= r) s0 += X[r][m] * Tm[m][c];
+      if (m <= r) s0 += X[r][m] * Tm[m - 16 * I][c];
       X[r][c] = -(s0 + s1);
     }
     __syncthreads();
