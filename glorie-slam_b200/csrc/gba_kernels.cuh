@@ -180,12 +180,21 @@ __global__ void k_prep_fill(BaParams p) {
   const int lane = threadIdx.x & 31;
   if (k >= p.st->K) return;
   int cnt = p.eptr[k];
-  for (int base = 0; base < p.E; base += 32) {
-    const int n = base + lane;
-    const bool m = (n < p.E) && (p.ek[n] == k);
-    const unsigned b = __ballot_sync(0xffffffffu, m);
-    if (m) p.eidx[cnt + __popc(b & ((1u << lane) - 1u))] = n;
-    cnt += __popc(b);
+  // the scan is latency bound (one L2 load per 32 edges): keep 8 loads in flight
+  for (int base = 0; base < p.E; base += 256) {
+    int ekv[8];
+#pragma unroll
+    for (int u = 0; u < 8; u++) {
+      const int n = base + 32 * u + lane;
+      ekv[u] = (n < p.E) ? p.ek[n] : -1;
+    }
+#pragma unroll
+    for (int u = 0; u < 8; u++) {
+      const bool m = ekv[u] == k;
+      const unsigned b = __ballot_sync(0xffffffffu, m);
+      if (m) p.eidx[cnt + __popc(b & ((1u << lane) - 1u))] = base + 32 * u + lane;
+      cnt += __popc(b);
+    }
   }
 }
 
