@@ -38,7 +38,8 @@ import numpy as np  # noqa: E402
 
 METRIC = "edge-pixel residuals/sec (global BA; ms per BA iteration in ms_per_ba_iteration)"
 UNIT = "edge-pixels/s"
-CPU_SAMPLE = dict(n=60, e=1000, r=9, iters=2, lm=1e-5, ep=1e-2, seed=0)
+# bounded CPU sample = config C (backend global BA, 200 keyframes / 3000 edges): a few seconds per run
+CPU_SAMPLE = dict(n=200, e=3000, r=7, iters=2, lm=1e-5, ep=1e-2, seed=0)
 
 
 def peaks():
@@ -118,6 +119,51 @@ def cpu_baseline(steps=1):
             g.n_frames, g.n_edges, g.disps.shape[1], g.disps.shape[2], g.iters, max(steps, 1), best),
         "ms_per_ba_iteration": 1e3 * best / g.iters,
     }
+
+
+def reference_cuda_side_by_side(dev, name="C", reps=5):
+    """Same-box GPU baseline: the reference's own CUDA droid_backends.ba (oracle/_ref, rebuilt
+    unmodified for sm_100 by oracle/build_ref.py) against libgba on config C, device resident,
+    CUDA events, best of `reps`.  Config E is left out: the reference's host-side Schur loop
+    (droid_kernels.cu:1257-1272) makes a single call take tens of seconds there."""
+    import importlib.util
+
+    import torch
+
+    import droid_backends
+    import synth
+
+    so = os.path.join(ROOT, "oracle", "_ref", "ref_droid_backends.so")
+    if not os.path.exists(so):
+        return None
+    try:
+        spec = importlib.util.spec_from_file_location("ref_droid_backends", so)
+        ref = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(ref)
+        g = synth.make_config(name)
+        t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+        base = [t(x) for x in (g.poses, g.disps)]
+        rest = [t(x) for x in (g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj)]
+        out = {}
+        for label, fn in (("reference", ref.ba), ("libgba", droid_backends.ba)):
+            best = None
+            for _ in range(reps + 1):
+                p_, d_ = base[0].clone(), base[1].clone()
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                torch.cuda.synchronize()
+                a.record()
+                fn(p_, d_, *rest, g.t0, g.t1, g.iters, g.lm, g.ep, False, False)
+                b.record()
+                torch.cuda.synchronize()
+                ms = a.elapsed_time(b)
+                best = ms if best is None else min(best, ms)
+            out[label + "_ms_per_ba_iteration"] = best / g.iters
+        out["config"] = "config %s: %d keyframes / %d edges, %d iterations, device resident" % (
+            name, g.n_frames, g.n_edges, g.iters)
+        out["speedup"] = out["reference_ms_per_ba_iteration"] / out["libgba_ms_per_ba_iteration"]
+        return out
+    except Exception as e:  # the prebuilt reference is optional evidence
+        return {"unavailable": repr(e)[:200]}
 
 
 def run_reference(args, rank):
@@ -301,8 +347,10 @@ def main():
             e2e["h2d_bytes_per_step"] = int(t.item())
 
     cb = None
+    ref_cuda = None
     if rank == 0 and world == 1 and not args.skip_cpu:
-        cb = cpu_baseline(2)
+        cb = cpu_baseline(3)
+        ref_cuda = reference_cuda_side_by_side(dev)
 
     if rank == 0:
         line = {
@@ -315,7 +363,7 @@ def main():
                        "lm": g.lm, "ep": g.ep, "sharding": "by source keyframe, %d rank(s)" % world,
                        "l2": "inputs (%.0f MB per rank) larger than L2" % (input_bytes / 1e6) if l2_flush is None
                              else "256 MB L2 flush between steps"},
-            "roofline": roofline, "stages": stages, "cpu_baseline": cb, "e2e": e2e,
+            "roofline": roofline, "stages": stages, "cpu_baseline": cb, "e2e": e2e, "reference_cuda": ref_cuda,
             "gpu_launches": int(launches_per_step * args.steps), "gpu_launches_per_step": int(launches_per_step),
             "clocks": clocks,
             "solver": {"tiles": info.n_tiles, "active_tiles": info.n_active_tiles, "chol_failures": info.chol_failures},

@@ -185,6 +185,39 @@ def test_non_spd_system_gives_zero_update():
     np.testing.assert_array_equal(r.poses, g.poses)
 
 
+def test_non_spd_at_scale_does_not_hang_and_zeroes_the_update():
+    """the failure path runs through the fused tile-column kernels (flags still get raised)"""
+    g = synth.make_config("C")
+    r = run_ba(g, iters=2, lm=-2.0, ep=0.0, motion_only=True)
+    assert r.info.chol_failures == 2
+    np.testing.assert_array_equal(r.dx, 0)
+    np.testing.assert_array_equal(r.poses, g.poses)
+    # and the context recovers: a normal call afterwards is fine
+    r2 = run_ba(g)
+    assert r2.info.chol_failures == 0 and np.isfinite(r2.poses).all()
+
+
+def test_hub_keyframe_with_large_out_degree():
+    """one keyframe with 40 out-edges: several Gram passes, producer batches > GRAM_PB, hub frame"""
+    n = 48
+    g = synth.make_graph(n, 2 * (n - 1), 1, iters=2, seed=9, ht=16, wd=24)
+    rng = np.random.default_rng(3)
+    hub = 5
+    extra_j = np.array([j for j in range(n) if abs(j - hub) > 1][:38], dtype=np.int64)
+    extra_i = np.full_like(extra_j, hub)
+    ii = np.concatenate([g.ii, extra_i, extra_j])
+    jj = np.concatenate([g.jj, extra_j, extra_i])
+    tg = synth.project(g.poses_gt, g.disps_gt, g.intrinsics, ii, jj) + rng.normal(0, 0.5, (len(ii), 2, 16, 24)).astype(np.float32)
+    g.ii, g.jj, g.targets = ii, jj, tg.astype(np.float32)
+    g.weights = rng.uniform(0, 1, tg.shape).astype(np.float32)
+    o = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj, g.t0, g.t1,
+                  g.iters, g.lm, g.ep, precision="f64")
+    r = run_ba(g)
+    assert r.info.max_out_degree >= 40
+    assert rel(sign_normalise(r.poses), sign_normalise(o.poses)) < STATE_RTOL
+    assert rel(r.disps, o.disps) < STATE_RTOL
+
+
 def test_argument_errors():
     import droid_backends
 
@@ -256,6 +289,25 @@ def test_dspo_against_oracle_config_b_with_ignored_frames():
     assert rel(wqs[0].cpu().numpy(), np.stack([o.scales, o.shifts], -1)) < STATE_RTOL
 
 
+def test_dspo_config_d_size_against_oracle():
+    """config D of BASELINE.json: DSPO with a synthetic mono prior, 200 keyframes / 3000 edges"""
+    import geom_ba
+
+    g = synth.make_config("D")
+    tg = np.ascontiguousarray(g.targets.transpose(0, 2, 3, 1))
+    wg = np.ascontiguousarray(g.weights.transpose(0, 2, 3, 1))
+    o = oracle.dspo(g.poses, g.disps, g.intrinsics, tg, wg, g.eta, g.ii, g.jj, g.mono_disps, g.scales, g.shifts,
+                    g.valid_depth_mask, 0, g.lm, g.ep, g.alpha, precision="f64")
+    d = to_dev(g)
+    _, disps, wqs = geom_ba.BA_with_scale_shift(
+        torch.from_numpy(tg).cuda()[None], torch.from_numpy(wg).cuda()[None], d.eta, d.poses[None], d.disps[None],
+        d.intr[None, None].repeat(1, g.n_frames, 1), d.ii, d.jj, torch.from_numpy(g.mono_disps).cuda()[None],
+        torch.from_numpy(g.scales).cuda()[None], torch.from_numpy(g.shifts).cuda()[None],
+        torch.from_numpy(g.valid_depth_mask).cuda()[None], 0, g.lm, g.ep, alpha=g.alpha)
+    assert rel(disps[0].cpu().numpy(), o.disps) < STATE_RTOL
+    assert rel(wqs[0].cpu().numpy(), np.stack([o.scales, o.shifts], -1)) < STATE_RTOL
+
+
 # ------------------------------------------------------------------------------------------
 # edge sharding (two emulated ranks on one GPU; the NCCL plumbing itself is covered on CPU/gloo)
 # ------------------------------------------------------------------------------------------
@@ -318,8 +370,8 @@ def test_reference_cuda_backend_if_present():
     spec = importlib.util.spec_from_file_location("ref_droid_backends", so)
     ref = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(ref)
-    for name in ("A", "R", "B"):
-        g = small_graphs()[name]
+    for name in ("A", "R", "B", "C"):
+        g = small_graphs()[name] if name != "C" else synth.make_config("C")
         d = to_dev(g)
         ref.ba(d.poses, d.disps, d.intr, d.sens, d.targets, d.weights, d.eta, d.ii, d.jj, g.t0, g.t1, g.iters, g.lm,
                g.ep, False, False)
