@@ -344,13 +344,16 @@ __device__ __forceinline__ void load_rows(TilePtr dst, const double *src) {
   }
 }
 
+// Reciprocal for the pivot loop.  Dependent fp64 operations cost ~40 cycles each on B200 (measured
+// with clock64), so the chain is kept to seed + ONE Newton step: rcp.approx.ftz.f64 gives ~20 bits,
+// one step ~40 bits (1e-12 relative).  The trailing update therefore eliminates with a pivot that is
+// off by 1e-12 relative -- a backward error far below fp64 assembly noise; the columns of L are
+// scaled afterwards with an exact sqrt of the pivots actually used.
 __device__ __forceinline__ double fast_rcp(double d) {
-  double r = (double)__frcp_rn((float)d);
-  double e = fma(-d, r, 1.0);
-  r = fma(r, e, r);
-  e = fma(-d, r, 1.0);
-  r = fma(r, e, r);
-  return r;
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+  const double e = fma(-d, r, 1.0);
+  return fma(r, e, r);
 }
 
 // Cholesky of the diagonal tile, its inverse, and the forward substitution y_kk = inv(L_kk) b_kk.
@@ -394,19 +397,24 @@ __device__ void role_potrf(const BaParams &p, const SolverBufs &sb, int kk, doub
       const double *col = s_col[j & 1];
       const double d = col[j];
       if (!(d > 0.0) || isinf(d)) bad = true;  // SimplicialLLT: NumericalIssue on a non-positive pivot
-      const double dinv = fast_rcp(d);
-      if (tid < GBA_NB) Lo[tid][j] = (tid >= j) ? col[tid] : 0.0;  // unscaled, scaled after the loop
-      if (tid == 0) s_dinv[j] = dinv;
-      double ar[4], ac[4];
+      double ar[4], ac[4], pr[4][4];
 #pragma unroll
       for (int u = 0; u < 4; u++) {
         ar[u] = col[ty + 16 * u];
-        ac[u] = col[tx + 16 * u] * dinv;
+        ac[u] = col[tx + 16 * u];
       }
+      // the products do not depend on 1/d: they are formed while the reciprocal is in flight
 #pragma unroll
       for (int u = 0; u < 4; u++)
 #pragma unroll
-        for (int v = 0; v < 4; v++) a[u][v] -= ar[u] * ac[v];
+        for (int v = 0; v < 4; v++) pr[u][v] = ar[u] * ac[v];
+      const double dinv = fast_rcp(d);
+      if (tid < GBA_NB) Lo[tid][j] = (tid >= j) ? col[tid] : 0.0;  // unscaled, scaled after the loop
+      if (tid == 0) s_dinv[j] = d;  // the pivot itself; exact scaling after the loop
+#pragma unroll
+      for (int u = 0; u < 4; u++)
+#pragma unroll
+        for (int v = 0; v < 4; v++) a[u][v] = fma(-pr[u][v], dinv, a[u][v]);
       // owners of column j+1 publish it into the other buffer
       if (jj < 15) {
         if (tx == jj + 1) {
@@ -429,7 +437,7 @@ __device__ void role_potrf(const BaParams &p, const SolverBufs &sb, int kk, doub
     return;
   }
   // scale the columns: L[:,j] = col_j / sqrt(d_j);  s_rd[j] = 1 / L[j][j] = sqrt(dinv_j)
-  if (tid < GBA_NB) s_rd[tid] = sqrt(s_dinv[tid]);
+  if (tid < GBA_NB) s_rd[tid] = rsqrt(s_dinv[tid]);
   __syncthreads();
   for (int i = tid; i < GBA_NB2; i += 256) {
     const int r = i >> 6, c = i & 63;
@@ -437,48 +445,57 @@ __device__ void role_potrf(const BaParams &p, const SolverBufs &sb, int kk, doub
   }
   __syncthreads();
   // ---- X = inv(L), blocked by 16 -----------------------------------------------------------
-  // level 0: the four 16x16 diagonal blocks, column c of block B by 4 lanes (64 columns total)
-  {
-    const int c = tid >> 2, part = tid & 3, base = (c >> 4) * 16;
-    for (int i = base; i < base + 16; i++) {
-      double s = 0.0;
-      for (int m = c + part; m < i; m += 4) s += Lo[i][m] * X[m][c];
-      s += __shfl_xor_sync(0xffffffffu, s, 1);
-      s += __shfl_xor_sync(0xffffffffu, s, 2);
-      if (part == 0 && i >= c) X[i][c] = ((i == c ? 1.0 : 0.0) - s) * s_rd[i];
-      __syncwarp();
+  // level 0: the four 16x16 diagonal blocks.  One thread per column, right-looking with the
+  // column's 16 partial results in registers: per step one multiply and 15 INDEPENDENT fmas,
+  // instead of a dot product whose dependent chain grows with the row.
+  if (tid < GBA_NB) {
+    const int c = tid, base = (c >> 4) * 16, cc = c - base;
+    double acc[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) acc[i] = (i == cc) ? 1.0 : 0.0;
+#pragma unroll
+    for (int j = 0; j < 16; j++) {
+      const double xj = acc[j] * s_rd[base + j];
+      X[base + j][c] = xj;
+#pragma unroll
+      for (int i = j + 1; i < 16; i++) acc[i] = fma(-Lo[base + i][base + j], xj, acc[i]);
     }
   }
   __syncthreads();
-  // block rows I = 1..3: T[I][J] = sum_{K=J}^{I-1} L[I][K] X[K][J];  X[I][J] = -X[I][I] T[I][J]
+  // block rows I = 1..3: T[I][J] = sum_{K=J}^{I-1} L[I][K] X[K][J];  X[I][J] = -X[I][I] T[I][J].
+  // Each thread owns up to 3 outputs (same row-in-block rr, columns cl, cl+16, cl+32) and advances
+  // them together with 2 partial sums each, so that 6 independent fma chains are in flight.
 #pragma unroll
   for (int I = 1; I < 4; I++) {
-    constexpr int dummy = 0;
-    (void)dummy;
-    const int ncol = 16 * I;  // columns 0 .. 16 I - 1
-    for (int e = tid; e < 16 * ncol; e += 256) {
-      const int r = 16 * I + e / ncol, c = e % ncol;
-      double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-      for (int m = (c & ~15); m < 16 * I; m += 4) {
-        s0 += Lo[r][m] * X[m][c];
-        s1 += Lo[r][m + 1] * X[m + 1][c];
-        s2 += Lo[r][m + 2] * X[m + 2][c];
-        s3 += Lo[r][m + 3] * X[m + 3][c];
-      }
-      Tm[r - 16 * I][c] = (s0 + s1) + (s2 + s3);
+    const int rr = tid >> 4, cl = tid & 15, r = 16 * I + rr;
+    double s0[3] = {0.0, 0.0, 0.0}, s1[3] = {0.0, 0.0, 0.0};
+    for (int m = 0; m < 16 * I; m += 2) {
+      const double l0 = Lo[r][m], l1 = Lo[r][m + 1];
+#pragma unroll
+      for (int q = 0; q < 3; q++)
+        if (q < I) {  // X[m][c] is zero above its block's diagonal, so starting at m = 0 is harmless
+          s0[q] = fma(l0, X[m][cl + 16 * q], s0[q]);
+          s1[q] = fma(l1, X[m + 1][cl + 16 * q], s1[q]);
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < 3; q++)
+      if (q < I) Tm[rr][cl + 16 * q] = s0[q] + s1[q];
+    __syncthreads();
+    double t0[3] = {0.0, 0.0, 0.0}, t1[3] = {0.0, 0.0, 0.0};
+    for (int m = 0; m < 16; m += 2) {  // X[I][I] is lower triangular: entries right of the diagonal are 0
+      const double x0 = X[r][16 * I + m], x1 = X[r][16 * I + m + 1];
+#pragma unroll
+      for (int q = 0; q < 3; q++)
+        if (q < I) {
+          t0[q] = fma(x0, Tm[m][cl + 16 * q], t0[q]);
+          t1[q] = fma(x1, Tm[m + 1][cl + 16 * q], t1[q]);
+        }
     }
     __syncthreads();
-    for (int e = tid; e < 16 * ncol; e += 256) {
-      const int r = 16 * I + e / ncol, c = e % ncol;
-      double s0 = 0.0, s1 = 0.0;
-      int m = 16 * I;
-      for (; m + 1 <= r; m += 2) {
-        s0 += X[r][m] * Tm[m - 16 * I][c];
-        s1 += X[r][m + 1] * Tm[m + 1 - 16 * I][c];
-      }
-      if (m <= r) s0 += X[r][m] * Tm[m - 16 * I][c];
-      X[r][c] = -(s0 + s1);
-    }
+#pragma unroll
+    for (int q = 0; q < 3; q++)
+      if (q < I) X[r][cl + 16 * q] = -(t0[q] + t1[q]);
     __syncthreads();
   }
   double *XI = sb.invL + (size_t)kk * GBA_NB2;
@@ -493,9 +510,15 @@ __device__ void role_potrf(const BaParams &p, const SolverBufs &sb, int kk, doub
   __syncthreads();
   {
     const int row = tid >> 2, part = tid & 3;
-    double s = 0.0;
-#pragma unroll 4
-    for (int m = part * 16; m < part * 16 + 16; m++) s += X[row][m] * s_v[m];
+    double sa = 0.0, sb_ = 0.0, sc = 0.0, sd = 0.0;
+#pragma unroll
+    for (int m = part * 16; m < part * 16 + 16; m += 4) {
+      sa = fma(X[row][m], s_v[m], sa);
+      sb_ = fma(X[row][m + 1], s_v[m + 1], sb_);
+      sc = fma(X[row][m + 2], s_v[m + 2], sc);
+      sd = fma(X[row][m + 3], s_v[m + 3], sd);
+    }
+    double s = (sa + sb_) + (sc + sd);
     s += __shfl_xor_sync(0xffffffffu, s, 1);
     s += __shfl_xor_sync(0xffffffffu, s, 2);
     if (part == 0) b[row] = s;
@@ -518,19 +541,34 @@ __device__ void role_trsm(const BaParams &p, const SolverBufs &sb, int kk, int a
   load_rows<SLAB>(A, T);
   if (tid < GBA_NB) s_y[tid] = __ldcg(rhs_ptr(p) + kk * GBA_NB + tid);
   __syncthreads();
-  double acc[RPT][4] = {};
-#pragma unroll 8
-  for (int m = 0; m < GBA_NB; m++) {
-    double av[RPT], xv[4];
+  // KS interleaved partial sums per output keep >= 16 independent fp64 fma chains per thread
+  constexpr int KS = (RPT >= 4) ? 1 : 4 / RPT;
+  double part_[KS][RPT][4] = {};
+#pragma unroll 2
+  for (int m = 0; m < GBA_NB; m += KS) {
 #pragma unroll
-    for (int u = 0; u < RPT; u++) av[u] = A[ty + 16 * u][m];
+    for (int ks = 0; ks < KS; ks++) {
+      double av[RPT], xv[4];
 #pragma unroll
-    for (int v = 0; v < 4; v++) xv[v] = X[tx + 16 * v][m];
+      for (int u = 0; u < RPT; u++) av[u] = A[ty + 16 * u][m + ks];
 #pragma unroll
-    for (int u = 0; u < RPT; u++)
+      for (int v = 0; v < 4; v++) xv[v] = X[tx + 16 * v][m + ks];
 #pragma unroll
-      for (int v = 0; v < 4; v++) acc[u][v] += av[u] * xv[v];
+      for (int u = 0; u < RPT; u++)
+#pragma unroll
+        for (int v = 0; v < 4; v++) part_[ks][u][v] = fma(av[u], xv[v], part_[ks][u][v]);
+    }
   }
+  double acc[RPT][4];
+#pragma unroll
+  for (int u = 0; u < RPT; u++)
+#pragma unroll
+    for (int v = 0; v < 4; v++) {
+      double t_ = part_[0][u][v];
+#pragma unroll
+      for (int ks = 1; ks < KS; ks++) t_ += part_[ks][u][v];
+      acc[u][v] = t_;
+    }
   __syncthreads();
 #pragma unroll
   for (int u = 0; u < RPT; u++)
@@ -542,9 +580,15 @@ __device__ void role_trsm(const BaParams &p, const SolverBufs &sb, int kk, int a
   __syncthreads();
   if (tid < SLAB * 4) {
     const int row = tid >> 2, part = tid & 3;
-    double s = 0.0;
-#pragma unroll 4
-    for (int m = part * 16; m < part * 16 + 16; m++) s += A[row][m] * s_y[m];
+    double sa = 0.0, sb_ = 0.0, sc = 0.0, sd = 0.0;
+#pragma unroll
+    for (int m = part * 16; m < part * 16 + 16; m += 4) {
+      sa = fma(A[row][m], s_y[m], sa);
+      sb_ = fma(A[row][m + 1], s_y[m + 1], sb_);
+      sc = fma(A[row][m + 2], s_y[m + 2], sc);
+      sd = fma(A[row][m + 3], s_y[m + 3], sd);
+    }
+    double s = (sa + sb_) + (sc + sd);
     s += __shfl_xor_sync(0xffffffffu, s, 1);
     s += __shfl_xor_sync(0xffffffffu, s, 2);
     if (part == 0) {
@@ -578,19 +622,33 @@ __device__ void role_syrk(const BaParams &p, const SolverBufs &sb, int kk, int a
 #pragma unroll
     for (int v = 0; v < 4; v++) t[u][v] = shared_tile ? 0.0 : __ldcg(T + (ty + 16 * u) * GBA_NB + tx + 16 * v);
   __syncthreads();
-  double acc[RPT][4] = {};
-#pragma unroll 8
-  for (int m = 0; m < GBA_NB; m++) {
-    double x[RPT], y[4];
+  constexpr int KS = (RPT >= 4) ? 1 : 4 / RPT;
+  double part_[KS][RPT][4] = {};
+#pragma unroll 2
+  for (int m = 0; m < GBA_NB; m += KS) {
 #pragma unroll
-    for (int u = 0; u < RPT; u++) x[u] = A[ty + 16 * u][m];
+    for (int ks = 0; ks < KS; ks++) {
+      double x[RPT], y[4];
 #pragma unroll
-    for (int v = 0; v < 4; v++) y[v] = B[tx + 16 * v][m];
+      for (int u = 0; u < RPT; u++) x[u] = A[ty + 16 * u][m + ks];
 #pragma unroll
-    for (int u = 0; u < RPT; u++)
+      for (int v = 0; v < 4; v++) y[v] = B[tx + 16 * v][m + ks];
 #pragma unroll
-      for (int v = 0; v < 4; v++) acc[u][v] += x[u] * y[v];
+      for (int u = 0; u < RPT; u++)
+#pragma unroll
+        for (int v = 0; v < 4; v++) part_[ks][u][v] = fma(x[u], y[v], part_[ks][u][v]);
+    }
   }
+  double acc[RPT][4];
+#pragma unroll
+  for (int u = 0; u < RPT; u++)
+#pragma unroll
+    for (int v = 0; v < 4; v++) {
+      double t_ = part_[0][u][v];
+#pragma unroll
+      for (int ks = 1; ks < KS; ks++) t_ += part_[ks][u][v];
+      acc[u][v] = t_;
+    }
 #pragma unroll
   for (int u = 0; u < RPT; u++)
 #pragma unroll
@@ -718,10 +776,15 @@ __global__ void __launch_bounds__(256) k_back_step(BaParams p, SolverBufs sb, in
     for (int m = 0; m < 16; m++) l[m] = __ldcg(XI + (part * 16 + m) * GBA_NB + col);
     if (tid < GBA_NB) s_x[tid] = __ldcg(rhs + i * GBA_NB + tid);
     __syncthreads();
-    double s = 0.0;
+    double sa = 0.0, sb_ = 0.0, sc = 0.0, sd = 0.0;
 #pragma unroll
-    for (int m = 0; m < 16; m++) s += l[m] * s_x[part * 16 + m];
-    s_part[part][col] = s;
+    for (int m = 0; m < 16; m += 4) {
+      sa = fma(l[m], s_x[part * 16 + m], sa);
+      sb_ = fma(l[m + 1], s_x[part * 16 + m + 1], sb_);
+      sc = fma(l[m + 2], s_x[part * 16 + m + 2], sc);
+      sd = fma(l[m + 3], s_x[part * 16 + m + 3], sd);
+    }
+    s_part[part][col] = (sa + sb_) + (sc + sd);
     __syncthreads();
     if (tid < GBA_NB) rhs[i * GBA_NB + tid] = s_part[0][tid] + s_part[1][tid] + s_part[2][tid] + s_part[3][tid];
     __threadfence();
@@ -741,10 +804,15 @@ __global__ void __launch_bounds__(256) k_back_step(BaParams p, SolverBufs sb, in
   __syncthreads();
   if (tid < GBA_NB) s_x[tid] = __ldcg(rhs + i * GBA_NB + tid);
   __syncthreads();
-  double s = 0.0;
+  double sa = 0.0, sb_ = 0.0, sc = 0.0, sd = 0.0;
 #pragma unroll
-  for (int m = 0; m < 16; m++) s += l[m] * s_x[part * 16 + m];
-  s_part[part][col] = s;
+  for (int m = 0; m < 16; m += 4) {
+    sa = fma(l[m], s_x[part * 16 + m], sa);
+    sb_ = fma(l[m + 1], s_x[part * 16 + m + 1], sb_);
+    sc = fma(l[m + 2], s_x[part * 16 + m + 2], sc);
+    sd = fma(l[m + 3], s_x[part * 16 + m + 3], sd);
+  }
+  s_part[part][col] = (sa + sb_) + (sc + sd);
   __syncthreads();
   if (tid < GBA_NB) rhs[k * GBA_NB + tid] -= s_part[0][tid] + s_part[1][tid] + s_part[2][tid] + s_part[3][tid];
 }
