@@ -372,6 +372,8 @@ __device__ void role_potrf(const BaParams &p, const SolverBufs &sb, int kk, doub
   const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
   double *T = p.sys + (size_t)p.tslot[kk * p.nT + kk] * GBA_NB2;
   if (tid == 0) s_bad = 0;
+  double *b = rhs_ptr(p) + kk * GBA_NB;
+  const double b_pre = (tid < GBA_NB) ? __ldcg(b + tid) : 0.0;  // rhs block, needed only at the end
   double a[4][4];
 #pragma unroll
   for (int u = 0; u < 4; u++)
@@ -397,24 +399,25 @@ __device__ void role_potrf(const BaParams &p, const SolverBufs &sb, int kk, doub
       const double *col = s_col[j & 1];
       const double d = col[j];
       if (!(d > 0.0) || isinf(d)) bad = true;  // SimplicialLLT: NumericalIssue on a non-positive pivot
+      // rows / columns below 16 v0 are finished: only the sub-blocks u, v >= v0 are still live
       double ar[4], ac[4], pr[4][4];
 #pragma unroll
-      for (int u = 0; u < 4; u++) {
+      for (int u = v0; u < 4; u++) {
         ar[u] = col[ty + 16 * u];
         ac[u] = col[tx + 16 * u];
       }
       // the products do not depend on 1/d: they are formed while the reciprocal is in flight
 #pragma unroll
-      for (int u = 0; u < 4; u++)
+      for (int u = v0; u < 4; u++)
 #pragma unroll
-        for (int v = 0; v < 4; v++) pr[u][v] = ar[u] * ac[v];
+        for (int v = v0; v < 4; v++) pr[u][v] = ar[u] * ac[v];
       const double dinv = fast_rcp(d);
       if (tid < GBA_NB) Lo[tid][j] = (tid >= j) ? col[tid] : 0.0;  // unscaled, scaled after the loop
       if (tid == 0) s_dinv[j] = d;  // the pivot itself; exact scaling after the loop
 #pragma unroll
-      for (int u = 0; u < 4; u++)
+      for (int u = v0; u < 4; u++)
 #pragma unroll
-        for (int v = 0; v < 4; v++) a[u][v] = fma(-pr[u][v], dinv, a[u][v]);
+        for (int v = v0; v < 4; v++) a[u][v] = fma(-pr[u][v], dinv, a[u][v]);
       // owners of column j+1 publish it into the other buffer
       if (jj < 15) {
         if (tx == jj + 1) {
@@ -468,34 +471,41 @@ __device__ void role_potrf(const BaParams &p, const SolverBufs &sb, int kk, doub
 #pragma unroll
   for (int I = 1; I < 4; I++) {
     const int rr = tid >> 4, cl = tid & 15, r = 16 * I + rr;
-    double s0[3] = {0.0, 0.0, 0.0}, s1[3] = {0.0, 0.0, 0.0};
-    for (int m = 0; m < 16 * I; m += 2) {
-      const double l0 = Lo[r][m], l1 = Lo[r][m + 1];
+    double s0[3] = {0.0, 0.0, 0.0}, s1[3] = {0.0, 0.0, 0.0}, s2[3] = {0.0, 0.0, 0.0}, s3[3] = {0.0, 0.0, 0.0};
+#pragma unroll 2
+    for (int m = 0; m < 16 * I; m += 4) {
+      const double l0 = Lo[r][m], l1 = Lo[r][m + 1], l2 = Lo[r][m + 2], l3 = Lo[r][m + 3];
 #pragma unroll
       for (int q = 0; q < 3; q++)
         if (q < I) {  // X[m][c] is zero above its block's diagonal, so starting at m = 0 is harmless
           s0[q] = fma(l0, X[m][cl + 16 * q], s0[q]);
           s1[q] = fma(l1, X[m + 1][cl + 16 * q], s1[q]);
+          s2[q] = fma(l2, X[m + 2][cl + 16 * q], s2[q]);
+          s3[q] = fma(l3, X[m + 3][cl + 16 * q], s3[q]);
         }
     }
 #pragma unroll
     for (int q = 0; q < 3; q++)
-      if (q < I) Tm[rr][cl + 16 * q] = s0[q] + s1[q];
+      if (q < I) Tm[rr][cl + 16 * q] = (s0[q] + s1[q]) + (s2[q] + s3[q]);
     __syncthreads();
-    double t0[3] = {0.0, 0.0, 0.0}, t1[3] = {0.0, 0.0, 0.0};
-    for (int m = 0; m < 16; m += 2) {  // X[I][I] is lower triangular: entries right of the diagonal are 0
-      const double x0 = X[r][16 * I + m], x1 = X[r][16 * I + m + 1];
+    double t0[3] = {0.0, 0.0, 0.0}, t1[3] = {0.0, 0.0, 0.0}, t2[3] = {0.0, 0.0, 0.0}, t3[3] = {0.0, 0.0, 0.0};
+#pragma unroll
+    for (int m = 0; m < 16; m += 4) {  // X[I][I] is lower triangular: entries right of the diagonal are 0
+      const double x0 = X[r][16 * I + m], x1 = X[r][16 * I + m + 1], x2 = X[r][16 * I + m + 2],
+                   x3 = X[r][16 * I + m + 3];
 #pragma unroll
       for (int q = 0; q < 3; q++)
         if (q < I) {
           t0[q] = fma(x0, Tm[m][cl + 16 * q], t0[q]);
           t1[q] = fma(x1, Tm[m + 1][cl + 16 * q], t1[q]);
+          t2[q] = fma(x2, Tm[m + 2][cl + 16 * q], t2[q]);
+          t3[q] = fma(x3, Tm[m + 3][cl + 16 * q], t3[q]);
         }
     }
     __syncthreads();
 #pragma unroll
     for (int q = 0; q < 3; q++)
-      if (q < I) X[r][cl + 16 * q] = -(t0[q] + t1[q]);
+      if (q < I) X[r][cl + 16 * q] = -((t0[q] + t1[q]) + (t2[q] + t3[q]));
     __syncthreads();
   }
   double *XI = sb.invL + (size_t)kk * GBA_NB2;
@@ -505,8 +515,7 @@ __device__ void role_potrf(const BaParams &p, const SolverBufs &sb, int kk, doub
     XI[i] = X[r][c];
   }
   // forward substitution of the rhs block
-  double *b = rhs_ptr(p) + kk * GBA_NB;
-  if (tid < GBA_NB) s_v[tid] = __ldcg(b + tid);
+  if (tid < GBA_NB) s_v[tid] = b_pre;
   __syncthreads();
   {
     const int row = tid >> 2, part = tid & 3;
@@ -544,7 +553,7 @@ __device__ void role_trsm(const BaParams &p, const SolverBufs &sb, int kk, int a
   // KS interleaved partial sums per output keep >= 16 independent fp64 fma chains per thread
   constexpr int KS = (RPT >= 4) ? 1 : 4 / RPT;
   double part_[KS][RPT][4] = {};
-#pragma unroll 2
+#pragma unroll 4
   for (int m = 0; m < GBA_NB; m += KS) {
 #pragma unroll
     for (int ks = 0; ks < KS; ks++) {
@@ -624,7 +633,7 @@ __device__ void role_syrk(const BaParams &p, const SolverBufs &sb, int kk, int a
   __syncthreads();
   constexpr int KS = (RPT >= 4) ? 1 : 4 / RPT;
   double part_[KS][RPT][4] = {};
-#pragma unroll 2
+#pragma unroll 4
   for (int m = 0; m < GBA_NB; m += KS) {
 #pragma unroll
     for (int ks = 0; ks < KS; ks++) {
