@@ -161,6 +161,23 @@ def reference_cuda_side_by_side(dev, name="C", reps=5):
         out["config"] = "config %s: %d keyframes / %d edges, %d iterations, device resident" % (
             name, g.n_frames, g.n_edges, g.iters)
         out["speedup"] = out["reference_ms_per_ba_iteration"] / out["libgba_ms_per_ba_iteration"]
+        # frame_distance over all keyframe pairs of the same graph
+        n = g.n_frames
+        gi, gj = torch.meshgrid(torch.arange(n, device=dev), torch.arange(n, device=dev), indexing="ij")
+        gi, gj = gi.reshape(-1).contiguous(), gj.reshape(-1).contiguous()
+        for label, fn in (("reference", ref.frame_distance), ("libgba", droid_backends.frame_distance)):
+            best = None
+            for _ in range(reps + 1):
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                torch.cuda.synchronize()
+                a.record()
+                fn(base[0], base[1], rest[0], gi, gj, 0.3)
+                b.record()
+                torch.cuda.synchronize()
+                ms = a.elapsed_time(b)
+                best = ms if best is None else min(best, ms)
+            out[label + "_frame_distance_ms"] = best
+        out["frame_distance_pairs"] = int(gi.numel())
         return out
     except Exception as e:  # the prebuilt reference is optional evidence
         return {"unavailable": repr(e)[:200]}

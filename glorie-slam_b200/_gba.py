@@ -52,6 +52,8 @@ def lib():
         L.gba_get.argtypes = [vp, ci, vp, ctypes.c_size_t]
         L.gba_edge_blocks_static.argtypes = [vp] * 7 + [ci] * 5 + [vp, vp]
         L.gba_edge_blocks_static.restype = ci
+        L.gba_frame_distance.argtypes = [vp] * 5 + [ci, ci, ci, cf, vp, vp]
+        L.gba_frame_distance.restype = ci
         L.gba_set_timing.argtypes = [vp, ci]
         L.gba_get_timing.argtypes = [vp, ctypes.POINTER(cf), ctypes.POINTER(ci)]
         L.gba_set_timing.restype = ci

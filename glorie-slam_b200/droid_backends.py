@@ -7,10 +7,9 @@ and `disps`, same return value `[dx, dz]` of the last iteration.  Put this direc
 sys.path and `import droid_backends` resolves here; depth_video.py stays unchanged.
 
 The work is done by libgba.so (hand-written sm_100a CUDA behind the C ABI in include/gba.h);
-torch only supplies device memory and the current stream.  The other functions of the
-reference module (frame_distance, projmap, depth_filter, iproj, corr kernels) are outside this
-repository's scope; set GBA_REFERENCE_BACKENDS to a module name to
-forward them.
+torch only supplies device memory and the current stream.  `frame_distance` is provided as well.  The remaining functions of
+the reference module (projmap, depth_filter, iproj, corr kernels) are outside this repository's
+scope; set GBA_REFERENCE_BACKENDS to a module name to forward them.
 """
 from __future__ import annotations
 
@@ -78,6 +77,26 @@ def ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, 
         if dz is not None:
             dz = dz[: _gba.query(ctx).n_depth_frames]
     return [dx, dz]
+
+
+def frame_distance(poses, disps, intrinsics, ii, jj, beta):
+    """Drop-in for the reference's droid_backends.frame_distance (src/lib/droid.cpp:122-135,
+    src/lib/droid_kernels.cu:518-657): mean induced flow of every keyframe pair (ii[n] -> jj[n]),
+    1000 where fewer than 75 % of the pixels stay in front of the target camera.  Returns [num] f32."""
+    for t, n in ((poses, "poses"), (disps, "disps"), (intrinsics, "intrinsics")):
+        _chk(t, n, torch.float32)
+    _chk(ii, "ii", torch.int64)
+    _chk(jj, "jj", torch.int64)
+    _, ht, wd = disps.shape
+    num = int(ii.shape[0])
+    dev = poses.device
+    dist = torch.zeros((num,), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        rc = _gba.lib().gba_frame_distance(poses.data_ptr(), disps.data_ptr(), intrinsics.data_ptr(), ii.data_ptr(),
+                                           jj.data_ptr(), num, ht, wd, float(beta), dist.data_ptr(),
+                                           torch.cuda.current_stream(dev).cuda_stream)
+        _gba.check(None, rc)
+    return dist
 
 
 def __getattr__(name):

@@ -80,3 +80,30 @@ def BA(target, weight, eta, poses, disps, intrinsics, ii, jj, sensor_disps=None,
                                None, None, torch.cuda.current_stream(dev).cuda_stream)
         _gba.check(ctx, rc)
     return _rewrap(poses, p7[None]), d[None]
+
+
+def MoBA(target, weight, eta, poses, disps, intrinsics, ii, jj, fixedp=1, rig=1):
+    """Motion-only bundle adjustment with the reference's semantics (src/geom/ba.py:223-271:
+    block_solve with its default damping ep = 0.1, lm = 1e-4, src/geom/chol.py:44-55)."""
+    if rig != 1:
+        raise NotImplementedError("rig != 1 is not used by GlORIE-SLAM")
+    pd = _data(poses)
+    B, N, ht, wd = disps.shape
+    dev = disps.device
+    E = int(ii.shape[0])
+    f32 = lambda t: t.to(device=dev, dtype=torch.float32).contiguous()
+    tg = f32(target).view(E, ht, wd, 2).permute(0, 3, 1, 2).contiguous()
+    wg = f32(weight).view(E, ht, wd, 2).permute(0, 3, 1, 2).contiguous()
+    p7, d = f32(pd[0]).clone(), f32(disps[0]).clone()
+    sens = torch.zeros_like(d)
+    intr = f32(intrinsics[0, 0])
+    dummy_eta = torch.zeros((1, ht, wd), dtype=torch.float32, device=dev)
+    iic, jjc = ii.to(device=dev, dtype=torch.int64).contiguous(), jj.to(device=dev, dtype=torch.int64).contiguous()
+    with torch.cuda.device(dev):
+        ctx = _gba.context(dev.index, N, E, ht, wd)
+        rc = _gba.lib().gba_ba(ctx, p7.data_ptr(), d.data_ptr(), intr.data_ptr(), sens.data_ptr(), tg.data_ptr(),
+                               wg.data_ptr(), dummy_eta.data_ptr(), iic.data_ptr(), jjc.data_ptr(), N, E, 1,
+                               int(fixedp), N, 1, 1e-4, 0.1, 1, 0, _gba.MODE_GEOM_PY, None, None,
+                               torch.cuda.current_stream(dev).cuda_stream)
+        _gba.check(ctx, rc)
+    return _rewrap(poses, p7[None])

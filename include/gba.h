@@ -152,6 +152,16 @@ int gba_get(gba_ctx *ctx, int what, void *dst, size_t bytes);
 int gba_set_timing(gba_ctx *ctx, int enable);
 int gba_get_timing(gba_ctx *ctx, float *ms /* [GBA_N_STAGES] */, int *launches /* [GBA_N_STAGES] */);
 
+/* ---- frame_distance -------------------------------------------------
+ * Replaces droid_backends.frame_distance (src/lib/droid.cpp:122-135 ->
+ * src/lib/droid_kernels.cu:518-657,1441-1463): for every pair (ii[n] -> jj[n]) the mean
+ * induced-flow magnitude, beta * full relative motion + (1 - beta) * translation only, over
+ * the pixels that land in front of the target camera; 1000 when fewer than 75 % do.
+ * poses [*,7], disps [*,ht,wd], intrinsics [4], ii/jj [n_pairs] int64, dist [n_pairs] out;
+ * device pointers, asynchronous on `stream`, needs no gba_ctx.  wd must be a multiple of 4. */
+int gba_frame_distance(const float *poses, const float *disps, const float *intrinsics, const int64_t *ii,
+                       const int64_t *jj, int n_pairs, int ht, int wd, float beta, float *dist, void *stream);
+
 /* ---- per-edge pose blocks for callers that cannot allocate --------------------------------
  * No counterpart in the reference: there, these numbers only exist inside ba_cuda.
  *

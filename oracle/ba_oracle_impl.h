@@ -712,6 +712,49 @@ int FN(oracle_dspo)(const REAL *poses, REAL *disps, const float *intr_f, const f
   return M;
 }
 
+/*
+ * frame_distance: mean induced-flow magnitude between keyframe pairs, beta-mix of the full
+ * relative motion and its translation-only part; 1000 when fewer than 75 % of the pixels land in
+ * front of the target camera.  src/lib/droid_kernels.cu:518-657 (frame_distance_kernel),
+ * called from src/depth_video.py:166-196 and src/factor_graph.py:323-462.
+ */
+int FN(oracle_frame_distance)(const REAL *poses, const REAL *disps, const float *intr_f, const int64_t *ii,
+                              const int64_t *jj, int n_pairs, int ht, int wd, float beta_f, REAL *dist) {
+  const int HW = ht * wd;
+  const REAL fx = (REAL)intr_f[0], fy = (REAL)intr_f[1], cx = (REAL)intr_f[2], cy = (REAL)intr_f[3];
+  const REAL beta = (REAL)beta_f;
+  int n;
+#pragma omp parallel for schedule(dynamic, 16)
+  for (n = 0; n < n_pairs; n++) {
+    const int ix = (int)ii[n], jx = (int)jj[n];
+    REAL tij[3], qij[4];
+    double accum = 0, valid = 0, total = 0;
+    int k;
+    FN(rel_se3)(poses + 7 * ix, poses + 7 * ix + 3, poses + 7 * jx, poses + 7 * jx + 3, tij, qij);
+    for (k = 0; k < HW; k++) {
+      const REAL u = (REAL)(k % wd), v = (REAL)(k / wd);
+      REAL Xi[4], Xj[3], du, dv, d;
+      Xi[0] = (u - cx) / fx; Xi[1] = (v - cy) / fy; Xi[2] = 1; Xi[3] = disps[(size_t)ix * HW + k];
+      FN(act_so3)(qij, Xi, Xj);  /* actSE3 */
+      Xj[0] += Xi[3] * tij[0]; Xj[1] += Xi[3] * tij[1]; Xj[2] += Xi[3] * tij[2];
+      du = fx * (Xj[0] / Xj[2]) + cx - u;
+      dv = fy * (Xj[1] / Xj[2]) + cy - v;
+      d = (REAL)sqrt((double)(du * du + dv * dv));
+      total += (double)beta;
+      if (Xj[2] > (REAL)0.25) { accum += (double)(beta * d); valid += (double)beta; }
+      /* translation only (droid_kernels.cu:611-628) */
+      Xj[0] = Xi[0] + Xi[3] * tij[0]; Xj[1] = Xi[1] + Xi[3] * tij[1]; Xj[2] = Xi[2] + Xi[3] * tij[2];
+      du = fx * (Xj[0] / Xj[2]) + cx - u;
+      dv = fy * (Xj[1] / Xj[2]) + cy - v;
+      d = (REAL)sqrt((double)(du * du + dv * dv));
+      total += (double)((REAL)1 - beta);
+      if (Xj[2] > (REAL)0.25) { accum += (double)(((REAL)1 - beta) * d); valid += (double)((REAL)1 - beta); }
+    }
+    dist[n] = (valid / (total + 1e-8) < 0.75) ? (REAL)1000.0 : (REAL)(accum / valid);
+  }
+  return 0;
+}
+
 #undef FN
 #undef FN1
 #undef FN2

@@ -127,3 +127,20 @@ def dspo(poses, disps, intrinsics, targets, weights, eta, ii, jj, mono_disps, sc
            ctypes.c_int(ignore_frames), ctypes.c_float(lm), ctypes.c_float(ep), ctypes.c_float(alpha),
            ctypes.c_int(int(interleaved)), _p(dz), _p(dwq), ctypes.byref(fail))
     return SimpleNamespace(disps=disps_o, scales=sc, shifts=sh, dz=dz[:M], dwq=dwq[:M], M=M, fail=fail.value)
+
+
+def frame_distance(poses, disps, intrinsics, ii, jj, beta=0.3, precision="f32"):
+    """reference droid_backends.frame_distance (src/lib/droid_kernels.cu:518-657,1441-1463) on numpy arrays"""
+    real = np.float32 if precision == "f32" else np.float64
+    fn = getattr(lib(), "oracle_frame_distance_" + precision)
+    fn.restype = ctypes.c_int
+    N, ht, wd = disps.shape
+    po = np.ascontiguousarray(poses, dtype=real)
+    di = np.ascontiguousarray(disps, dtype=real)
+    intr = np.ascontiguousarray(intrinsics, dtype=np.float32)
+    ii64 = np.ascontiguousarray(ii, dtype=np.int64)
+    jj64 = np.ascontiguousarray(jj, dtype=np.int64)
+    out = np.zeros((ii64.shape[0],), dtype=real)
+    fn(_p(po), _p(di), _p(intr), _p(ii64), _p(jj64), ctypes.c_int(ii64.shape[0]), ctypes.c_int(ht), ctypes.c_int(wd),
+       ctypes.c_float(beta), _p(out))
+    return out

@@ -356,6 +356,68 @@ def test_full_size_properties(name):
     assert rel(r3.poses, r.poses) < 1e-5 and rel(r3.disps, r.disps) < 1e-5
 
 
+# ------------------------------------------------------------------------------------------
+# frame_distance
+# ------------------------------------------------------------------------------------------
+def _load_reference_so():
+    import importlib.util
+    import os
+
+    from helpers import ROOT
+
+    so = os.path.join(ROOT, "oracle", "_ref", "ref_droid_backends.so")
+    if not os.path.exists(so):
+        return None
+    spec = importlib.util.spec_from_file_location("ref_droid_backends", so)
+    ref = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ref)
+    return ref
+
+
+@pytest.mark.parametrize("name,hw", [("A", None), ("R", None), ("C", None)])
+def test_frame_distance_matches_oracle_and_reference(name, hw):
+    import droid_backends
+
+    g = small_graphs()[name] if name != "C" else synth.make_config("C")
+    n = g.n_frames
+    ii, jj = np.meshgrid(np.arange(n), np.arange(n), indexing="ij")
+    ii, jj = ii.reshape(-1), jj.reshape(-1)
+    poses = g.poses.copy()
+    poses[n // 2, 3:] = [0.0, 1.0, 0.0, 0.0]  # one keyframe looks the other way: its pairs return 1000
+    want = oracle.frame_distance(poses, g.disps, g.intrinsics, ii, jj, 0.3, precision="f64")
+    d = to_dev(g)
+    tp = torch.from_numpy(poses).cuda()
+    ti, tj = torch.from_numpy(ii).cuda(), torch.from_numpy(jj).cuda()
+    for a, b in ((ti, tj), (tj, ti)):  # the reference calls it both ways (depth_video.py:181-188)
+        got = droid_backends.frame_distance(tp, d.disps, d.intr, a, b, 0.3).cpu().numpy()
+        w = want if a is ti else oracle.frame_distance(poses, g.disps, g.intrinsics, jj, ii, 0.3, precision="f64")
+        np.testing.assert_array_equal(got == 1000.0, w == 1000.0)
+        assert (w == 1000.0).sum() >= n - 1
+        ok = w != 1000.0
+        np.testing.assert_allclose(got[ok], w[ok], rtol=1e-4, atol=1e-4)
+    ref = _load_reference_so()
+    if ref is not None:
+        r = ref.frame_distance(tp, d.disps, d.intr, ti, tj, 0.3).cpu().numpy()
+        got = droid_backends.frame_distance(tp, d.disps, d.intr, ti, tj, 0.3).cpu().numpy()
+        np.testing.assert_array_equal(got == 1000.0, r == 1000.0)
+        ok = r != 1000.0
+        np.testing.assert_allclose(got[ok], r[ok], rtol=1e-4, atol=1e-4)
+
+
+def test_moba_mirror_matches_oracle():
+    import geom_ba
+
+    g = small_graphs()["R"]
+    o = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj, g.t0, g.t1,
+                  1, 1e-4, 0.1, motion_only=True, mode=oracle.MODE_GEOM_PY, precision="f64")
+    d = to_dev(g)
+    target = d.targets.permute(0, 2, 3, 1).contiguous()[None]
+    weight = d.weights.permute(0, 2, 3, 1).contiguous()[None]
+    poses = geom_ba.MoBA(target, weight, None, d.poses[None], d.disps[None], d.intr[None, None].repeat(1, g.n_frames, 1),
+                         d.ii, d.jj, fixedp=g.t0)
+    assert rel(sign_normalise(poses[0].cpu().numpy()), sign_normalise(o.poses)) < STATE_RTOL
+
+
 def test_reference_cuda_backend_if_present():
     """On the B200 box: the reference's own droid_backends.ba (oracle/_ref, built by
     oracle/build_ref.py from the unmodified sources) against libgba on configs A, R and B."""

@@ -99,3 +99,18 @@ def test_non_spd_gives_zero_update():
     assert o.fail == 1
     np.testing.assert_array_equal(o.dx, 0)
     np.testing.assert_array_equal(o.poses, g.poses)
+
+
+def test_frame_distance_oracle_basics():
+    """droid_kernels.cu:518-657: zero on the diagonal, positive elsewhere, 1000 when the target looks away"""
+    g = synth.make_graph(6, 10, 1, seed=4, ht=16, wd=24)
+    ii, jj = np.meshgrid(np.arange(6), np.arange(6), indexing="ij")
+    d = oracle.frame_distance(g.poses, g.disps, g.intrinsics, ii.reshape(-1), jj.reshape(-1), 0.3).reshape(6, 6)
+    np.testing.assert_allclose(np.diag(d), 0.0, atol=1e-4)
+    assert (d[~np.eye(6, dtype=bool)] > 0).all() and (d < 1000).all()
+    poses = g.poses.copy()
+    poses[3, 3:] = [0.0, 1.0, 0.0, 0.0]  # 180 degrees about y: everything ends up behind camera 3
+    d2 = oracle.frame_distance(poses, g.disps, g.intrinsics, np.array([0]), np.array([3]), 0.3)
+    assert d2[0] == 1000.0
+    d64 = oracle.frame_distance(g.poses, g.disps, g.intrinsics, ii.reshape(-1), jj.reshape(-1), 0.3, precision="f64")
+    assert rel(d.reshape(-1), d64) < 1e-5
