@@ -178,6 +178,36 @@ def reference_cuda_side_by_side(dev, name="C", reps=5):
                 best = ms if best is None else min(best, ms)
             out[label + "_frame_distance_ms"] = best
         out["frame_distance_pairs"] = int(gi.numel())
+        # depth_filter over every keyframe + the torch form of align_scale_and_shift
+        import common
+
+        ix = torch.arange(n, device=dev)
+        th = (0.05 / base[1].mean(dim=(1, 2))).contiguous()
+
+        def torch_align(p, t_, w):  # src/utils/common.py:402-438 verbatim semantics, the reference's own torch ops
+            a00, a01, a11 = (w * p * p).sum((1, 2)), (w * p).sum((1, 2)), w.sum((1, 2))
+            b0, b1 = (w * p * t_).sum((1, 2)), (w * t_).sum((1, 2))
+            det = a00 * a11 - a01 * a01
+            s_, q_ = (a11 * b0 - a01 * b1) / det, (-a01 * b0 + a00 * b1) / det
+            e_ = ((s_[:, None, None] * p + q_[:, None, None] - t_).abs() * w).sum((1, 2)) / a11
+            return s_, q_, e_
+
+        wts = (base[1] > base[1].median()).float()
+        for key, fn in (("reference_depth_filter_ms", lambda: ref.depth_filter(base[0], base[1], rest[0], ix, th)),
+                        ("libgba_depth_filter_ms", lambda: droid_backends.depth_filter(base[0], base[1], rest[0], ix, th)),
+                        ("torch_align_scale_shift_ms", lambda: torch_align(rest[1], base[1], wts)),
+                        ("libgba_align_scale_shift_ms", lambda: common.align_scale_and_shift(rest[1], base[1], wts))):
+            best = None
+            for _ in range(reps + 1):
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                torch.cuda.synchronize()
+                a.record()
+                fn()
+                b.record()
+                torch.cuda.synchronize()
+                ms = a.elapsed_time(b)
+                best = ms if best is None else min(best, ms)
+            out[key] = best
         return out
     except Exception as e:  # the prebuilt reference is optional evidence
         return {"unavailable": repr(e)[:200]}

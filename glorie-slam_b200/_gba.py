@@ -54,6 +54,10 @@ def lib():
         L.gba_edge_blocks_static.restype = ci
         L.gba_frame_distance.argtypes = [vp] * 5 + [ci, ci, ci, cf, vp, vp]
         L.gba_frame_distance.restype = ci
+        L.gba_depth_filter.argtypes = [vp] * 5 + [ci, ci, ci, ci, vp, vp]
+        L.gba_depth_filter.restype = ci
+        L.gba_align_scale_shift.argtypes = [vp] * 3 + [ci, ci, ci, vp, vp, vp, vp]
+        L.gba_align_scale_shift.restype = ci
         L.gba_set_timing.argtypes = [vp, ci]
         L.gba_get_timing.argtypes = [vp, ctypes.POINTER(cf), ctypes.POINTER(ci)]
         L.gba_set_timing.restype = ci

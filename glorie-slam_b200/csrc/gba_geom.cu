@@ -1,7 +1,12 @@
-// gba_geom.cu -- geometry helpers next to the BA hot path:
-// frame_distance, the O(n^2) keyframe-proximity metric that runs before every global BA
-// (reference src/lib/droid_kernels.cu:518-657,1441-1463; callers src/depth_video.py:166-196,
-// src/factor_graph.py:323-462).  Context-free: no workspace, asynchronous on the given stream.
+// gba_geom.cu -- geometry helpers next to the BA hot path, all context-free
+// (no workspace) and asynchronous on the given stream:
+//  rank 1: frame_distance, the O(n^2) keyframe-proximity metric that runs before every global BA
+//          (reference src/lib/droid_kernels.cu:518-657,1441-1463; callers src/depth_video.py:166-196,
+//          src/factor_graph.py:323-462);
+//  rank 2: depth_filter, the multi-view consistency count behind the DSPO valid-depth mask
+//          (src/lib/droid_kernels.cu:661-775,1494-1518; caller src/depth_video.py:326-361), and
+//          align_scale_shift, the per-keyframe weighted scale/shift fit of the mono prior
+//          (src/utils/common.py:402-438; callers src/depth_video.py:233,308).
 #include <cuda_runtime.h>
 #include <stdio.h>
 
@@ -149,5 +154,183 @@ extern "C" int gba_frame_distance(const float *poses, const float *disps, const 
   else return fail_geom(GBA_ECAPACITY, "ht*wd larger than 8192 pixels is not supported");
   const cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail_geom(GBA_ECUDA, cudaGetErrorString(e));
+  return GBA_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// depth_filter
+// ---------------------------------------------------------------------------------------------
+#define DF_NT 256
+
+// One thread per pixel of a listed keyframe; it visits the 6 neighbouring keyframes itself and keeps
+// the count in a register.  The reference launches one CTA per (keyframe, neighbour, pixel block) and
+// bumps the count with a global atomicAdd; here the counter is written once, needs no zero-fill and
+// the source disparity is read once instead of six times.  Arithmetic follows the reference step by
+// step (quaternion sandwich, true divisions, agreement test in double) because the result is a
+// thresholded decision: a different rounding would flip borderline pixels.
+__global__ void __launch_bounds__(DF_NT) k_depth_filter(const float *__restrict__ poses, const float *__restrict__ disps,
+                                                        const float *__restrict__ intr,
+                                                        const int64_t *__restrict__ inds,
+                                                        const float *__restrict__ thresh, int n_frames, int ht, int wd,
+                                                        float *__restrict__ counter) {
+  __shared__ float s_rel[6][8];  // t[3], q[4], valid
+  const int HW = ht * wd, b = blockIdx.y, tid = threadIdx.x;
+  const int ix = (int)inds[b];
+  if (tid < 6) {
+    const int jx = (tid < 3) ? ix - tid - 1 : ix + tid;  // droid_kernels.cu:696
+    const bool ok = jx >= 0 && jx < n_frames;
+    s_rel[tid][7] = ok ? 1.f : 0.f;
+    if (ok) {
+      const float *Pi = poses + 7 * (size_t)ix, *Pj = poses + 7 * (size_t)jx, *qi = Pi + 3, *qj = Pj + 3;
+      float qq[4];
+      qq[0] = -qj[3] * qi[0] + qj[0] * qi[3] - qj[1] * qi[2] + qj[2] * qi[1];
+      qq[1] = -qj[3] * qi[1] + qj[1] * qi[3] - qj[2] * qi[0] + qj[0] * qi[2];
+      qq[2] = -qj[3] * qi[2] + qj[2] * qi[3] - qj[0] * qi[1] + qj[1] * qi[0];
+      qq[3] = qj[3] * qi[3] + qj[0] * qi[0] + qj[1] * qi[1] + qj[2] * qi[2];
+      const float uv0 = 2.f * (qq[1] * Pi[2] - qq[2] * Pi[1]);
+      const float uv1 = 2.f * (qq[2] * Pi[0] - qq[0] * Pi[2]);
+      const float uv2 = 2.f * (qq[0] * Pi[1] - qq[1] * Pi[0]);
+      s_rel[tid][0] = Pj[0] - (Pi[0] + qq[3] * uv0 + (qq[1] * uv2 - qq[2] * uv1));
+      s_rel[tid][1] = Pj[1] - (Pi[1] + qq[3] * uv1 + (qq[2] * uv0 - qq[0] * uv2));
+      s_rel[tid][2] = Pj[2] - (Pi[2] + qq[3] * uv2 + (qq[0] * uv1 - qq[1] * uv0));
+      s_rel[tid][3] = qq[0]; s_rel[tid][4] = qq[1]; s_rel[tid][5] = qq[2]; s_rel[tid][6] = qq[3];
+    }
+  }
+  __syncthreads();
+  const int k = blockIdx.x * DF_NT + tid;
+  if (k >= HW) return;
+  const float fx = intr[0], fy = intr[1], cx = intr[2], cy = intr[3];
+  const int i = k / wd, j = k - i * wd;
+  const float X0 = ((float)j - cx) / fx, X1 = ((float)i - cy) / fy, d = disps[(size_t)ix * HW + k];
+  const double t = (double)thresh[b];
+  int count = 0;
+#pragma unroll 1
+  for (int nb = 0; nb < 6; nb++) {
+    if (s_rel[nb][7] == 0.f) continue;
+    const int jx = (nb < 3) ? ix - nb - 1 : ix + nb;
+    const float qx = s_rel[nb][3], qy = s_rel[nb][4], qz = s_rel[nb][5], qw = s_rel[nb][6];
+    // Y = X + w * uv + q x uv,  uv = 2 q x X  with X = (X0, X1, 1)   (actSO3, lietorch so3 sandwich)
+    const float uvx = 2.f * (qy * 1.f - qz * X1), uvy = 2.f * (qz * X0 - qx * 1.f), uvz = 2.f * (qx * X1 - qy * X0);
+    float Yx = X0 + qw * uvx + (qy * uvz - qz * uvy);
+    float Yy = X1 + qw * uvy + (qz * uvx - qx * uvz);
+    float Yz = 1.f + qw * uvz + (qx * uvy - qy * uvx);
+    Yx += d * s_rel[nb][0]; Yy += d * s_rel[nb][1]; Yz += d * s_rel[nb][2];
+    const float uj = fx * (Yx / Yz) + cx, vj = fy * (Yy / Yz) + cy, dj = d / Yz;
+    if (!(uj > -1e8f && uj < 1e8f && vj > -1e8f && vj < 1e8f)) continue;
+    const int u0 = (int)floorf(uj), v0 = (int)floorf(vj);
+    if (u0 >= 0 && v0 >= 0 && u0 < wd - 1 && v0 < ht - 1) {
+      const float *dp = disps + (size_t)jx * HW + v0 * wd + u0;
+      const float d00 = dp[0], d01 = dp[1], d10 = dp[wd], d11 = dp[wd + 1];
+      const double inv = 1.0 / (double)dj;
+      if (fabs(inv - 1.0 / (double)d00) < t || fabs(inv - 1.0 / (double)d01) < t ||
+          fabs(inv - 1.0 / (double)d10) < t || fabs(inv - 1.0 / (double)d11) < t)
+        count++;
+    }
+  }
+  counter[(size_t)b * HW + k] = (float)count;
+}
+
+extern "C" int gba_depth_filter(const float *poses, const float *disps, const float *intrinsics, const int64_t *inds,
+                                const float *thresh, int n_frames, int n_inds, int ht, int wd, float *counter,
+                                void *stream) {
+  if (n_inds == 0) return GBA_OK;  // empty index list: nothing to write (torch hands out NULL for empty tensors)
+  if (!poses || !disps || !intrinsics || !inds || !thresh || !counter) {
+    snprintf(g_create_err, sizeof(g_create_err), "gba_depth_filter: NULL array argument");
+    return GBA_EINVAL;
+  }
+  if (n_frames < 1 || n_inds < 0 || ht < 2 || wd < 2 || n_inds > 65535) {
+    snprintf(g_create_err, sizeof(g_create_err), "gba_depth_filter: bad sizes (n_inds <= 65535, ht, wd >= 2)");
+    return GBA_EINVAL;
+  }
+  if (n_inds == 0) return GBA_OK;
+  const dim3 grid((ht * wd + DF_NT - 1) / DF_NT, n_inds);
+  k_depth_filter<<<grid, DF_NT, 0, (cudaStream_t)stream>>>(poses, disps, intrinsics, inds, thresh, n_frames, ht, wd,
+                                                           counter);
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    snprintf(g_create_err, sizeof(g_create_err), "gba_depth_filter: %s", cudaGetErrorString(e));
+    return GBA_ECUDA;
+  }
+  return GBA_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// align_scale_shift
+// ---------------------------------------------------------------------------------------------
+#define AS_NT 256
+
+template <int NS>
+__device__ __forceinline__ void block_sum(double (&v)[NS], double (*s_red)[NS]) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int c = 0; c < NS; c++)
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) v[c] += __shfl_xor_sync(0xffffffffu, v[c], o);
+  __syncthreads();
+  if (lane == 0)
+#pragma unroll
+    for (int c = 0; c < NS; c++) s_red[warp][c] = v[c];
+  __syncthreads();
+#pragma unroll
+  for (int c = 0; c < NS; c++) {
+    double a = 0.0;
+#pragma unroll
+    for (int w = 0; w < AS_NT / 32; w++) a += s_red[w][c];
+    v[c] = a;
+  }
+}
+
+// One CTA per keyframe: five weighted sums, the 2x2 solve, then the weighted mean |residual| of the
+// fit from the same (L1/L2-hot) rows.  The reference makes ~15 torch reductions over full-size
+// temporaries for this; float32 partial sums per thread, combined in double.
+__global__ void __launch_bounds__(AS_NT) k_align_scale_shift(const float *__restrict__ pred,
+                                                             const float *__restrict__ target,
+                                                             const float *__restrict__ weights, int HW,
+                                                             float *__restrict__ scale, float *__restrict__ shift,
+                                                             float *__restrict__ err) {
+  __shared__ double s_red[AS_NT / 32][5];
+  const size_t base = (size_t)blockIdx.x * HW;
+  const float *p = pred + base, *t = target + base, *w = weights + base;
+  float a[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+  for (int k = threadIdx.x; k < HW; k += AS_NT) {
+    const float pk = p[k], tk = t[k], wk = w[k], wp = wk * pk;
+    a[0] = fmaf(wp, pk, a[0]); a[1] += wp; a[2] += wk; a[3] = fmaf(wp, tk, a[3]); a[4] = fmaf(wk, tk, a[4]);
+  }
+  double v[5];
+#pragma unroll
+  for (int c = 0; c < 5; c++) v[c] = (double)a[c];
+  block_sum<5>(v, s_red);
+  const double det = v[0] * v[2] - v[1] * v[1];
+  const float s = (float)((v[2] * v[3] - v[1] * v[4]) / det), q = (float)((-v[1] * v[3] + v[0] * v[4]) / det);
+  float e = 0.f;
+  for (int k = threadIdx.x; k < HW; k += AS_NT) e = fmaf(fabsf(fmaf(s, p[k], q) - t[k]), w[k], e);
+  double ev[5] = {(double)e, 0.0, 0.0, 0.0, 0.0};
+  block_sum<5>(ev, s_red);
+  if (threadIdx.x == 0) {
+    scale[blockIdx.x] = s;
+    shift[blockIdx.x] = q;
+    err[blockIdx.x] = (float)(ev[0] / v[2]);
+  }
+}
+
+extern "C" int gba_align_scale_shift(const float *prediction, const float *target, const float *weights, int n, int ht,
+                                     int wd, float *scale, float *shift, float *avg_error, void *stream) {
+  if (n == 0) return GBA_OK;
+  if (!prediction || !target || !weights || !scale || !shift || !avg_error) {
+    snprintf(g_create_err, sizeof(g_create_err), "gba_align_scale_shift: NULL array argument");
+    return GBA_EINVAL;
+  }
+  if (n < 0 || ht < 1 || wd < 1) {
+    snprintf(g_create_err, sizeof(g_create_err), "gba_align_scale_shift: bad sizes");
+    return GBA_EINVAL;
+  }
+  if (n == 0) return GBA_OK;
+  k_align_scale_shift<<<n, AS_NT, 0, (cudaStream_t)stream>>>(prediction, target, weights, ht * wd, scale, shift,
+                                                             avg_error);
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    snprintf(g_create_err, sizeof(g_create_err), "gba_align_scale_shift: %s", cudaGetErrorString(e));
+    return GBA_ECUDA;
+  }
   return GBA_OK;
 }

@@ -99,10 +99,32 @@ def frame_distance(poses, disps, intrinsics, ii, jj, beta):
     return dist
 
 
+def depth_filter(poses, disps, intrinsics, ix, thresh):
+    """Drop-in for the reference's droid_backends.depth_filter (src/lib/droid.cpp:138-146,
+    src/lib/droid_kernels.cu:661-775,1494-1518; caller src/depth_video.py:349): per listed keyframe and
+    pixel, the number of neighbouring keyframes (ix-1,-2,-3,+3,+4,+5) whose depth agrees with the
+    reprojection within thresh.  Returns counter [len(ix), ht, wd] f32."""
+    for t, n in ((poses, "poses"), (disps, "disps"), (intrinsics, "intrinsics"), (thresh, "thresh")):
+        _chk(t, n, torch.float32)
+    _chk(ix, "ix", torch.int64)
+    n_frames, ht, wd = disps.shape
+    num = int(ix.shape[0])
+    if int(thresh.shape[0]) != num:
+        raise ValueError("thresh must hold one value per entry of ix")
+    dev = poses.device
+    counter = torch.empty((num, ht, wd), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        rc = _gba.lib().gba_depth_filter(poses.data_ptr(), disps.data_ptr(), intrinsics.data_ptr(), ix.data_ptr(),
+                                         thresh.data_ptr(), n_frames, num, ht, wd, counter.data_ptr(),
+                                         torch.cuda.current_stream(dev).cuda_stream)
+        _gba.check(None, rc)
+    return counter
+
+
 def __getattr__(name):
     fwd = os.environ.get("GBA_REFERENCE_BACKENDS")
     if fwd:
         return getattr(importlib.import_module(fwd), name)
     raise AttributeError(
-        "droid_backends.%s is outside the B200 hot path (only `ba` is provided); set GBA_REFERENCE_BACKENDS "
+        "droid_backends.%s is outside the B200 hot path (only `ba`, `frame_distance` and `depth_filter` are provided); set GBA_REFERENCE_BACKENDS "
         "to the reference extension's module name to forward it" % name)

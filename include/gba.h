@@ -162,6 +162,28 @@ int gba_get_timing(gba_ctx *ctx, float *ms /* [GBA_N_STAGES] */, int *launches /
 int gba_frame_distance(const float *poses, const float *disps, const float *intrinsics, const int64_t *ii,
                        const int64_t *jj, int n_pairs, int ht, int wd, float beta, float *dist, void *stream);
 
+/* ---- depth_filter ---------------------------------------------------
+ * Replaces droid_backends.depth_filter (src/lib/droid.cpp:138-146 ->
+ * src/lib/droid_kernels.cu:661-775,1494-1518; caller src/depth_video.py:326-361): for every
+ * listed keyframe inds[b] and pixel, how many of the 6 neighbouring keyframes (inds[b]-1,-2,-3,
+ * +3,+4,+5, those inside [0, n_frames)) hold, at one of the 4 pixels around the reprojection,
+ * a depth within thresh[b] of the reprojected one.  counter [n_inds,ht,wd] is fully written
+ * (values 0..6 as float, like the reference's float counter); it need not be zeroed.
+ * poses [n_frames,7], disps [n_frames,ht,wd], intrinsics [4], inds [n_inds] int64,
+ * thresh [n_inds]; device pointers, asynchronous on `stream`, needs no gba_ctx. */
+int gba_depth_filter(const float *poses, const float *disps, const float *intrinsics, const int64_t *inds,
+                     const float *thresh, int n_frames, int n_inds, int ht, int wd, float *counter, void *stream);
+
+/* ---- align_scale_shift ----------------------------------------------
+ * Replaces src/utils/common.py:402-438 align_scale_and_shift (callers src/depth_video.py:233,
+ * 308): per keyframe b the weighted least-squares fit  min sum w (scale*prediction + shift -
+ * target)^2  and the weighted mean absolute residual of that fit.  prediction/target/weights
+ * [n,ht,wd] float32; scale/shift/avg_error [n] out.  A keyframe whose weights make the 2x2
+ * normal matrix singular yields inf/nan exactly like the reference's division by det = 0.
+ * Device pointers, asynchronous on `stream`, needs no gba_ctx. */
+int gba_align_scale_shift(const float *prediction, const float *target, const float *weights, int n, int ht, int wd,
+                          float *scale, float *shift, float *avg_error, void *stream);
+
 /* ---- per-edge pose blocks for callers that cannot allocate --------------------------------
  * No counterpart in the reference: there, these numbers only exist inside ba_cuda.
  *

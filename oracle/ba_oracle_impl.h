@@ -755,6 +755,81 @@ int FN(oracle_frame_distance)(const REAL *poses, const REAL *disps, const float 
   return 0;
 }
 
+/*
+ * depth_filter: for every listed keyframe and pixel, the number of the 6 neighbouring keyframes
+ * (ix-1, ix-2, ix-3, ix+3, ix+4, ix+5) whose disparity map agrees with the reprojected depth at one
+ * of the 4 pixels around the reprojection.  src/lib/droid_kernels.cu:661-775,1494-1518; caller
+ * src/depth_video.py:326-361 (update_valid_depth_mask).  The comparisons are done in double like
+ * the reference (its `1.0/dj` literals promote to double).
+ */
+int FN(oracle_depth_filter)(const REAL *poses, const REAL *disps, const float *intr_f, const int64_t *inds,
+                            const float *thresh, int n_frames, int n_inds, int ht, int wd, float *counter) {
+  const int HW = ht * wd;
+  const REAL fx = (REAL)intr_f[0], fy = (REAL)intr_f[1], cx = (REAL)intr_f[2], cy = (REAL)intr_f[3];
+  int b;
+#pragma omp parallel for schedule(dynamic, 1)
+  for (b = 0; b < n_inds; b++) {
+    const int ix = (int)inds[b];
+    const double t = (double)thresh[b];
+    int nb, k;
+    for (k = 0; k < HW; k++) counter[(size_t)b * HW + k] = 0.f;
+    for (nb = 0; nb < 6; nb++) {
+      const int jx = (nb < 3) ? ix - nb - 1 : ix + nb; /* droid_kernels.cu:696 */
+      REAL tij[3], qij[4];
+      if (jx < 0 || jx >= n_frames) continue;
+      FN(rel_se3)(poses + 7 * ix, poses + 7 * ix + 3, poses + 7 * jx, poses + 7 * jx + 3, tij, qij);
+      for (k = 0; k < HW; k++) {
+        const int i = k / wd, j = k % wd;
+        REAL Xi[4], Xj[3], uj, vj, dj;
+        int u0, v0;
+        Xi[0] = ((REAL)j - cx) / fx; Xi[1] = ((REAL)i - cy) / fy; Xi[2] = 1; Xi[3] = disps[(size_t)ix * HW + k];
+        FN(act_so3)(qij, Xi, Xj);
+        Xj[0] += Xi[3] * tij[0]; Xj[1] += Xi[3] * tij[1]; Xj[2] += Xi[3] * tij[2];
+        uj = fx * (Xj[0] / Xj[2]) + cx;
+        vj = fy * (Xj[1] / Xj[2]) + cy;
+        dj = Xi[3] / Xj[2];
+        if (!(uj > (REAL)-1e8 && uj < (REAL)1e8 && vj > (REAL)-1e8 && vj < (REAL)1e8)) continue; /* NaN / overflow: never inside */
+        u0 = (int)floor((double)uj);
+        v0 = (int)floor((double)vj);
+        if (u0 >= 0 && v0 >= 0 && u0 < wd - 1 && v0 < ht - 1) {
+          const REAL *dp = disps + (size_t)jx * HW;
+          const double inv = 1.0 / (double)dj;
+          const double d00 = dp[v0 * wd + u0], d01 = dp[v0 * wd + u0 + 1], d10 = dp[(v0 + 1) * wd + u0],
+                       d11 = dp[(v0 + 1) * wd + u0 + 1];
+          if (fabs(inv - 1.0 / d00) < t || fabs(inv - 1.0 / d01) < t || fabs(inv - 1.0 / d10) < t ||
+              fabs(inv - 1.0 / d11) < t)
+            counter[(size_t)b * HW + k] += 1.0f;
+        }
+      }
+    }
+  }
+  return 0;
+}
+
+/*
+ * align_scale_and_shift: per keyframe, weighted least squares  min sum w (s p + q - t)^2  and the
+ * weighted mean absolute error of the fit.  src/utils/common.py:402-438 (float32 torch sums there).
+ */
+int FN(oracle_align_scale_shift)(const REAL *pred, const REAL *target, const REAL *weights, int n, int HW, REAL *scale,
+                                 REAL *shift, REAL *err) {
+  int b;
+  for (b = 0; b < n; b++) {
+    const REAL *p = pred + (size_t)b * HW, *t = target + (size_t)b * HW, *w = weights + (size_t)b * HW;
+    double a00 = 0, a01 = 0, a11 = 0, b0 = 0, b1 = 0, es = 0, det, s, q;
+    int k;
+    for (k = 0; k < HW; k++) {
+      a00 += (double)(w[k] * p[k] * p[k]); a01 += (double)(w[k] * p[k]); a11 += (double)w[k];
+      b0 += (double)(w[k] * p[k] * t[k]);  b1 += (double)(w[k] * t[k]);
+    }
+    det = a00 * a11 - a01 * a01;
+    s = (a11 * b0 - a01 * b1) / det;
+    q = (-a01 * b0 + a00 * b1) / det;
+    for (k = 0; k < HW; k++) es += fabs((double)((REAL)s * p[k] + (REAL)q - t[k])) * (double)w[k];
+    scale[b] = (REAL)s; shift[b] = (REAL)q; err[b] = (REAL)(es / a11);
+  }
+  return 0;
+}
+
 #undef FN
 #undef FN1
 #undef FN2

@@ -144,3 +144,31 @@ def frame_distance(poses, disps, intrinsics, ii, jj, beta=0.3, precision="f32"):
     fn(_p(po), _p(di), _p(intr), _p(ii64), _p(jj64), ctypes.c_int(ii64.shape[0]), ctypes.c_int(ht), ctypes.c_int(wd),
        ctypes.c_float(beta), _p(out))
     return out
+
+
+def depth_filter(poses, disps, intrinsics, inds, thresh, precision="f32"):
+    """reference droid_backends.depth_filter (src/lib/droid_kernels.cu:661-775,1494-1518) -> counter [n,ht,wd] f32"""
+    real = np.float32 if precision == "f32" else np.float64
+    fn = getattr(lib(), "oracle_depth_filter_" + precision)
+    fn.restype = ctypes.c_int
+    N, ht, wd = disps.shape
+    po, di = np.ascontiguousarray(poses, dtype=real), np.ascontiguousarray(disps, dtype=real)
+    intr = np.ascontiguousarray(intrinsics, dtype=np.float32)
+    ix = np.ascontiguousarray(inds, dtype=np.int64)
+    th = np.ascontiguousarray(thresh, dtype=np.float32)
+    out = np.zeros((ix.shape[0], ht, wd), dtype=np.float32)
+    fn(_p(po), _p(di), _p(intr), _p(ix), _p(th), ctypes.c_int(N), ctypes.c_int(ix.shape[0]), ctypes.c_int(ht),
+       ctypes.c_int(wd), _p(out))
+    return out
+
+
+def align_scale_and_shift(prediction, target, weights, precision="f32"):
+    """reference src/utils/common.py:402-438 -> (scale [n], shift [n], avg_error [n])"""
+    real = np.float32 if precision == "f32" else np.float64
+    fn = getattr(lib(), "oracle_align_scale_shift_" + precision)
+    fn.restype = ctypes.c_int
+    n, ht, wd = prediction.shape
+    p_, t_, w_ = (np.ascontiguousarray(a, dtype=real) for a in (prediction, target, weights))
+    s, q, e = (np.zeros((n,), dtype=real) for _ in range(3))
+    fn(_p(p_), _p(t_), _p(w_), ctypes.c_int(n), ctypes.c_int(ht * wd), _p(s), _p(q), _p(e))
+    return s, q, e

@@ -404,6 +404,92 @@ def test_frame_distance_matches_oracle_and_reference(name, hw):
         np.testing.assert_allclose(got[ok], r[ok], rtol=1e-4, atol=1e-4)
 
 
+# ------------------------------------------------------------------------------------------
+# depth_filter + align_scale_and_shift
+# ------------------------------------------------------------------------------------------
+# The count is a thresholded decision on float32 geometry: an implementation that rounds the
+# reprojection differently (FMA contraction) may flip a pixel that sits exactly on the threshold or
+# on a pixel boundary.  Bound: at most 0.2 % of the pixels differ, and never by more than one vote.
+DEPTH_FILTER_MAX_FLIPS = 2e-3
+
+
+@pytest.mark.parametrize("n,ht,wd,noise", [(12, 24, 32, 0.0), (40, 48, 64, 0.01), (9, 21, 30, 0.02)])
+def test_depth_filter_matches_oracle_and_reference(n, ht, wd, noise):
+    import droid_backends
+    from helpers import planar_scene
+
+    poses, disps, intr = planar_scene(n, ht, wd, seed=n, noise=noise)
+    thresh = (0.02 * (1.0 / disps).mean(axis=(1, 2))).astype(np.float32)
+    inds = np.concatenate([np.arange(n), [3, 0]])  # repeated / unordered entries are legal
+    th = np.concatenate([thresh, thresh[[3, 0]] * 0.1]).astype(np.float32)
+    want = oracle.depth_filter(poses, disps, intr, inds, th)
+    tp, td, ti = (torch.from_numpy(a).cuda() for a in (poses, disps, intr))
+    tix, tth = torch.from_numpy(inds).cuda(), torch.from_numpy(th).cuda()
+    got = droid_backends.depth_filter(tp, td, ti, tix, tth).cpu().numpy()
+    assert got.shape == want.shape and got.dtype == np.float32
+    assert want.max() >= 5 and 0.1 < (want > 0).mean()
+    diff = np.abs(got - want)
+    assert diff.max() <= 1 and (diff > 0).mean() <= DEPTH_FILTER_MAX_FLIPS
+    # the poses buffer of the reference is longer than the keyframe count: only disps bounds the neighbours
+    tp_long = torch.cat([tp, tp[:5]], 0)
+    got2 = droid_backends.depth_filter(tp_long, td, ti, tix, tth).cpu().numpy()
+    np.testing.assert_array_equal(got2, got)
+    ref = _load_reference_so()
+    if ref is not None:
+        r = ref.depth_filter(tp, td, ti, tix, tth).cpu().numpy()
+        d = np.abs(got - r)
+        assert d.max() <= 1 and (d > 0).mean() <= DEPTH_FILTER_MAX_FLIPS
+
+
+def test_depth_filter_empty_and_errors():
+    import droid_backends
+    from helpers import planar_scene
+
+    poses, disps, intr = planar_scene(4, 8, 12)
+    tp, td, ti = (torch.from_numpy(a).cuda() for a in (poses, disps, intr))
+    out = droid_backends.depth_filter(tp, td, ti, torch.zeros(0, dtype=torch.int64).cuda(), torch.zeros(0).cuda())
+    assert out.shape == (0, 8, 12)
+    with pytest.raises(ValueError):
+        droid_backends.depth_filter(tp, td, ti, torch.zeros(2, dtype=torch.int64).cuda(), torch.zeros(1).cuda())
+    with pytest.raises((TypeError, ValueError, RuntimeError)):
+        droid_backends.depth_filter(tp.cpu(), td, ti, torch.zeros(1, dtype=torch.int64).cuda(), torch.zeros(1).cuda())
+
+
+def _torch_align(prediction, target, weights):
+    """float64 torch restatement of src/utils/common.py:402-438"""
+    p, t, w = prediction.double(), target.double(), weights.double()
+    a00, a01, a11 = (w * p * p).sum((1, 2)), (w * p).sum((1, 2)), w.sum((1, 2))
+    b0, b1 = (w * p * t).sum((1, 2)), (w * t).sum((1, 2))
+    det = a00 * a11 - a01 * a01
+    s, q = (a11 * b0 - a01 * b1) / det, (-a01 * b0 + a00 * b1) / det
+    e = ((s[:, None, None] * p + q[:, None, None] - t).abs() * w).sum((1, 2)) / a11
+    return s, q, e
+
+
+@pytest.mark.parametrize("name", ["A", "B", "C"])
+def test_align_scale_shift_matches_oracle(name):
+    import common
+
+    g = synth.with_mono_prior(small_graphs()[name] if name == "A" else synth.make_config(name))
+    w = g.valid_depth_mask.astype(np.float32)
+    s, q, e = oracle.align_scale_and_shift(g.mono_disps, g.disps, w, precision="f64")
+    tp, tt, tw = (torch.from_numpy(np.ascontiguousarray(a)).cuda() for a in (g.mono_disps, g.disps, w))
+    gs, gq, ge = common.align_scale_and_shift(tp, tt, tw)
+    np.testing.assert_allclose(gs.cpu().numpy(), s, rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(gq.cpu().numpy(), q, rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(ge.cpu().numpy(), e, rtol=1e-4, atol=1e-6)
+    # bool weights and the 2-D form of the reference signature (depth_video.py:308), against torch fp64
+    gs1, gq1, ge1 = common.align_scale_and_shift(tp[1], tt[1], tw[1] > 0)
+    rs, rq, re_ = _torch_align(tp[1:2], tt[1:2], tw[1:2])
+    assert abs(gs1.item() - rs.item()) < 1e-4 * abs(rs.item()) + 1e-5
+    assert abs(gq1.item() - rq.item()) < 1e-4 * abs(rq.item()) + 1e-5
+    assert abs(ge1.item() - re_.item()) < 1e-4 * abs(re_.item()) + 1e-6
+    # weights = None means all ones
+    gs2, _, _ = common.align_scale_and_shift(tp, tt, None)
+    rs2, _, _ = _torch_align(tp, tt, torch.ones_like(tp))
+    np.testing.assert_allclose(gs2.cpu().numpy(), rs2.cpu().numpy(), rtol=1e-4, atol=1e-5)
+
+
 def test_moba_mirror_matches_oracle():
     import geom_ba
 

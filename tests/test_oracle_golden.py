@@ -114,3 +114,46 @@ def test_frame_distance_oracle_basics():
     assert d2[0] == 1000.0
     d64 = oracle.frame_distance(g.poses, g.disps, g.intrinsics, ii.reshape(-1), jj.reshape(-1), 0.3, precision="f64")
     assert rel(d.reshape(-1), d64) < 1e-5
+
+
+def test_depth_filter_oracle_on_consistent_scene():
+    """droid_kernels.cu:661-775: with exact multi-view-consistent depth every neighbour that sees the
+    point agrees; a keyframe with wrong depth collects no votes and gives none."""
+    from helpers import planar_scene
+
+    n, ht, wd = 12, 24, 32
+    poses, disps, intr = planar_scene(n, ht, wd)
+    thresh = 0.02 * (1.0 / disps).mean(axis=(1, 2))
+    cnt = oracle.depth_filter(poses, disps, intr, np.arange(n), thresh)
+    assert cnt.shape == (n, ht, wd) and cnt.min() >= 0 and cnt.max() == 6
+    # neighbours that exist: -1,-2,-3,+3,+4,+5
+    exist = np.array([sum(0 <= k + o < n for o in (-1, -2, -3, 3, 4, 5)) for k in range(n)])
+    assert (cnt.reshape(n, -1).max(axis=1) == exist).all()
+    # interior pixels stay inside every neighbour's image: full count there
+    assert (cnt[5, 8:16, 10:22] == 6).all()
+    bad = disps.copy()
+    bad[5] *= 2.0
+    cnt2 = oracle.depth_filter(poses, bad, intr, np.arange(n), thresh)
+    assert cnt2[5].max() == 0
+    assert (cnt2[6] <= cnt[6]).all() and cnt2[6].sum() < cnt[6].sum()  # 6 lost neighbour 5 (= 6-1)
+    np.testing.assert_array_equal(cnt2[9], cnt[9])  # 9 looks at 8, 7, 6, 12.., never at 5
+    sub = oracle.depth_filter(poses, disps, intr, np.array([7, 2]), thresh[[7, 2]])
+    np.testing.assert_array_equal(sub, cnt[[7, 2]])
+    c64 = oracle.depth_filter(poses, disps, intr, np.arange(n), thresh, precision="f64")
+    assert (c64 != cnt).mean() < 2e-3
+
+
+def test_align_scale_shift_oracle_recovers_affine():
+    """src/utils/common.py:402-438: target = 1.7 * prediction - 0.3 on the weighted pixels"""
+    rng = np.random.default_rng(3)
+    p = rng.uniform(0.2, 2.0, (5, 16, 24)).astype(np.float32)
+    w = (rng.uniform(size=p.shape) > 0.3).astype(np.float32)
+    t = (1.7 * p - 0.3).astype(np.float32)
+    t[w == 0] = 99.0  # ignored pixels
+    s, q, e = oracle.align_scale_and_shift(p, t, w)
+    np.testing.assert_allclose(s, 1.7, rtol=1e-4)
+    np.testing.assert_allclose(q, -0.3, atol=1e-4)
+    assert e.max() < 1e-4
+    t2 = t + (rng.normal(0, 0.05, p.shape) * w).astype(np.float32)
+    s2, q2, e2 = oracle.align_scale_and_shift(p, t2, w, precision="f64")
+    assert 0.02 < e2.mean() < 0.06 and abs(s2 - 1.7).max() < 0.05
