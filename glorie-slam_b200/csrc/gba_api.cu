@@ -13,6 +13,7 @@
 #include "gba_common.cuh"
 #include "gba_dspo.cuh"
 #include "gba_kernels.cuh"
+#include "gba_gram_tc.cuh"
 #include "gba_solver.cuh"
 
 thread_local char g_create_err[512] = "";  // also written by gba_noalloc.cu
@@ -28,7 +29,7 @@ struct gba_ctx {
   float *hpart, *edge_hv, *Q, *W, *gram, *dx, *dzbuf, *dspo_part, *dwq;
   size_t gram_cap, sys_cap;
   double *sys;
-  int *tslot, *perm, *iperm, *dspo_bad;
+  int *tslot, *perm, *iperm, *dspo_bad, *wdog;
   int *h_cnt;  // pinned: colcnt[nT_max] | rowcnt[nT_max], read back with the status
   int pos_cap;
   SolverBufs sb;
@@ -105,7 +106,7 @@ extern "C" void gba_destroy(gba_ctx *c) {
   if (!c) return;
   cudaSetDevice(c->device);
   void *ptrs[] = {c->kx, c->fmap, c->deg, c->eptr, c->eidx, c->ek, c->goff, c->st_d, c->geo, c->hpart, c->edge_hv,
-                  c->Q, c->W, c->gram, c->dx, c->dzbuf, c->dspo_part, c->dwq, c->sys, c->tslot, c->perm, c->iperm, c->dspo_bad,
+                  c->Q, c->W, c->gram, c->dx, c->dzbuf, c->dspo_part, c->dwq, c->sys, c->tslot, c->perm, c->iperm, c->dspo_bad, c->wdog,
                   c->sb.tbits, c->sb.colrows, c->sb.colcnt, c->sb.rowcols, c->sb.rowcnt, c->sb.invL, c->sb.fail,
                   c->flags};
   for (void *q : ptrs)
@@ -197,6 +198,8 @@ extern "C" int gba_create(gba_ctx **out, int device, int max_frames, int max_edg
   CKC(dalloc(&c->sb.rowcnt, nT));
   CKC(dalloc(&c->sb.fail, 1));
   CKC(dalloc(&c->dspo_bad, 1));
+  CKC(dalloc(&c->wdog, 256));
+  CKC(cudaMemset(c->wdog, 0, 256 * sizeof(int)));
   CKC(dalloc(&c->sb.tbits, nT * TS_WORDS));
   CKC(dalloc(&c->flags, 5 * nT));
   c->sb.ticket = c->flags + 4 * nT;
@@ -207,6 +210,8 @@ extern "C" int gba_create(gba_ctx **out, int device, int max_frames, int max_edg
   CKC(cudaMemset(c->sb.fail, 0, sizeof(int)));
   CKC(cudaMemset(c->st_d, 0, sizeof(Status)));
   CKC(cudaFuncSetAttribute(k_gram, cudaFuncAttributeMaxDynamicSharedMemorySize, kGramSmemMax));
+  CKC(cudaFuncSetAttribute(k_gram_tc<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gram_tc_smem(GT_MAXDEG)));
+  CKC(cudaFuncSetAttribute(k_gram_tc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gram_tc_smem(GT_MAXDEG)));
   CKC(cudaFuncSetAttribute(k_potrf_diag, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolverSmem));
   CKC(cudaFuncSetAttribute(k_trsm, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolverSmem));
   CKC(cudaFuncSetAttribute(k_syrk, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolverSmem));
@@ -322,6 +327,13 @@ extern "C" int gba_ba_begin(gba_ctx *c, float *poses, float *disps, const float 
   p.perm = c->perm;
   p.iperm = c->iperm;
   p.nT = c->nT_max;  // stride of the tile tables; the actual tile count comes back in the status
+  {  // GBA_GRAM_TC=0 sends every keyframe through the CUDA-core k_gram (diagnostics, A/B comparison)
+    const char *e = getenv("GBA_GRAM_TC");
+    p.tc_maxdeg = (e && e[0] == '0') ? 0 : GT_MAXDEG;
+    p.wdog = c->wdog;
+    // the bulk copies of k_gram_tc need 16-byte aligned rows (HW % 4 == 0 is already required)
+    if ((((uintptr_t)p.targets | (uintptr_t)p.weights | (uintptr_t)p.disps) & 15) != 0) p.tc_maxdeg = 0;
+  }
   p.ld = 0;
   c->last_P = p.P;
   int rc = build_index(c, kx_global, n_kx, true, ii_all, jj_all, n_all);
@@ -412,10 +424,35 @@ extern "C" int gba_ba_build(gba_ctx *c) {
   stage_end(c);
   if (!p.motion_only && p.E > 0 && st.K > 0) {
     stage_begin(c, GBA_STAGE_GRAM);
-    if (c->gsplit > 1) CK(cudaMemsetAsync(c->gram, 0, (size_t)st.gram_floats * sizeof(float), s));
-    const int RS = gram_pitch((6 * st.max_deg + 1 + 7) / 8);
-    k_gram<<<dim3(c->gsplit, st.K), GRAM_NT, (size_t)2 * GRAM_T * RS * sizeof(float) + (size_t)st.max_deg * 68, s>>>(p);
-    LAUNCH_CHECK("k_gram");
+    // pixel split per keyframe.  k_gram_tc runs one CTA per SM and pays ~15 us of set-up per CTA, so it
+    // is only split when the keyframes alone leave SMs idle; with it active, k_gram only sees the few
+    // high-degree keyframes and is split wide.
+    int gs_tc = 1, gs_cc = c->gsplit;
+    if (p.tc_maxdeg > 0) {
+      const int ntile = (c->HW + GT_K - 1) / GT_K;
+      double best = 1e30;
+      for (int g = 1; g <= std::min(16, ntile); g++) {
+        const double cost = (double)((st.K * g + c->sm_count - 1) / c->sm_count) * (1.0 / g + 0.12);
+        if (cost < best - 1e-9) {
+          best = cost;
+          gs_tc = g;
+        }
+      }
+      gs_cc = std::max(c->gsplit, std::min(16, ntile));
+    }
+    const bool need_cc = st.max_deg > p.tc_maxdeg;
+    if ((p.tc_maxdeg > 0 && gs_tc > 1) || (need_cc && gs_cc > 1))
+      CK(cudaMemsetAsync(c->gram, 0, (size_t)st.gram_floats * sizeof(float), s));
+    if (p.tc_maxdeg > 0) {  // tensor-core Gram for the keyframes with <= GT_MAXDEG out-edges
+      if (p.mode == GBA_MODE_DROID_CUDA) k_gram_tc<0><<<dim3(gs_tc, st.K), GT_NT, gram_tc_smem(st.max_deg), s>>>(p);
+      else k_gram_tc<1><<<dim3(gs_tc, st.K), GT_NT, gram_tc_smem(st.max_deg), s>>>(p);
+      LAUNCH_CHECK("k_gram_tc");
+    }
+    if (need_cc) {
+      const int RS = gram_pitch((6 * st.max_deg + 1 + 7) / 8);
+      k_gram<<<dim3(gs_cc, st.K), GRAM_NT, (size_t)2 * GRAM_T * RS * sizeof(float) + (size_t)st.max_deg * 68, s>>>(p);
+      LAUNCH_CHECK("k_gram");
+    }
     stage_end(c);
     stage_begin(c, GBA_STAGE_SCHUR);
     k_schur<<<st.K, SCHUR_NT, (size_t)6 * (6 * st.max_deg + 1) * sizeof(float), s>>>(p);
@@ -669,6 +706,8 @@ extern "C" int gba_get(gba_ctx *c, int what, void *dst, size_t bytes) {
     case GBA_GET_EDGE_HV: src = c->edge_hv; need = (size_t)p.E * 32 * 4; break;
     case GBA_GET_Q: src = c->Q; need = (size_t)st.K * p.HW * 4; break;
     case GBA_GET_W: src = c->W; need = (size_t)st.K * p.HW * 4; break;
+    case GBA_GET_GRAM: src = c->gram; need = (size_t)st.gram_floats * 4; break;
+    case GBA_GET_WATCHDOG: src = c->wdog; need = 256 * 4; break;
     case GBA_GET_TILEMASK: {
       const int nTa = st.n_tiles;
       need = (size_t)nTa * nTa;

@@ -534,7 +534,7 @@ __global__ void __launch_bounds__(GRAM_NT, 2) k_gram(BaParams p) {
   if (k >= p.st->K) return;
   if (p.owned && !p.owned[k]) return;
   const int e0 = p.eptr[k], deg = p.eptr[k + 1] - e0;
-  if (deg == 0) return;
+  if (deg == 0 || deg <= p.tc_maxdeg) return;  // small keyframes are k_gram_tc's
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int Rw = 6 * deg;              // rows of E; shared-memory column Rw holds sqrt(Q) * w
   const int nb = (Rw + 7) / 8;         // 8-row blocks of G proper

@@ -131,6 +131,12 @@ int gba_query(gba_ctx *ctx, gba_info *info);
                               left by the last gba_ba_build (geom mode: damping already on A; droid mode: not
                               yet damped), then the rhs b - vS.  Valid between gba_ba_build and gba_ba_solve. */
 #define GBA_GET_TILEMASK 8 /* uint8 [nT,nT] lower-triangular tile structure after fill        */
+#define GBA_GET_GRAM 9     /* float: per depth keyframe k (in GBA_GET_KX order) one Rp x Rp block, Rp = 8*ceil((6 deg_k
+                              + 1)/8), concatenated; entry (r, c >= r) = sum_pix E_r Q E_c, column 6 deg_k = sum_pix
+                              E_r Q w; entries below the diagonal are unspecified (last iteration)                  */
+#define GBA_GET_WATCHDOG 10 /* int32 [256]: [0] = number of pipeline waits in the tensor-core Gram kernel that exceeded
+                               the watchdog limit since gba_create (0 in a healthy run), then up to 42 records
+                               {keyframe, split, warp, wait site, index, group}                                  */
 int gba_get(gba_ctx *ctx, int what, void *dst, size_t bytes);
 
 /* ---- optional per-stage device timing ---------------------------------------------------

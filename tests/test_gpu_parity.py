@@ -218,6 +218,64 @@ def test_hub_keyframe_with_large_out_degree():
     assert rel(r.disps, o.disps) < STATE_RTOL
 
 
+def _mixed_degree_graph(n, ht, wd, seed):
+    """temporal chain plus out-degree classes <= 6, 7..14, 15..21 and > 21 (one hub)"""
+    g = synth.make_graph(n, 2 * (n - 1), 1, iters=2, seed=seed, ht=ht, wd=wd, lm=1e-4, ep=0.1)
+    rng = np.random.default_rng(seed + 1)
+    ei, ej = [g.ii], [g.jj]
+    for i in range(0, n, 3):
+        want = [3, 9, 17, 19][(i // 3) % 4] if i != 6 else 26
+        cand = np.array([j for j in range(n) if abs(j - i) > 1])
+        js = rng.choice(cand, size=min(want, len(cand)), replace=False)
+        ei.append(np.full(len(js), i)); ej.append(js)
+    ii, jj = np.concatenate(ei).astype(np.int64), np.concatenate(ej).astype(np.int64)
+    tg = synth.project(g.poses_gt, g.disps_gt, g.intrinsics, ii, jj) + rng.normal(0, 0.5, (len(ii), 2, ht, wd))
+    g.ii, g.jj, g.targets = ii, jj, tg.astype(np.float32)
+    g.weights = rng.uniform(0, 1, tg.shape).astype(np.float32)
+    return g
+
+
+def _gram_blocks(r):
+    K = r.info.n_depth_frames
+    deg = np.diff(get_array(r.ctx, _gba.GET_EPTR, (K + 1,), np.int32))
+    Rp = 8 * ((6 * deg + 1 + 7) // 8)
+    flat = get_array(r.ctx, _gba.GET_GRAM, (int((Rp.astype(np.int64) ** 2).sum()),), np.float32)
+    out, off = [], 0
+    for k in range(K):
+        R = 6 * deg[k] + 1
+        blk = np.triu(flat[off:off + Rp[k] ** 2].reshape(Rp[k], Rp[k])[:R, :R]).astype(np.float64)
+        blk[R - 1, R - 1] = 0.0  # sum Q w^2: not part of the contract (never read)
+        out.append(blk)
+        off += Rp[k] ** 2
+    return deg, out
+
+
+@pytest.mark.parametrize("n,ht,wd", [(40, 16, 24), (190, 30, 40)])
+def test_tensor_core_gram_matches_cuda_core_gram(n, ht, wd, monkeypatch):
+    """k_gram_tc (tcgen05, 3xTF32, drained accumulators) against k_gram (fp32 FFMA) entry by entry, on
+    out-degrees below 14 (idle producer warps), 15-21 (two edges per warp), above 21 (k_gram fallback),
+    a last tile that is not full (30 x 40 pixels) and more keyframes than SMs; then end to end
+    against the fp64 oracle."""
+    g = _mixed_degree_graph(n, ht, wd, seed=n)
+    monkeypatch.setenv("GBA_GRAM_TC", "0")
+    r0 = run_ba(g, iters=1)
+    deg0, G0 = _gram_blocks(r0)
+    monkeypatch.setenv("GBA_GRAM_TC", "1")
+    r1 = run_ba(g, iters=1)
+    deg1, G1 = _gram_blocks(r1)
+    np.testing.assert_array_equal(deg0, deg1)
+    assert deg0.max() > 21 and (deg0 <= 6).any() and ((deg0 > 14) & (deg0 <= 21)).any()
+    for k in range(len(G0)):
+        scale = np.abs(G0[k]).max() + 1e-30
+        assert np.abs(G1[k] - G0[k]).max() / scale < 5e-6, (k, deg0[k])
+    o = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj, g.t0, g.t1,
+                  g.iters, g.lm, g.ep, precision="f64")
+    r = run_ba(g)
+    assert rel(sign_normalise(r.poses), sign_normalise(o.poses)) < STATE_RTOL
+    assert rel(r.disps, o.disps) < STATE_RTOL
+    assert get_array(r.ctx, _gba.GET_WATCHDOG, (256,), np.int32)[0] == 0  # no pipeline wait ever expired
+
+
 def test_argument_errors():
     import droid_backends
 
