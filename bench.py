@@ -370,6 +370,26 @@ def main():
     except Exception:
         pass
 
+    # The Schur Gram (k_gram_tc) is the GEMM-shaped kernel of the path: G_k = A_k A_k^T per depth keyframe,
+    # A_k = [6 deg_k + 1 rows] x [HW pixels].  Algorithmic flops = sum_k R_k (R_k + 1) HW (the symmetric
+    # half, 2 flops per multiply-add); the tensor cores execute 3 tf32 MMAs of 128 x N_k x HW for it
+    # (3xTF32 split, full square).  Peak: dense tf32 = half the measured dense bf16 rate.
+    deg_local = np.bincount(np.searchsorted(kx, g.ii[sel]), minlength=len(kx))
+    R = 6.0 * deg_local[deg_local > 0] + 1.0
+    gram_ms = stages.get("gram", {}).get("ms_per_step", 0.0) / max(iters, 1)
+    gram_alg = float((R * (R + 1.0)).sum()) * HW
+    small = R <= 128
+    gram_exec = float((3.0 * 2.0 * 128.0 * (np.ceil(R[small] / 16.0) * 16.0)).sum()) * HW
+    tf32_peak = pk.get("bf16_tflops_sustained", pk.get("bf16_tflops", 0.0)) / 2.0
+    roofline_gram = None
+    if gram_ms > 0:
+        roofline_gram = {"bound": "tensor", "kernel": "k_gram_tc (+ k_gram for out-degree > 21)", "unit": "TFLOP/s",
+                         "achieved": gram_alg / (gram_ms * 1e-3) / 1e12, "peak": tf32_peak,
+                         "frac": gram_alg / (gram_ms * 1e-3) / 1e12 / tf32_peak if tf32_peak else None,
+                         "executed_tf32": gram_exec / (gram_ms * 1e-3) / 1e12, "ms_per_launch": gram_ms,
+                         "note": "producer-bound: the CUDA cores rebuild the operand rows (about 170 instructions per "
+                                 "edge pixel); the MMAs run underneath"}
+
     # ---- end to end: pinned host buffers -> public API -> host, copies inside the timed region ----
     # Every step copies ITS inputs from pinned host memory and reads its result back.  The copies run
     # on a second stream into one of two device buffer sets, so the transfer of step s+1 overlaps the
@@ -448,7 +468,7 @@ def main():
                        "lm": g.lm, "ep": g.ep, "sharding": "by source keyframe, %d rank(s)" % world,
                        "l2": "inputs (%.0f MB per rank) larger than L2" % (input_bytes / 1e6) if l2_flush is None
                              else "256 MB L2 flush between steps"},
-            "roofline": roofline, "stages": stages, "cpu_baseline": cb, "e2e": e2e, "reference_cuda": ref_cuda,
+            "roofline": roofline, "roofline_gram": roofline_gram, "stages": stages, "cpu_baseline": cb, "e2e": e2e, "reference_cuda": ref_cuda,
             "gpu_launches": int(launches_per_step * args.steps), "gpu_launches_per_step": int(launches_per_step),
             "clocks": clocks,
             "solver": {"tiles": info.n_tiles, "active_tiles": info.n_active_tiles, "chol_failures": info.chol_failures},
