@@ -34,7 +34,9 @@ struct gba_ctx {
   int pos_cap;
   SolverBufs sb;
   unsigned int *flags;  // flagA | cntB | cntD | flagX | ticket, nT_max each
-  int nT_max, hpart_chunks, panel_capacity;
+  unsigned int *upd;    // per tile slot: slab updates received inside k_chain
+  size_t slot_cap;
+  int nT_max, hpart_chunks, panel_capacity, chain_capacity;
   // state of the current call
   BaParams p;
   cudaStream_t stream;
@@ -108,7 +110,7 @@ extern "C" void gba_destroy(gba_ctx *c) {
   void *ptrs[] = {c->kx, c->fmap, c->deg, c->eptr, c->eidx, c->ek, c->goff, c->st_d, c->geo, c->hpart, c->edge_hv,
                   c->Q, c->W, c->gram, c->dx, c->dzbuf, c->dspo_part, c->dwq, c->sys, c->tslot, c->perm, c->iperm, c->dspo_bad, c->wdog,
                   c->sb.tbits, c->sb.colrows, c->sb.colcnt, c->sb.rowcols, c->sb.rowcnt, c->sb.invL, c->sb.fail,
-                  c->flags};
+                  c->flags, c->upd};
   for (void *q : ptrs)
     if (q) cudaFree(q);
   if (c->st_h) cudaFreeHost(c->st_h);
@@ -202,6 +204,9 @@ extern "C" int gba_create(gba_ctx **out, int device, int max_frames, int max_edg
   CKC(cudaMemset(c->wdog, 0, 256 * sizeof(int)));
   CKC(dalloc(&c->sb.tbits, nT * TS_WORDS));
   CKC(dalloc(&c->flags, 5 * nT));
+  c->slot_cap = std::min<size_t>(nT * (nT + 1) / 2, (size_t)131072);
+  CKC(dalloc(&c->upd, c->slot_cap));
+  c->sb.upd = c->upd;
   c->sb.ticket = c->flags + 4 * nT;
   c->sb.flagA = c->flags;
   c->sb.cntB = c->flags + nT;
@@ -217,10 +222,13 @@ extern "C" int gba_create(gba_ctx **out, int device, int max_frames, int max_edg
   CKC(cudaFuncSetAttribute(k_syrk, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolverSmem));
   CKC(cudaFuncSetAttribute(k_panel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolverSmem));
   CKC(cudaFuncSetAttribute(k_panel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolverSmem));
+  CKC(cudaFuncSetAttribute(k_chain<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolverSmem));
   {
     int per_sm = 0;
     CKC(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_panel<16>, 256, kSolverSmem));
     c->panel_capacity = per_sm * c->sm_count;  // the fused tile-column kernel needs a co-resident grid
+    CKC(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_chain<16>, 256, kSolverSmem));
+    c->chain_capacity = std::max(1, per_sm) * c->sm_count;
   }
 #undef CKC
   *out = ctx;
@@ -517,9 +525,27 @@ extern "C" int gba_ba_solve(gba_ctx *c) {
       const int rc = panel(t, segT, nseg, false);
       if (rc) return rc;
     }
-    for (int kk = band; kk < nT; kk++) {
-      const int rc = panel(kk, 0, 1, kk + 1 >= nT);
-      if (rc) return rc;
+    if (!getenv("GBA_NO_CHAIN")) {
+      // the remaining columns (the closure block, or everything when the band was not cut into
+      // segments) as one dependency graph of tile tasks on a persistent grid
+      long long total = 1;
+      int mc = 0;
+      for (int kk = band; kk < nT; kk++) {
+        const int cnt = colcnt[kk];
+        mc = std::max(mc, cnt);
+        total += 4LL * cnt + (cnt > 0 ? 4 + (long long)cnt * (cnt + 1) / 2 - 1 : 0) + (kk + 1 < nT ? 1 : 0);
+      }
+      if (band < nT) {
+        CK(cudaMemsetAsync(c->upd, 0, (size_t)st.n_slots * sizeof(unsigned int), s));
+        const int grid = (int)std::min<long long>(total, (long long)c->chain_capacity);
+        k_chain<16><<<grid, 256, kSolverSmem, s>>>(p, c->sb, band, (int)total);
+        LAUNCH_CHECK("k_chain");
+      }
+    } else {
+      for (int kk = band; kk < nT; kk++) {
+        const int rc = panel(kk, 0, 1, kk + 1 >= nT);
+        if (rc) return rc;
+      }
     }
     stage_end(c);
     stage_begin(c, GBA_STAGE_SOLVE);

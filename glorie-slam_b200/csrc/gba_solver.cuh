@@ -25,6 +25,7 @@ struct SolverBufs {
   double *invL;           // [nT][NB*NB]
   int *fail;              // factorisation hit a non-positive pivot
   unsigned int *flagA, *cntB, *cntD, *flagX, *ticket;  // per-panel in-kernel synchronisation
+  unsigned int *upd;      // [n_slots] slab updates a tile has received inside k_chain
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -730,7 +731,8 @@ __global__ void __launch_bounds__(256) k_panel(BaParams p, SolverBufs sb, int kk
   const bool failed = __ldcg(sb.fail);
   if (!failed) role_syrk<SLAB>(p, sb, kk, a, rem, q, atomic_from, s_buf);
   // look-ahead: tile (kk+1, kk+1) is complete once its SPLIT slabs are updated
-  if (pair == 0 && sb.colrows[kk * p.nT] == kk + 1) {
+  // (not into the closure block: its tiles are still being updated by the other band segments)
+  if (pair == 0 && sb.colrows[kk * p.nT] == kk + 1 && kk + 1 < atomic_from) {
     __threadfence();
     __syncthreads();
     if (tid == 0) s_flag = (atomicAdd(&sb.cntD[kk], 1u) == (unsigned)(SPLIT - 1));
@@ -741,6 +743,153 @@ __global__ void __launch_bounds__(256) k_panel(BaParams p, SolverBufs sb, int kk
       __threadfence();
       __syncthreads();
       if (tid == 0) atomicExch(&sb.flagA[kk + 1], 1u);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_chain: ALL tile columns c0 .. nT-1 in ONE launch, as a dependency graph of tile tasks.
+//
+// With one launch per column (k_panel) a column costs its critical path -- Cholesky of the diagonal
+// tile, one triangular solve, one update -- PLUS the tail of its ~1000 independent updates and the
+// launch boundary: ~42 us per closure column on a B200, of which the path itself is ~28.  Here the
+// updates of column k run underneath the critical path of columns k+1, k+2, ...
+//
+// Tasks, in ticket order (P = potrf, T = trsm slab of 16 rows, S = update; pair 0 is the tile below the
+// diagonal, the one the next potrf waits for: it is updated in 4 slabs by 4 CTAs, the other tiles
+// whole):
+//     P(c0) | T(c0,*) S(c0,pair 0) P(c0+1) S(c0,rest) | T(c0+1,*) S(c0+1,pair 0) P(c0+2) S(c0+1,rest) | ...
+// A persistent CTA takes the next ticket, waits for the task's inputs, runs it, publishes it:
+//     P(k)       waits until tile (k,k) has received every update of columns c0..k-1      -> flagA[k]
+//     T(k,a,q)   waits for flagA[k] and for tile (i_a,k) to be fully updated              -> cntB[k]++
+//     S(k,a,b,q) waits for cntB[k] == all slabs of column k, and for the updates of earlier columns to
+//                the same tile (plain read-modify-write, so they are applied in column order) -> upd[tile]++
+// The number of updates a tile receives from columns c0..k-1 is a popcount over the symbolic
+// structure bits.  Every wait is for a task with a smaller ticket, i.e. one that is finished or
+// running on a resident CTA, so the graph cannot deadlock whatever the grid size; a watchdog turns a
+// broken invariant into a failed factorisation (zero update) instead of a hung GPU.
+// rhs blocks are updated with atomics: two columns that do not touch each other may both update the
+// same row block.
+// ---------------------------------------------------------------------------------------------
+#define CHAIN_WATCHDOG (1 << 21)  // polls of >= 32 ns: > 60 ms
+__device__ __forceinline__ void chain_wait(const unsigned *ptr, unsigned target, int *fail) {
+  int spins = 0;
+  while (ld_acquire(ptr) < target) {
+    __nanosleep(32);
+    if (++spins > CHAIN_WATCHDOG) {
+      *fail = 3;
+      break;
+    }
+  }
+}
+
+template <int SLAB>
+__global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int c0, int total) {
+  extern __shared__ double s_buf[];
+  constexpr int SPLIT = GBA_NB / SLAB;
+  __shared__ int s_task[5];  // role, kk, a, b, q
+  __shared__ unsigned s_need[2];
+  const int tid = threadIdx.x, nT = p.st->n_tiles;
+  int col = c0, base = 1;  // ticket of the first task of column `col`'s block (thread 0 only)
+  for (;;) {
+    __syncthreads();  // the previous task's shared memory is dead
+    if (tid == 0) {
+      const int t = (int)atomicAdd(&sb.ticket[c0], 1u);
+      int role = -1, kk = 0, a = 0, b = 0, q = 0;
+      if (t == 0) {
+        role = 0;
+        kk = c0;
+      } else if (t < total) {
+        for (;;) {  // tickets only grow: the walk over the columns is amortised
+          const int cnt = sb.colcnt[col], pairs = cnt * (cnt + 1) / 2, nxt = (col + 1 < nT) ? 1 : 0;
+          const int n = SPLIT * cnt + (cnt > 0 ? SPLIT + pairs - 1 : 0) + nxt;
+          if (t < base + n) {
+            int o = t - base;
+            kk = col;
+            if (o < SPLIT * cnt) {
+              role = 1; a = o / SPLIT; q = o % SPLIT;
+            } else {
+              o -= SPLIT * cnt;
+              if (cnt > 0 && o < SPLIT) {
+                role = 2; a = 0; b = 0; q = o;
+              } else {
+                if (cnt > 0) o -= SPLIT;
+                if (nxt && o == 0) {
+                  role = 0; kk = col + 1;
+                } else {
+                  o -= nxt;
+                  int pr = 1 + o;  // whole-tile update
+                  a = 0;
+                  while (pr > a) { pr -= a + 1; a++; }
+                  b = pr;
+                  role = 3;
+                }
+              }
+            }
+            break;
+          }
+          base += n;
+          col++;
+        }
+      }
+      s_task[0] = role; s_task[1] = kk; s_task[2] = a; s_task[3] = b; s_task[4] = q;
+    }
+    __syncthreads();
+    const int role = s_task[0], kk = s_task[1], a = s_task[2], b = s_task[3], q = s_task[4];
+    if (role < 0) return;
+    // tiles whose update counts gate this task: (i, j) and the number of earlier columns touching both
+    int ti, tj;
+    if (role == 0) ti = tj = kk;
+    else if (role == 1) { ti = sb.colrows[kk * p.nT + a]; tj = kk; }
+    else { ti = sb.colrows[kk * p.nT + a]; tj = sb.colrows[kk * p.nT + b]; }
+    if (tid < 32) {
+      unsigned n = 0;
+      if (tid < TS_WORDS) {
+        unsigned m = sb.tbits[ti * TS_WORDS + tid] & sb.tbits[tj * TS_WORDS + tid];
+        // keep bits c0 <= c < kk of this word
+        const int lo = c0 - 32 * tid, hi = kk - 32 * tid;
+        if (hi <= 0 || lo >= 32) m = 0;
+        else {
+          if (lo > 0) m &= ~0u << lo;
+          if (hi < 32) m &= (1u << hi) - 1u;
+        }
+        n = __popc(m);
+      }
+#pragma unroll
+      for (int o = 16; o >= 1; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+      if (tid == 0) s_need[0] = n * SPLIT;
+    }
+    __syncthreads();
+    const unsigned need = s_need[0];
+    const unsigned *updp = sb.upd + p.tslot[ti * p.nT + tj];
+    if (tid == 0) {
+      if (role == 1) chain_wait(&sb.flagA[kk], 1u, sb.fail);
+      if (role >= 2) chain_wait(&sb.cntB[kk], (unsigned)(SPLIT * sb.colcnt[kk]), sb.fail);
+      chain_wait(updp, need, sb.fail);
+    }
+    __syncthreads();
+    const bool failed = __ldcg(sb.fail) != 0;
+    if (role == 0) {
+      // (the first column may already have been factorised by the look-ahead of the launch before)
+      if (!failed && ld_acquire(&sb.flagA[kk]) == 0u) role_potrf(p, sb, kk, s_buf);
+      __threadfence();
+      __syncthreads();
+      if (tid == 0) atomicExch(&sb.flagA[kk], 1u);
+    } else if (role == 1) {
+      if (!failed) role_trsm<SLAB>(p, sb, kk, a, q, 0, s_buf);
+      __threadfence();
+      __syncthreads();
+      if (tid == 0) atomicAdd(&sb.cntB[kk], 1u);
+    } else if (role == 2) {
+      if (!failed) role_syrk<SLAB>(p, sb, kk, a, b, q, 1 << 30, s_buf);
+      __threadfence();
+      __syncthreads();
+      if (tid == 0) atomicAdd(const_cast<unsigned *>(updp), 1u);
+    } else {  // a whole tile at once: a quarter of the tasks, the L[j,kk] operand is loaded once instead of 4 times
+      if (!failed) role_syrk<GBA_NB>(p, sb, kk, a, b, 0, 1 << 30, s_buf);
+      __threadfence();
+      __syncthreads();
+      if (tid == 0) atomicAdd(const_cast<unsigned *>(updp), (unsigned)SPLIT);
     }
   }
 }
