@@ -521,27 +521,25 @@ extern "C" int gba_ba_solve(gba_ctx *c) {
       }
       return GBA_OK;
     };
-    for (int t = 0; t < (nseg > 1 ? segT : 0); t++) {
-      const int rc = panel(t, segT, nseg, false);
-      if (rc) return rc;
+    // One launch: the whole factorisation as a dependency graph of tile tasks on a persistent grid.
+    // GBA_NO_CHAIN=1 keeps the older sequence, one launch per band step and per closure column.
+    long long total = nseg > 1 ? nseg : 1;
+    for (int kk = 0; kk < nT; kk++) {
+      const int cnt = colcnt[kk];
+      const bool in_band = kk < band;
+      const bool has_next = in_band ? ((kk % segT) + 1 < segT || (kk == band - 1 && band < nT)) : (kk + 1 < nT);
+      total += 4LL * cnt + (cnt > 0 ? 4 + (long long)cnt * (cnt + 1) / 2 - 1 : 0) + (has_next ? 1 : 0);
     }
-    if (!getenv("GBA_NO_CHAIN")) {
-      // the remaining columns (the closure block, or everything when the band was not cut into
-      // segments) as one dependency graph of tile tasks on a persistent grid
-      long long total = 1;
-      int mc = 0;
-      for (int kk = band; kk < nT; kk++) {
-        const int cnt = colcnt[kk];
-        mc = std::max(mc, cnt);
-        total += 4LL * cnt + (cnt > 0 ? 4 + (long long)cnt * (cnt + 1) / 2 - 1 : 0) + (kk + 1 < nT ? 1 : 0);
-      }
-      if (band < nT) {
-        CK(cudaMemsetAsync(c->upd, 0, (size_t)st.n_slots * sizeof(unsigned int), s));
-        const int grid = (int)std::min<long long>(total, (long long)c->chain_capacity);
-        k_chain<16><<<grid, 256, kSolverSmem, s>>>(p, c->sb, band, (int)total);
-        LAUNCH_CHECK("k_chain");
-      }
+    if (!getenv("GBA_NO_CHAIN") && total < (1LL << 30)) {
+      CK(cudaMemsetAsync(c->upd, 0, (size_t)st.n_slots * sizeof(unsigned int), s));
+      const int grid = (int)std::min<long long>(total, (long long)c->chain_capacity);
+      k_chain<16><<<grid, 256, kSolverSmem, s>>>(p, c->sb, nseg, segT, (int)total);
+      LAUNCH_CHECK("k_chain");
     } else {
+      for (int t = 0; t < (nseg > 1 ? segT : 0); t++) {
+        const int rc = panel(t, segT, nseg, false);
+        if (rc) return rc;
+      }
       for (int kk = band; kk < nT; kk++) {
         const int rc = panel(kk, 0, 1, kk + 1 >= nT);
         if (rc) return rc;

@@ -748,26 +748,34 @@ __global__ void __launch_bounds__(256) k_panel(BaParams p, SolverBufs sb, int kk
 }
 
 // ---------------------------------------------------------------------------------------------
-// k_chain: ALL tile columns c0 .. nT-1 in ONE launch, as a dependency graph of tile tasks.
+// k_chain: the WHOLE factorisation in ONE launch, as a dependency graph of tile tasks.
 //
 // With one launch per column (k_panel) a column costs its critical path -- Cholesky of the diagonal
-// tile, one triangular solve, one update -- PLUS the tail of its ~1000 independent updates and the
-// launch boundary: ~42 us per closure column on a B200, of which the path itself is ~28.  Here the
-// updates of column k run underneath the critical path of columns k+1, k+2, ...
+// tile, one triangular solve, one update -- PLUS the tail of its independent updates and the launch
+// boundary: ~42 us per closure column and ~78 us per band step on a B200, of which the path itself
+// is ~28.  Here the updates of a column run underneath the critical path of the following ones.
 //
+// Column sequence: the band segments are independent, so their columns are interleaved (step t of
+// every segment, then step t+1, ...), followed by the closure columns in order:
+//     seq(s) = (s % nseg) * segT + s / nseg   for s < band = nseg * segT,      seq(s) = s   otherwise.
 // Tasks, in ticket order (P = potrf, T = trsm slab of 16 rows, S = update; pair 0 is the tile below the
 // diagonal, the one the next potrf waits for: it is updated in 4 slabs by 4 CTAs, the other tiles
-// whole):
-//     P(c0) | T(c0,*) S(c0,pair 0) P(c0+1) S(c0,rest) | T(c0+1,*) S(c0+1,pair 0) P(c0+2) S(c0+1,rest) | ...
+// whole).  next(k) is k+1 inside a segment and inside the closure block, the first closure column
+// after the last band column of the sequence, nothing at the end of the other segments:
+//     P(first column of every segment) | block(seq 0) | block(seq 1) | ...
+//     block(k) = T(k,*)  S(k,pair 0)  P(next(k))  S(k,rest)
 // A persistent CTA takes the next ticket, waits for the task's inputs, runs it, publishes it:
-//     P(k)       waits until tile (k,k) has received every update of columns c0..k-1      -> flagA[k]
-//     T(k,a,q)   waits for flagA[k] and for tile (i_a,k) to be fully updated              -> cntB[k]++
+//     P(k)       waits until tile (k,k) has received every update of the columns before k     -> flagA[k]
+//     T(k,a,q)   waits for flagA[k] and for tile (i_a,k) to be fully updated                  -> cntB[k]++
 //     S(k,a,b,q) waits for cntB[k] == all slabs of column k, and for the updates of earlier columns to
-//                the same tile (plain read-modify-write, so they are applied in column order) -> upd[tile]++
-// The number of updates a tile receives from columns c0..k-1 is a popcount over the symbolic
-// structure bits.  Every wait is for a task with a smaller ticket, i.e. one that is finished or
-// running on a resident CTA, so the graph cannot deadlock whatever the grid size; a watchdog turns a
-// broken invariant into a failed factorisation (zero update) instead of a hung GPU.
+//                the same tile (plain read-modify-write, so they are applied in column order)  -> upd[tile]+=
+//                Exception: closure tiles updated from band columns -- every segment updates them,
+//                in no particular order -- take atomic adds and wait for nobody.
+// The number of updates a tile receives from the columns before k is a popcount over the symbolic
+// structure bits (columns of other segments never touch a band tile, so "before k" can simply mean
+// index < k).  Every wait is for a task with a smaller ticket, i.e. one that is finished or running
+// on a resident CTA, so the graph cannot deadlock whatever the grid size; a watchdog turns a broken
+// invariant into a failed factorisation (zero update) instead of a hung GPU.
 // rhs blocks are updated with atomics: two columns that do not touch each other may both update the
 // same row block.
 // ---------------------------------------------------------------------------------------------
@@ -784,24 +792,35 @@ __device__ __forceinline__ void chain_wait(const unsigned *ptr, unsigned target,
 }
 
 template <int SLAB>
-__global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int c0, int total) {
+__global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int nseg, int segT, int total) {
   extern __shared__ double s_buf[];
   constexpr int SPLIT = GBA_NB / SLAB;
   __shared__ int s_task[5];  // role, kk, a, b, q
   __shared__ unsigned s_need[2];
   const int tid = threadIdx.x, nT = p.st->n_tiles;
-  int col = c0, base = 1;  // ticket of the first task of column `col`'s block (thread 0 only)
+  const int band = nseg > 1 ? nseg * segT : 0, ninit = nseg > 1 ? nseg : 1;
+  const int atomic_from = nseg > 1 ? band : (1 << 30);
+  auto seq = [&](int s_) { return s_ < band ? (s_ % nseg) * segT + s_ / nseg : s_; };
+  auto next_of = [&](int s_, int kk_) {  // column whose potrf is issued inside block(kk_), or -1
+    if (s_ < band) {
+      if (s_ / nseg + 1 < segT) return kk_ + 1;
+      return (s_ == band - 1 && band < nT) ? band : -1;
+    }
+    return kk_ + 1 < nT ? kk_ + 1 : -1;
+  };
+  int spos = 0, base = ninit;  // sequence position and first ticket of its block (thread 0 only)
   for (;;) {
     __syncthreads();  // the previous task's shared memory is dead
     if (tid == 0) {
-      const int t = (int)atomicAdd(&sb.ticket[c0], 1u);
+      const int t = (int)atomicAdd(&sb.ticket[0], 1u);
       int role = -1, kk = 0, a = 0, b = 0, q = 0;
-      if (t == 0) {
+      if (t < ninit) {
         role = 0;
-        kk = c0;
+        kk = nseg > 1 ? t * segT : 0;
       } else if (t < total) {
-        for (;;) {  // tickets only grow: the walk over the columns is amortised
-          const int cnt = sb.colcnt[col], pairs = cnt * (cnt + 1) / 2, nxt = (col + 1 < nT) ? 1 : 0;
+        for (;;) {  // tickets only grow: the walk over the sequence is amortised
+          const int col = seq(spos), nx = next_of(spos, col);
+          const int cnt = sb.colcnt[col], pairs = cnt * (cnt + 1) / 2, nxt = nx >= 0 ? 1 : 0;
           const int n = SPLIT * cnt + (cnt > 0 ? SPLIT + pairs - 1 : 0) + nxt;
           if (t < base + n) {
             int o = t - base;
@@ -815,7 +834,7 @@ __global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int c0
               } else {
                 if (cnt > 0) o -= SPLIT;
                 if (nxt && o == 0) {
-                  role = 0; kk = col + 1;
+                  role = 0; kk = nx;
                 } else {
                   o -= nxt;
                   int pr = 1 + o;  // whole-tile update
@@ -829,7 +848,7 @@ __global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int c0
             break;
           }
           base += n;
-          col++;
+          spos++;
         }
       }
       s_task[0] = role; s_task[1] = kk; s_task[2] = a; s_task[3] = b; s_task[4] = q;
@@ -842,17 +861,15 @@ __global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int c0
     if (role == 0) ti = tj = kk;
     else if (role == 1) { ti = sb.colrows[kk * p.nT + a]; tj = kk; }
     else { ti = sb.colrows[kk * p.nT + a]; tj = sb.colrows[kk * p.nT + b]; }
+    // closure tile updated from a band column: atomic, unordered
+    const bool unordered = role >= 2 && tj >= atomic_from && kk < band;
     if (tid < 32) {
       unsigned n = 0;
-      if (tid < TS_WORDS) {
+      if (tid < TS_WORDS && !unordered) {
         unsigned m = sb.tbits[ti * TS_WORDS + tid] & sb.tbits[tj * TS_WORDS + tid];
-        // keep bits c0 <= c < kk of this word
-        const int lo = c0 - 32 * tid, hi = kk - 32 * tid;
-        if (hi <= 0 || lo >= 32) m = 0;
-        else {
-          if (lo > 0) m &= ~0u << lo;
-          if (hi < 32) m &= (1u << hi) - 1u;
-        }
+        const int hi = kk - 32 * tid;  // keep bits c < kk of this word
+        if (hi <= 0) m = 0;
+        else if (hi < 32) m &= (1u << hi) - 1u;
         n = __popc(m);
       }
 #pragma unroll
@@ -870,8 +887,7 @@ __global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int c0
     __syncthreads();
     const bool failed = __ldcg(sb.fail) != 0;
     if (role == 0) {
-      // (the first column may already have been factorised by the look-ahead of the launch before)
-      if (!failed && ld_acquire(&sb.flagA[kk]) == 0u) role_potrf(p, sb, kk, s_buf);
+      if (!failed) role_potrf(p, sb, kk, s_buf);
       __threadfence();
       __syncthreads();
       if (tid == 0) atomicExch(&sb.flagA[kk], 1u);
@@ -881,12 +897,12 @@ __global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int c0
       __syncthreads();
       if (tid == 0) atomicAdd(&sb.cntB[kk], 1u);
     } else if (role == 2) {
-      if (!failed) role_syrk<SLAB>(p, sb, kk, a, b, q, 1 << 30, s_buf);
+      if (!failed) role_syrk<SLAB>(p, sb, kk, a, b, q, kk < band ? atomic_from : (1 << 30), s_buf);
       __threadfence();
       __syncthreads();
       if (tid == 0) atomicAdd(const_cast<unsigned *>(updp), 1u);
     } else {  // a whole tile at once: a quarter of the tasks, the L[j,kk] operand is loaded once instead of 4 times
-      if (!failed) role_syrk<GBA_NB>(p, sb, kk, a, b, 0, 1 << 30, s_buf);
+      if (!failed) role_syrk<GBA_NB>(p, sb, kk, a, b, 0, kk < band ? atomic_from : (1 << 30), s_buf);
       __threadfence();
       __syncthreads();
       if (tid == 0) atomicAdd(const_cast<unsigned *>(updp), (unsigned)SPLIT);
