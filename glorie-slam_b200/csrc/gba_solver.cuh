@@ -766,9 +766,9 @@ __global__ void __launch_bounds__(256) k_panel(BaParams p, SolverBufs sb, int kk
 //     block(k) = T(k,*)  S(k,pair 0)  P(next(k))  S(k,rest)
 // A persistent CTA takes the next ticket, waits for the task's inputs, runs it, publishes it:
 //     P(k)       waits until tile (k,k) has received every update of the columns before k     -> flagA[k]
-//     T(k,a,q)   waits for flagA[k] and for tile (i_a,k) to be fully updated                  -> cntB[k]++
-//     S(k,a,b,q) waits for cntB[k] == all slabs of column k, and for the updates of earlier columns to
-//                the same tile (plain read-modify-write, so they are applied in column order)  -> upd[tile]+=
+//     T(k,a,q)   waits for flagA[k] and for tile (i_a,k) to be fully updated        -> upd[(i_a,k)] += TDONE
+//     S(k,a,b,q) waits until both operand tiles (i_a,k), (i_b,k) are solved, and for the updates of earlier
+//                columns to the target tile (plain read-modify-write: applied in column order) -> upd[(i_a,i_b)]+=
 //                Exception: closure tiles updated from band columns -- every segment updates them,
 //                in no particular order -- take atomic adds and wait for nobody.
 // The number of updates a tile receives from the columns before k is a popcount over the symbolic
@@ -780,6 +780,7 @@ __global__ void __launch_bounds__(256) k_panel(BaParams p, SolverBufs sb, int kk
 // same row block.
 // ---------------------------------------------------------------------------------------------
 #define CHAIN_WATCHDOG (1 << 21)  // polls of >= 32 ns: > 60 ms
+#define CHAIN_TDONE (1u << 20)      // upd[tile]: low 20 bits count update slabs, the rest solved slabs
 __device__ __forceinline__ void chain_wait(const unsigned *ptr, unsigned target, int *fail) {
   int spins = 0;
   while (ld_acquire(ptr) < target) {
@@ -881,7 +882,10 @@ __global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int ns
     const unsigned *updp = sb.upd + p.tslot[ti * p.nT + tj];
     if (tid == 0) {
       if (role == 1) chain_wait(&sb.flagA[kk], 1u, sb.fail);
-      if (role >= 2) chain_wait(&sb.cntB[kk], (unsigned)(SPLIT * sb.colcnt[kk]), sb.fail);
+      if (role >= 2) {  // both operand tiles solved: their counters carry one CHAIN_TDONE per slab
+        chain_wait(sb.upd + p.tslot[ti * p.nT + kk], (unsigned)SPLIT * CHAIN_TDONE, sb.fail);
+        chain_wait(sb.upd + p.tslot[tj * p.nT + kk], (unsigned)SPLIT * CHAIN_TDONE, sb.fail);
+      }
       chain_wait(updp, need, sb.fail);
     }
     __syncthreads();
@@ -895,7 +899,7 @@ __global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int ns
       if (!failed) role_trsm<SLAB>(p, sb, kk, a, q, 0, s_buf);
       __threadfence();
       __syncthreads();
-      if (tid == 0) atomicAdd(&sb.cntB[kk], 1u);
+      if (tid == 0) atomicAdd(const_cast<unsigned *>(updp), CHAIN_TDONE);
     } else if (role == 2) {
       if (!failed) role_syrk<SLAB>(p, sb, kk, a, b, q, kk < band ? atomic_from : (1 << 30), s_buf);
       __threadfence();
