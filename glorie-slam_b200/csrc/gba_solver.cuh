@@ -369,7 +369,7 @@ __device__ void role_potrf(const BaParams &p, const SolverBufs &sb, int kk, doub
   TilePtr X = reinterpret_cast<TilePtr>(s_buf + TILE_STRIDE);
   TilePtr Tm = reinterpret_cast<TilePtr>(s_buf + 2 * TILE_STRIDE);
   __shared__ int s_bad;
-  __shared__ double s_v[GBA_NB], s_rd[GBA_NB], s_dinv[GBA_NB], s_col[2][GBA_NB];
+  __shared__ double s_v[GBA_NB], s_rd[GBA_NB], s_dinv[GBA_NB], s_col[2][2][GBA_NB];
   const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
   double *T = p.sys + (size_t)p.tslot[kk * p.nT + kk] * GBA_NB2;
   if (tid == 0) s_bad = 0;
@@ -387,48 +387,66 @@ __device__ void role_potrf(const BaParams &p, const SolverBufs &sb, int kk, doub
     (&Lo[0][0])[i] = 0.0;
     (&X[0][0])[i] = 0.0;
   }
-  if (tx == 0) {  // column 0 -> buffer 0
+  // Two pivots per barrier.  The owners publish columns j and j+1 as they stand after pivots < j;
+  // every thread derives the pivot-j update of column j+1 itself (B' = B - A * A[j+1] / d0) and
+  // applies both rank-1 updates.  1/d1 = d0 / (d0 * B[j+1] - A[j+1]^2) does not wait for 1/d0.
+  if (tx < 2) {  // columns 0, 1 -> buffer 0
 #pragma unroll
-    for (int u = 0; u < 4; u++) s_col[0][ty + 16 * u] = a[u][0];
+    for (int u = 0; u < 4; u++) s_col[0][tx][ty + 16 * u] = a[u][0];
   }
   __syncthreads();
   bool bad = false;
 #pragma unroll
   for (int v0 = 0; v0 < 4; v0++) {  // columns 16 v0 .. 16 v0 + 15
-    for (int jj = 0; jj < 16; jj++) {
+    for (int jj = 0; jj < 16; jj += 2) {
       const int j = 16 * v0 + jj;
-      const double *col = s_col[j & 1];
-      const double d = col[j];
-      if (!(d > 0.0) || isinf(d)) bad = true;  // SimplicialLLT: NumericalIssue on a non-positive pivot
+      const double *cA = s_col[(j >> 1) & 1][0], *cB = s_col[(j >> 1) & 1][1];
+      const double d0 = cA[j], e = cA[j + 1], f = cB[j + 1];
       // rows / columns below 16 v0 are finished: only the sub-blocks u, v >= v0 are still live
-      double ar[4], ac[4], pr[4][4];
+      double arA[4], acA[4], arB[4], acB[4];
 #pragma unroll
       for (int u = v0; u < 4; u++) {
-        ar[u] = col[ty + 16 * u];
-        ac[u] = col[tx + 16 * u];
+        arA[u] = cA[ty + 16 * u];
+        acA[u] = cA[tx + 16 * u];
+        arB[u] = cB[ty + 16 * u];
+        acB[u] = cB[tx + 16 * u];
       }
-      // the products do not depend on 1/d: they are formed while the reciprocal is in flight
+      const double lA = (tid < GBA_NB) ? cA[tid] : 0.0, lB = (tid < GBA_NB) ? cB[tid] : 0.0;
+      const double t = fma(d0, f, -e * e);  // d0 * d1
+      const double dinv0 = fast_rcp(d0), rt = fast_rcp(t);
+      const double m = e * dinv0;           // L[j+1][j] / L[j][j], unscaled form
+      const double d1 = fma(-e, m, f);
+      const double dinv1 = d0 * rt;
+      if (!(d0 > 0.0) || isinf(d0) || !(d1 > 0.0) || isinf(d1)) bad = true;  // SimplicialLLT: NumericalIssue
 #pragma unroll
-      for (int u = v0; u < 4; u++)
+      for (int u = v0; u < 4; u++) {
+        arB[u] = fma(-arA[u], m, arB[u]);
+        acB[u] = fma(-acA[u], m, acB[u]);
+      }
+      if (tid < GBA_NB) {  // unscaled columns of L, scaled after the loop
+        Lo[tid][j] = (tid >= j) ? lA : 0.0;
+        Lo[tid][j + 1] = (tid >= j + 1) ? fma(-lA, m, lB) : 0.0;
+      }
+      if (tid == 0) {  // the pivots themselves; exact scaling after the loop
+        s_dinv[j] = d0;
+        s_dinv[j + 1] = d1;
+      }
 #pragma unroll
-        for (int v = v0; v < 4; v++) pr[u][v] = ar[u] * ac[v];
-      const double dinv = fast_rcp(d);
-      if (tid < GBA_NB) Lo[tid][j] = (tid >= j) ? col[tid] : 0.0;  // unscaled, scaled after the loop
-      if (tid == 0) s_dinv[j] = d;  // the pivot itself; exact scaling after the loop
+      for (int u = v0; u < 4; u++) {
+        const double ra = arA[u] * dinv0, rb = arB[u] * dinv1;
 #pragma unroll
-      for (int u = v0; u < 4; u++)
+        for (int v = v0; v < 4; v++) a[u][v] = fma(-rb, acB[v], fma(-ra, acA[v], a[u][v]));
+      }
+      // owners of columns j+2, j+3 publish them into the other buffer
+      if (jj < 14) {
+        if (tx == jj + 2 || tx == jj + 3) {
 #pragma unroll
-        for (int v = v0; v < 4; v++) a[u][v] = fma(-pr[u][v], dinv, a[u][v]);
-      // owners of column j+1 publish it into the other buffer
-      if (jj < 15) {
-        if (tx == jj + 1) {
-#pragma unroll
-          for (int u = 0; u < 4; u++) s_col[(j + 1) & 1][ty + 16 * u] = a[u][v0];
+          for (int u = 0; u < 4; u++) s_col[((j >> 1) + 1) & 1][tx - jj - 2][ty + 16 * u] = a[u][v0];
         }
       } else if (v0 < 3) {
-        if (tx == 0) {
+        if (tx < 2) {
 #pragma unroll
-          for (int u = 0; u < 4; u++) s_col[(j + 1) & 1][ty + 16 * u] = a[u][(v0 + 1) & 3];
+          for (int u = 0; u < 4; u++) s_col[((j >> 1) + 1) & 1][tx][ty + 16 * u] = a[u][(v0 + 1) & 3];
         }
       }
       __syncthreads();
