@@ -390,6 +390,16 @@ def main():
                          "note": "producer-bound: the CUDA cores rebuild the operand rows (about 170 instructions per "
                                  "edge pixel); the MMAs run underneath"}
 
+    # The factorisation (k_chain, one launch, the largest single kernel) is bound by neither HBM nor a
+    # throughput pipe but by its dependency chain: potrf -> trsm -> update per tile column.
+    fac_ms = stages.get("factor", {}).get("ms_per_step", 0.0) / max(iters, 1)
+    info2 = _gba.query(ctx)
+    roofline_chain = {"bound": "dependency chain (fp64 tile Cholesky)", "kernel": "k_chain", "ms_per_launch": fac_ms,
+                      "sequential_tile_columns": info2.chain_columns,
+                      "us_per_column": 1e3 * fac_ms / max(info2.chain_columns, 1),
+                      "note": "per column: potrf of a 64x64 fp64 tile (~19 us, two pivots per barrier) + one trsm "
+                              "slab + one update + three flag hops; see DESIGN.md section 3"}
+
     # ---- end to end: pinned host buffers -> public API -> host, copies inside the timed region ----
     # Every step copies ITS inputs from pinned host memory and reads its result back.  The copies run
     # on a second stream into one of two device buffer sets, so the transfer of step s+1 overlaps the
@@ -468,7 +478,7 @@ def main():
                        "lm": g.lm, "ep": g.ep, "sharding": "by source keyframe, %d rank(s)" % world,
                        "l2": "inputs (%.0f MB per rank) larger than L2" % (input_bytes / 1e6) if l2_flush is None
                              else "256 MB L2 flush between steps"},
-            "roofline": roofline, "roofline_gram": roofline_gram, "stages": stages, "cpu_baseline": cb, "e2e": e2e, "reference_cuda": ref_cuda,
+            "roofline": roofline, "roofline_gram": roofline_gram, "roofline_chain": roofline_chain, "stages": stages, "cpu_baseline": cb, "e2e": e2e, "reference_cuda": ref_cuda,
             "gpu_launches": int(launches_per_step * args.steps), "gpu_launches_per_step": int(launches_per_step),
             "clocks": clocks,
             "solver": {"tiles": info.n_tiles, "active_tiles": info.n_active_tiles, "chol_failures": info.chol_failures},

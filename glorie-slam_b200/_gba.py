@@ -24,7 +24,7 @@ _ctx = {}
 class Info(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int) for n in (
         "n_depth_frames", "n_poses", "max_out_degree", "chol_failures", "n_tiles", "n_active_tiles",
-        "kernel_launches", "reserved")]
+        "kernel_launches", "chain_columns")]
 
 
 def lib():

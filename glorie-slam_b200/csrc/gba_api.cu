@@ -711,7 +711,8 @@ extern "C" int gba_query(gba_ctx *c, gba_info *info) {
   info->n_tiles = st.n_tiles;
   info->n_active_tiles = st.n_slots;
   info->kernel_launches = c->launches;
-  info->reserved = 0;
+  // sequential tile columns of the factorisation: one band segment's worth plus the closure block
+  info->chain_columns = (st.n_seg > 1 ? st.seg_tiles : 0) + (st.n_tiles - (st.n_seg > 1 ? st.n_seg * st.seg_tiles : 0));
   return GBA_OK;
 }
 

@@ -115,7 +115,7 @@ typedef struct gba_info {
   int n_tiles;          /* tile rows of the reduced camera matrix             */
   int n_active_tiles;   /* lower-triangular tiles touched after symbolic fill */
   int kernel_launches;  /* kernels launched by the last gba_ba / gba_dspo call */
-  int reserved;
+  int chain_columns;    /* tile columns on the factorisation's critical path: one band segment + the closure block */
 } gba_info;
 int gba_query(gba_ctx *ctx, gba_info *info);
 
