@@ -339,6 +339,7 @@ extern "C" int gba_ba_begin(gba_ctx *c, float *poses, float *disps, const float 
     const char *e = getenv("GBA_GRAM_TC");
     p.tc_maxdeg = (e && e[0] == '0') ? 0 : GT_MAXDEG;
     p.wdog = c->wdog;
+    p.fail = c->sb.fail;
     // the bulk copies of k_gram_tc need 16-byte aligned rows (HW % 4 == 0 is already required)
     if ((((uintptr_t)p.targets | (uintptr_t)p.weights | (uintptr_t)p.disps) & 15) != 0) p.tc_maxdeg = 0;
   }

@@ -68,6 +68,7 @@ struct BaParams {
   int *perm;      // [P] pose -> position in the reduced system (ordering below)
   int *iperm;     // [positions] position -> pose, -1 for padding positions
   int nT;         // STRIDE of the tile tables (upper bound); the actual count is st->n_tiles
+  int *fail;      // the solver's failure flag (SolverBufs::fail): a pipeline watchdog raises it too
   int *wdog;      // [256] watchdog records of k_gram_tc: [0] = count, then 6 ints per record
   int tc_maxdeg;  // keyframes with out-degree <= this go to k_gram_tc (tensor cores), the rest to k_gram; 0 = all k_gram
   int ld;

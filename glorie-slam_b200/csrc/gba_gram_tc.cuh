@@ -172,10 +172,12 @@ __device__ __forceinline__ float tf32_rna(float x) {
 // A wait that is still unsatisfied after GT_WATCHDOG probes (>= 10 ms; a healthy wait is microseconds)
 // means the pipeline protocol is broken.  Rather than hang the SM -- and with it the process and the
 // GPU -- the warp records where it was and leaves; the others follow as their own waits expire, the
-// CTA still frees its tensor memory, and the host finds the count in GBA_GET_WATCHDOG.
+// CTA still frees its tensor memory, the iteration is treated like a failed factorisation (zero
+// update, gba_info.chol_failures) and the host finds the records in GBA_GET_WATCHDOG.
 #define GT_WATCHDOG 25000
 __device__ __noinline__ void gram_tc_stuck(const BaParams &p, int site, int a, int b) {
   if ((threadIdx.x & 31) == 0) {
+    *p.fail = 4;  // the iteration ends like a failed factorisation: zero pose update, counted in chol_failures
     const int n = atomicAdd(p.wdog, 1);
     if (n < 42) {
       int *r = p.wdog + 1 + 6 * n;
