@@ -276,6 +276,29 @@ def test_tensor_core_gram_matches_cuda_core_gram(n, ht, wd, monkeypatch):
     assert get_array(r.ctx, _gba.GET_WATCHDOG, (256,), np.int32)[0] == 0  # no pipeline wait ever expired
 
 
+@pytest.mark.parametrize("n,e,r", [(60, 700, 3), (260, 4200, 8)])
+def test_task_graph_factorisation_matches_per_column_launches(n, e, r, monkeypatch):
+    """k_chain (whole factorisation as one dependency graph of tile tasks) against the launch-per-column
+    sequence it replaced: same tiles, same arithmetic, only the order of the atomic closure updates
+    may differ.  The larger graph has several band segments and a closure block."""
+    g = synth.make_graph(n, e, r, iters=2, seed=n + e, ht=24, wd=32, lm=1e-5, ep=0.01)
+    monkeypatch.setenv("GBA_NO_CHAIN", "1")
+    r0 = run_ba(g)
+    monkeypatch.delenv("GBA_NO_CHAIN")
+    r1 = run_ba(g)
+    assert r0.info.chol_failures == 0 and r1.info.chol_failures == 0
+    assert r1.info.chain_columns <= r1.info.n_tiles
+    if n > 200:
+        assert r1.info.chain_columns < r1.info.n_tiles  # nested dissection shortened the chain
+    assert rel(sign_normalise(r1.poses), sign_normalise(r0.poses)) < 5e-6
+    assert rel(r1.disps, r0.disps) < 5e-6
+    assert r1.info.kernel_launches < r0.info.kernel_launches
+    o = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj, g.t0, g.t1,
+                  g.iters, g.lm, g.ep, precision="f64")
+    assert rel(sign_normalise(r1.poses), sign_normalise(o.poses)) < STATE_RTOL
+    assert rel(r1.disps, o.disps) < STATE_RTOL
+
+
 def test_argument_errors():
     import droid_backends
 
