@@ -192,6 +192,33 @@ def reference_cuda_side_by_side(dev, name="C", reps=5):
             e_ = ((s_[:, None, None] * p + q_[:, None, None] - t_).abs() * w).sum((1, 2)) / a11
             return s_, q_, e_
 
+        # layout hand-off: what GlORIE does today -- permute + contiguous copy of the
+        # network's [E,ht,wd,2] tensors, then ba -- against ba_interleaved on the tensors as they are
+        tg_hwc = rest[2].permute(0, 2, 3, 1).contiguous()
+        wg_hwc = rest[3].permute(0, 2, 3, 1).contiguous()
+
+        def planar_with_permute():
+            p_, d_ = base[0].clone(), base[1].clone()
+            droid_backends.ba(p_, d_, rest[0], rest[1], tg_hwc.permute(0, 3, 1, 2).contiguous(),
+                              wg_hwc.permute(0, 3, 1, 2).contiguous(), *rest[4:], g.t0, g.t1, g.iters, g.lm, g.ep, False, False)
+
+        def interleaved():
+            p_, d_ = base[0].clone(), base[1].clone()
+            droid_backends.ba_interleaved(p_, d_, rest[0], rest[1], tg_hwc, wg_hwc, *rest[4:], g.t0, g.t1, g.iters, g.lm,
+                                          g.ep, False, False)
+
+        for key, fn in (("libgba_permute_then_ba_ms", planar_with_permute), ("libgba_ba_interleaved_ms", interleaved)):
+            best = None
+            for _ in range(reps + 1):
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                torch.cuda.synchronize()
+                a.record()
+                fn()
+                b.record()
+                torch.cuda.synchronize()
+                ms = a.elapsed_time(b)
+                best = ms if best is None else min(best, ms)
+            out[key] = best
         wts = (base[1] > base[1].median()).float()
         for key, fn in (("reference_depth_filter_ms", lambda: ref.depth_filter(base[0], base[1], rest[0], ix, th)),
                         ("libgba_depth_filter_ms", lambda: droid_backends.depth_filter(base[0], base[1], rest[0], ix, th)),

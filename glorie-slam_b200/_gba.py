@@ -14,6 +14,7 @@ LIB_PATH = os.path.join(HERE, "lib", "libgba.so")
 MODE_DROID_CUDA = 0
 MODE_GEOM_PY = 1
 MODES = {"droid_cuda": MODE_DROID_CUDA, "geom_py": MODE_GEOM_PY}
+LAYOUT_INTERLEAVED = 0x100
 
 GET_KX, GET_EPTR, GET_EIDX, GET_EDGE_HV, GET_Q, GET_W, GET_SYSTEM, GET_TILEMASK, GET_GRAM, GET_WATCHDOG = range(1, 11)
 

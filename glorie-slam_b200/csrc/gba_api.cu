@@ -215,8 +215,10 @@ extern "C" int gba_create(gba_ctx **out, int device, int max_frames, int max_edg
   CKC(cudaMemset(c->sb.fail, 0, sizeof(int)));
   CKC(cudaMemset(c->st_d, 0, sizeof(Status)));
   CKC(cudaFuncSetAttribute(k_gram, cudaFuncAttributeMaxDynamicSharedMemorySize, kGramSmemMax));
-  CKC(cudaFuncSetAttribute(k_gram_tc<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gram_tc_smem(GT_MAXDEG)));
-  CKC(cudaFuncSetAttribute(k_gram_tc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gram_tc_smem(GT_MAXDEG)));
+  CKC(cudaFuncSetAttribute(k_gram_tc<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gram_tc_smem(GT_MAXDEG)));
+  CKC(cudaFuncSetAttribute(k_gram_tc<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gram_tc_smem(GT_MAXDEG)));
+  CKC(cudaFuncSetAttribute(k_gram_tc<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gram_tc_smem(GT_MAXDEG)));
+  CKC(cudaFuncSetAttribute(k_gram_tc<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gram_tc_smem(GT_MAXDEG)));
   CKC(cudaFuncSetAttribute(k_potrf_diag, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolverSmem));
   CKC(cudaFuncSetAttribute(k_trsm, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolverSmem));
   CKC(cudaFuncSetAttribute(k_syrk, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolverSmem));
@@ -318,7 +320,8 @@ extern "C" int gba_ba_begin(gba_ctx *c, float *poses, float *disps, const float 
     return fail_msg(c, GBA_ECAPACITY, "n_all %d outside [n_edges,%d]", n_all, c->E_max);
   if (t0 < 0 || t1 <= t0 || t1 > n_frames)
     return fail_msg(c, GBA_EINVAL, "optimised window [%d,%d) not inside [0,%d)", t0, t1, n_frames);
-  if (mode != GBA_MODE_DROID_CUDA && mode != GBA_MODE_GEOM_PY) return fail_msg(c, GBA_EINVAL, "unknown mode %d", mode);
+  if ((mode & ~GBA_LAYOUT_INTERLEAVED) != GBA_MODE_DROID_CUDA && (mode & ~GBA_LAYOUT_INTERLEAVED) != GBA_MODE_GEOM_PY)
+    return fail_msg(c, GBA_EINVAL, "unknown mode %d", mode);
   CK(cudaSetDevice(c->device));
   c->stream = (cudaStream_t)stream;
   c->launches = 0;
@@ -328,7 +331,8 @@ extern "C" int gba_ba_begin(gba_ctx *c, float *poses, float *disps, const float 
   p.poses = poses; p.disps = disps; p.intr = intrinsics; p.sens = disps_sens; p.targets = targets;
   p.weights = weights; p.eta = eta; p.ii = ii; p.jj = jj;
   p.N = n_frames; p.E = n_edges; p.HW = c->HW; p.wd = c->wd; p.t0 = t0; p.t1 = t1; p.P = t1 - t0;
-  p.mode = mode; p.motion_only = motion_only ? 1 : 0; p.depth_only = depth_only ? 1 : 0; p.lm = lm; p.ep = ep;
+  p.mode = mode & ~GBA_LAYOUT_INTERLEAVED; p.il = (mode & GBA_LAYOUT_INTERLEAVED) ? 1 : 0;
+  p.motion_only = motion_only ? 1 : 0; p.depth_only = depth_only ? 1 : 0; p.lm = lm; p.ep = ep;
   p.kx = c->kx; p.fmap = c->fmap; p.deg = c->deg; p.eptr = c->eptr; p.eidx = c->eidx; p.ek = c->ek;
   p.owned = owned; p.goff = c->goff; p.st = c->st_d; p.geo = c->geo; p.hpart = c->hpart; p.edge_hv = c->edge_hv;
   p.Q = c->Q; p.W = c->W; p.gram = c->gram; p.dx = c->dx; p.dz_out = c->dzbuf; p.sys = c->sys; p.tslot = c->tslot;
@@ -406,15 +410,18 @@ extern "C" int gba_ba_build(gba_ctx *c) {
   stage_begin(c, GBA_STAGE_LINEARIZE);  // brackets k_linearize alone (roofline kernel)
   if (st.K > 0) {
     dim3 grid(p.nchunk, st.K);
-    if (p.mode == 0) {
-      if (c->variant == 0) k_linearize<256, 2, 0><<<grid, 256, 0, s>>>(p);
-      else if (c->variant == 1) k_linearize<128, 2, 0><<<grid, 128, 0, s>>>(p);
-      else k_linearize<128, 1, 0><<<grid, 128, 0, s>>>(p);
-    } else {
-      if (c->variant == 0) k_linearize<256, 2, 1><<<grid, 256, 0, s>>>(p);
-      else if (c->variant == 1) k_linearize<128, 2, 1><<<grid, 128, 0, s>>>(p);
-      else k_linearize<128, 1, 1><<<grid, 128, 0, s>>>(p);
-    }
+    // (semantics mode, layout) x (CTA footprint): compile-time variants, chosen once per launch
+#define GBA_LAUNCH_K_LINEARIZE(MODE, IL)                                                    \
+  do {                                                                                   \
+    if (c->variant == 0) k_linearize<256, 2, MODE, IL><<<grid, 256, 0, s>>>(p);            \
+    else if (c->variant == 1) k_linearize<128, 2, MODE, IL><<<grid, 128, 0, s>>>(p);       \
+    else k_linearize<128, 1, MODE, IL><<<grid, 128, 0, s>>>(p);                            \
+  } while (0)
+    if (p.mode == 0 && !p.il) GBA_LAUNCH_K_LINEARIZE(0, false);
+    else if (p.mode == 0) GBA_LAUNCH_K_LINEARIZE(0, true);
+    else if (!p.il) GBA_LAUNCH_K_LINEARIZE(1, false);
+    else GBA_LAUNCH_K_LINEARIZE(1, true);
+#undef GBA_LAUNCH_K_LINEARIZE
     LAUNCH_CHECK("k_linearize");
   }
   stage_end(c);
@@ -453,8 +460,12 @@ extern "C" int gba_ba_build(gba_ctx *c) {
     if ((p.tc_maxdeg > 0 && gs_tc > 1) || (need_cc && gs_cc > 1))
       CK(cudaMemsetAsync(c->gram, 0, (size_t)st.gram_floats * sizeof(float), s));
     if (p.tc_maxdeg > 0) {  // tensor-core Gram for the keyframes with <= GT_MAXDEG out-edges
-      if (p.mode == GBA_MODE_DROID_CUDA) k_gram_tc<0><<<dim3(gs_tc, st.K), GT_NT, gram_tc_smem(st.max_deg), s>>>(p);
-      else k_gram_tc<1><<<dim3(gs_tc, st.K), GT_NT, gram_tc_smem(st.max_deg), s>>>(p);
+      const dim3 gg(gs_tc, st.K);
+      const size_t sm = gram_tc_smem(st.max_deg);
+      if (p.mode == GBA_MODE_DROID_CUDA && !p.il) k_gram_tc<0, false><<<gg, GT_NT, sm, s>>>(p);
+      else if (p.mode == GBA_MODE_DROID_CUDA) k_gram_tc<0, true><<<gg, GT_NT, sm, s>>>(p);
+      else if (!p.il) k_gram_tc<1, false><<<gg, GT_NT, sm, s>>>(p);
+      else k_gram_tc<1, true><<<gg, GT_NT, sm, s>>>(p);
       LAUNCH_CHECK("k_gram_tc");
     }
     if (need_cc) {
@@ -567,15 +578,18 @@ extern "C" int gba_ba_solve(gba_ctx *c) {
   if (!p.motion_only && st.K > 0) {
     stage_begin(c, GBA_STAGE_BACKSUB);
     dim3 grid(p.nchunk, st.K);
-    if (p.mode == 0) {
-      if (c->variant == 0) k_backsub<256, 2, 0><<<grid, 256, 0, s>>>(p);
-      else if (c->variant == 1) k_backsub<128, 2, 0><<<grid, 128, 0, s>>>(p);
-      else k_backsub<128, 1, 0><<<grid, 128, 0, s>>>(p);
-    } else {
-      if (c->variant == 0) k_backsub<256, 2, 1><<<grid, 256, 0, s>>>(p);
-      else if (c->variant == 1) k_backsub<128, 2, 1><<<grid, 128, 0, s>>>(p);
-      else k_backsub<128, 1, 1><<<grid, 128, 0, s>>>(p);
-    }
+    // (semantics mode, layout) x (CTA footprint): compile-time variants, chosen once per launch
+#define GBA_LAUNCH_K_BACKSUB(MODE, IL)                                                    \
+  do {                                                                                   \
+    if (c->variant == 0) k_backsub<256, 2, MODE, IL><<<grid, 256, 0, s>>>(p);            \
+    else if (c->variant == 1) k_backsub<128, 2, MODE, IL><<<grid, 128, 0, s>>>(p);       \
+    else k_backsub<128, 1, MODE, IL><<<grid, 128, 0, s>>>(p);                            \
+  } while (0)
+    if (p.mode == 0 && !p.il) GBA_LAUNCH_K_BACKSUB(0, false);
+    else if (p.mode == 0) GBA_LAUNCH_K_BACKSUB(0, true);
+    else if (!p.il) GBA_LAUNCH_K_BACKSUB(1, false);
+    else GBA_LAUNCH_K_BACKSUB(1, true);
+#undef GBA_LAUNCH_K_BACKSUB
     LAUNCH_CHECK("k_backsub");
     stage_end(c);
   }

@@ -70,12 +70,24 @@ struct BaParams {
   int nT;         // STRIDE of the tile tables (upper bound); the actual count is st->n_tiles
   int *fail;      // the solver's failure flag (SolverBufs::fail): a pipeline watchdog raises it too
   int *wdog;      // [256] watchdog records of k_gram_tc: [0] = count, then 6 ints per record
+  int il;         // targets / weights are [E,ht,wd,2] (interleaved, as the update network emits them) instead of [E,2,ht,wd]
   int tc_maxdeg;  // keyframes with out-degree <= this go to k_gram_tc (tensor cores), the rest to k_gram; 0 = all k_gram
   int ld;
 };
 
 __device__ __forceinline__ float ldg_stream(const float *p) { return __ldcs(p); }
 __device__ __forceinline__ float4 ldg_stream4(const float *p) { return __ldcs(reinterpret_cast<const float4 *>(p)); }
+// u / v components of 4 consecutive pixels px..px+3 of one edge's [2,HW] (planar) or [HW,2] (interleaved) block
+__device__ __forceinline__ void ldg_uv4(const float *base, int HW, int px, bool il, float4 &u, float4 &v) {
+  if (il) {
+    const float4 a = ldg_stream4(base + 2 * px), b = ldg_stream4(base + 2 * px + 4);
+    u = make_float4(a.x, a.z, b.x, b.z);
+    v = make_float4(a.y, a.w, b.y, b.w);
+  } else {
+    u = ldg_stream4(base + px);
+    v = ldg_stream4(base + HW + px);
+  }
+}
 
 // address of element (r, c), r >= c, of the tile-packed lower-triangular system
 __device__ __forceinline__ double *sys_at(const BaParams &p, int r, int c) {

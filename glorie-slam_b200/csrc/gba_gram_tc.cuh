@@ -186,7 +186,7 @@ __device__ __noinline__ void gram_tc_stuck(const BaParams &p, int site, int a, i
   }
 }
 
-template <int MODE>
+template <int MODE, bool IL>
 __global__ void __launch_bounds__(GT_NT, 1) k_gram_tc(BaParams p) {
   extern __shared__ __align__(128) unsigned char s_raw[];
   const int k = blockIdx.y;
@@ -251,7 +251,10 @@ __global__ void __launch_bounds__(GT_NT, 1) k_gram_tc(BaParams p) {
     const float *src;
     if (c < 4 * deg) {
       const int n = p.eidx[e0 + (c >> 2)], a = c & 3;
-      src = ((a < 2) ? p.targets : p.weights) + ((size_t)n * 2 + (a & 1)) * HW;
+      // interleaved layout: rows 4q, 4q+1 of a slot are the two 64-float halves of ONE run of 128 floats
+      // (u0 v0 u1 v1 ...) of the edge's targets, rows 4q+2, 4q+3 of its weights
+      src = IL ? ((a < 2) ? p.targets : p.weights) + (size_t)n * 2 * HW + (a & 1) * GT_IPX
+                 : ((a < 2) ? p.targets : p.weights) + ((size_t)n * 2 + (a & 1)) * HW;
     } else {
       const int a = c - 4 * deg;
       src = (a == 0 ? p.disps + (size_t)frame * HW : a == 1 ? p.Q + (size_t)k * HW : p.W + (size_t)k * HW);
@@ -315,10 +318,16 @@ __global__ void __launch_bounds__(GT_NT, 1) k_gram_tc(BaParams p) {
 #pragma unroll
         for (int h = 0; h < NE; h++) {
           const int q = b0 + h * GT_NPW;
-          ctu[h][u] = in[(4 * q + 0) * GT_IPX + u * GT_K];
-          ctv[h][u] = in[(4 * q + 1) * GT_IPX + u * GT_K];
-          cwu[h][u] = in[(4 * q + 2) * GT_IPX + u * GT_K];
-          cwv[h][u] = in[(4 * q + 3) * GT_IPX + u * GT_K];
+          if (IL) {  // (u, v) pairs: pixel u * 32 + lane of the slot sits at float 2 * (u * 32 + lane) of the run
+            const float2 tt = *reinterpret_cast<const float2 *>(in + lane + (4 * q + 0) * GT_IPX + 2 * u * GT_K);
+            const float2 ww = *reinterpret_cast<const float2 *>(in + lane + (4 * q + 2) * GT_IPX + 2 * u * GT_K);
+            ctu[h][u] = tt.x; ctv[h][u] = tt.y; cwu[h][u] = ww.x; cwv[h][u] = ww.y;
+          } else {
+            ctu[h][u] = in[(4 * q + 0) * GT_IPX + u * GT_K];
+            ctv[h][u] = in[(4 * q + 1) * GT_IPX + u * GT_K];
+            cwu[h][u] = in[(4 * q + 2) * GT_IPX + u * GT_K];
+            cwv[h][u] = in[(4 * q + 3) * GT_IPX + u * GT_K];
+          }
         }
         czq[u] = in[(4 * deg + 0) * GT_IPX + u * GT_K];
         cqv[u] = in[(4 * deg + 1) * GT_IPX + u * GT_K];
@@ -422,10 +431,16 @@ __global__ void __launch_bounds__(GT_NT, 1) k_gram_tc(BaParams p) {
   #pragma unroll
           for (int h = 0; h < 2; h++) {
             const int q = (h < ne) ? b0 + h * GT_NPW : b0;
-            ctu[h][u] = in[(4 * q + 0) * GT_IPX + u * GT_K];
-            ctv[h][u] = in[(4 * q + 1) * GT_IPX + u * GT_K];
-            cwu[h][u] = in[(4 * q + 2) * GT_IPX + u * GT_K];
-            cwv[h][u] = in[(4 * q + 3) * GT_IPX + u * GT_K];
+            if (IL) {
+              const float2 tt = *reinterpret_cast<const float2 *>(in + lane + (4 * q + 0) * GT_IPX + 2 * u * GT_K);
+              const float2 ww = *reinterpret_cast<const float2 *>(in + lane + (4 * q + 2) * GT_IPX + 2 * u * GT_K);
+              ctu[h][u] = tt.x; ctv[h][u] = tt.y; cwu[h][u] = ww.x; cwv[h][u] = ww.y;
+            } else {
+              ctu[h][u] = in[(4 * q + 0) * GT_IPX + u * GT_K];
+              ctv[h][u] = in[(4 * q + 1) * GT_IPX + u * GT_K];
+              cwu[h][u] = in[(4 * q + 2) * GT_IPX + u * GT_K];
+              cwv[h][u] = in[(4 * q + 3) * GT_IPX + u * GT_K];
+            }
           }
           czq[u] = in[(4 * deg + 0) * GT_IPX + u * GT_K];
           cqv[u] = in[(4 * deg + 1) * GT_IPX + u * GT_K];
@@ -527,9 +542,21 @@ __global__ void __launch_bounds__(GT_NT, 1) k_gram_tc(BaParams p) {
       const int start = (tile0 + j * GT_TPI) * GT_K;
       const int npx = min(min(GT_IPX, HW - start), (nloc - j * GT_TPI) * GT_K);  // HW % 4 == 0: whole 16 B pieces
       const uint32_t dst0 = tc::smem_u32(s_in) + (uint32_t)is * GT_IN_BYTES + (uint32_t)c4 * 4u;
-      if (c4 < npx) {
+      if (!IL) {
+        if (c4 < npx) {
 #pragma unroll 4
-        for (int c = sub; c < nrow; c += 2) tc::cp_async16(dst0 + (uint32_t)c * (GT_IPX * 4), s_row[c] + start + c4);
+          for (int c = sub; c < nrow; c += 2) tc::cp_async16(dst0 + (uint32_t)c * (GT_IPX * 4), s_row[c] + start + c4);
+        }
+      } else {
+        const int nedge = 4 * deg;  // edge rows advance 2 floats per pixel, keyframe rows 1
+#pragma unroll 4
+        for (int c = sub; c < nrow; c += 2) {
+          if (c < nedge) {
+            if ((c & 1) * GT_IPX + c4 < 2 * npx) tc::cp_async16(dst0 + (uint32_t)c * (GT_IPX * 4), s_row[c] + 2 * start + c4);
+          } else if (c4 < npx) {
+            tc::cp_async16(dst0 + (uint32_t)c * (GT_IPX * 4), s_row[c] + start + c4);
+          }
+        }
       }
       tc::cp_async_arrive(infull_bar(is));  // fires when this lane's copies above have landed
     }

@@ -262,7 +262,7 @@ __global__ void k_edge_geo(BaParams p) {
 // --------------------------------------------------------------------------------------------
 #define LIN_EB 8  // edges per shared-memory batch
 
-template <int NT, int NV, int MODE>
+template <int NT, int NV, int MODE, bool IL>
 __global__ void __launch_bounds__(NT, (NT >= 256) ? 2 : 3) k_linearize(BaParams p) {
   constexpr int NW = NT / 32;
   __shared__ EdgeGeo s_geo[LIN_EB];
@@ -315,10 +315,8 @@ __global__ void __launch_bounds__(NT, (NT >= 256) ? 2 : 3) k_linearize(BaParams 
 #pragma unroll
       for (int g = 0; g < NV; g++) {
         if (px[g] < HW) {
-          tu[g] = ldg_stream4(tg + px[g]);
-          tv[g] = ldg_stream4(tg + HW + px[g]);
-          wu[g] = ldg_stream4(wg + px[g]);
-          wv[g] = ldg_stream4(wg + HW + px[g]);
+          ldg_uv4(tg, HW, px[g], IL, tu[g], tv[g]);
+          ldg_uv4(wg, HW, px[g], IL, wu[g], wv[g]);
         } else {
           tu[g] = tv[g] = wu[g] = wv[g] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
@@ -616,10 +614,11 @@ __global__ void __launch_bounds__(GRAM_NT, 2) k_gram(BaParams p) {
 #pragma unroll
           for (int u = 0; u < GRAM_PB; u++) {
             const bool ok = pv && u < nq;
-            tu_[u] = ok ? ldg_stream(tgp[u] + pix) : 0.f;
-            tv_[u] = ok ? ldg_stream(tgp[u] + HW + pix) : 0.f;
-            wu_[u] = ok ? ldg_stream(wgp[u] + pix) : 0.f;
-            wv_[u] = ok ? ldg_stream(wgp[u] + HW + pix) : 0.f;
+            const int ou = p.il ? 2 * pix : pix, ov = p.il ? 2 * pix + 1 : HW + pix;
+            tu_[u] = ok ? ldg_stream(tgp[u] + ou) : 0.f;
+            tv_[u] = ok ? ldg_stream(tgp[u] + ov) : 0.f;
+            wu_[u] = ok ? ldg_stream(wgp[u] + ou) : 0.f;
+            wv_[u] = ok ? ldg_stream(wgp[u] + ov) : 0.f;
           }
         };
         if (nloc > 0) fetch(0);
@@ -664,10 +663,11 @@ __global__ void __launch_bounds__(GRAM_NT, 2) k_gram(BaParams p) {
               if (j0 + u < nq && pv) {
                 const int n = s_eid[pw + (j0 + u) * npw];
                 const float *tg = p.targets + (size_t)n * 2 * HW, *wg = p.weights + (size_t)n * 2 * HW;
-                tu_[u] = ldg_stream(tg + pix);
-                tv_[u] = ldg_stream(tg + HW + pix);
-                wu_[u] = ldg_stream(wg + pix);
-                wv_[u] = ldg_stream(wg + HW + pix);
+                const int ou = p.il ? 2 * pix : pix, ov = p.il ? 2 * pix + 1 : HW + pix;
+                tu_[u] = ldg_stream(tg + ou);
+                tv_[u] = ldg_stream(tg + ov);
+                wu_[u] = ldg_stream(wg + ou);
+                wv_[u] = ldg_stream(wg + ov);
               }
             }
 #pragma unroll
@@ -869,7 +869,7 @@ __global__ void k_damp(BaParams p, float lm, float ep) {
 // with one 6-vector per edge, delta_n = dx[jj] + B_n^T dx[k]; disps is updated in place.
 // Replaces EvT6x1 + accum + disp_retr (droid_kernels.cu:1095-1115,1409-1418,933-946,1428-1431).
 // --------------------------------------------------------------------------------------------
-template <int NT, int NV, int MODE>
+template <int NT, int NV, int MODE, bool IL>
 __global__ void __launch_bounds__(NT) k_backsub(BaParams p) {
   __shared__ EdgeGeo s_geo[LIN_EB];
   __shared__ float s_delta[LIN_EB][8];
@@ -931,10 +931,8 @@ __global__ void __launch_bounds__(NT) k_backsub(BaParams p) {
 #pragma unroll
       for (int g = 0; g < NV; g++) {
         if (px[g] < HW) {
-          tu[g] = ldg_stream4(tg + px[g]);
-          tv[g] = ldg_stream4(tg + HW + px[g]);
-          wu[g] = ldg_stream4(wg + px[g]);
-          wv[g] = ldg_stream4(wg + HW + px[g]);
+          ldg_uv4(tg, HW, px[g], IL, tu[g], tv[g]);
+          ldg_uv4(wg, HW, px[g], IL, wu[g], wv[g]);
         } else {
           tu[g] = tv[g] = wu[g] = wv[g] = make_float4(0.f, 0.f, 0.f, 0.f);
         }

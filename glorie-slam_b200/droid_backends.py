@@ -7,9 +7,9 @@ and `disps`, same return value `[dx, dz]` of the last iteration.  Put this direc
 sys.path and `import droid_backends` resolves here; depth_video.py stays unchanged.
 
 The work is done by libgba.so (hand-written sm_100a CUDA behind the C ABI in include/gba.h);
-torch only supplies device memory and the current stream.  `frame_distance` is provided as well.  The remaining functions of
-the reference module (projmap, depth_filter, iproj, corr kernels) are outside this repository's
-scope; set GBA_REFERENCE_BACKENDS to a module name to forward them.
+torch only supplies device memory and the current stream.  Also provided: `frame_distance`,
+`depth_filter` and `ba_interleaved` (rank 3).  The remaining
+functions of the reference module (projmap, iproj, corr kernels) are outside this repository's scope; set GBA_REFERENCE_BACKENDS to a module name to forward them.
 """
 from __future__ import annotations
 
@@ -38,7 +38,7 @@ def _chk(t, name, dtype):
 
 
 def ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1, iterations, lm, ep,
-       motion_only, depth_only=False):
+       motion_only, depth_only=False, _interleaved=False):
     """Dense bundle adjustment over the factor graph (ii -> jj), in place on poses / disps.
 
     poses [N,7] f32, disps [N,ht,wd] f32, intrinsics [4], disps_sens [N,ht,wd],
@@ -57,6 +57,8 @@ def ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, 
     E = int(ii.shape[0])
     if targets.numel() != E * 2 * ht * wd or weights.numel() != E * 2 * ht * wd or jj.shape[0] != E:
         raise RuntimeError("targets/weights must be [E,2,ht,wd] for E = len(ii) = len(jj)")
+    if _interleaved and (tuple(targets.shape[-3:]) != (ht, wd, 2) or tuple(weights.shape[-3:]) != (ht, wd, 2)):
+        raise RuntimeError("ba_interleaved: targets/weights must be [E,ht,wd,2]")
     t0, t1, iterations = int(t0), int(t1), int(iterations)
     dev = poses.device
     with torch.cuda.device(dev):
@@ -71,12 +73,25 @@ def ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, 
         rc = _gba.lib().gba_ba(ctx, poses.data_ptr(), disps.data_ptr(), intrinsics.data_ptr(), disps_sens.data_ptr(),
                                targets.data_ptr(), weights.data_ptr(), eta.data_ptr(), ii.data_ptr(), jj.data_ptr(),
                                N, E, eta_rows, t0, t1, iterations, float(lm), float(ep), int(bool(motion_only)),
-                               int(bool(depth_only)), _gba.MODES[SEMANTICS], dx.data_ptr(),
+                               int(bool(depth_only)), _gba.MODES[SEMANTICS] | (_gba.LAYOUT_INTERLEAVED if _interleaved else 0),
+                               dx.data_ptr(),
                                dz.data_ptr() if dz is not None else None, stream)
         _gba.check(ctx, rc)
         if dz is not None:
             dz = dz[: _gba.query(ctx).n_depth_frames]
     return [dx, dz]
+
+
+def ba_interleaved(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1, iterations, lm, ep,
+                   motion_only, depth_only=False):
+    """`ba` for targets / weights in the layout the update network produces, [E,ht,wd,2] (or
+    [1,E,ht,wd,2]): the caller skips the permute + contiguous copy of src/depth_video.py:215-216.
+    Opt-in; no counterpart in the reference extension.  Same
+    per-pixel arithmetic as `ba`."""
+    if targets.dim() == 5 and targets.shape[0] == 1:
+        targets, weights = targets[0], weights[0]
+    return ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1, iterations, lm, ep,
+              motion_only, depth_only, _interleaved=True)
 
 
 def frame_distance(poses, disps, intrinsics, ii, jj, beta):

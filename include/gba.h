@@ -35,6 +35,12 @@ typedef struct gba_ctx gba_ctx;
 /* semantics modes (the reference's two BA implementations differ) */
 #define GBA_MODE_DROID_CUDA 0 /* src/lib/droid_kernels.cu::ba_cuda -- what droid_backends.ba runs */
 #define GBA_MODE_GEOM_PY 1    /* src/geom/ba.py::BA + src/geom/chol.py::schur_solve              */
+/* Layout flag, OR-ed into `mode` of gba_ba / gba_ba_begin: targets and weights
+ * are [E,ht,wd,2] -- (u,v) interleaved, the layout the update network emits and src/geom/ba.py takes --
+ * instead of the [E,2,ht,wd] that droid_backends.ba requires.  The caller can then drop the
+ * permute + contiguous copy of src/depth_video.py:215-216 (2 x 16 B per edge pixel of extra HBM
+ * traffic per call).  Same per-pixel arithmetic as the planar call.  gba_edge_blocks_static is planar only. */
+#define GBA_LAYOUT_INTERLEAVED 0x100
 
 #define GBA_OK 0
 #define GBA_EINVAL -1   /* bad argument / index out of range / eta rows != K */

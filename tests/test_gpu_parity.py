@@ -299,6 +299,38 @@ def test_task_graph_factorisation_matches_per_column_launches(n, e, r, monkeypat
     assert rel(r1.disps, o.disps) < STATE_RTOL
 
 
+@pytest.mark.parametrize("name", ["A", "B", "mixed"])
+def test_interleaved_layout_matches_planar(name):
+    """targets / weights as [E,ht,wd,2] (what the update network emits) through
+    ba_interleaved against the planar [E,2,ht,wd] call: same per-pixel arithmetic --
+    on the tensor-core Gram path (out-degree <= 21), the CUDA-core fallback (hub) and an image whose
+    last 64-pixel slot is partial (30 x 40)."""
+    import droid_backends
+
+    g = _mixed_degree_graph(70, 30, 40, seed=5) if name == "mixed" else small_graphs()[name]
+    outs = []
+    for il in (False, True):
+        d = to_dev(g)
+        if il:
+            tg = d.targets.permute(0, 2, 3, 1).contiguous()
+            wg = d.weights.permute(0, 2, 3, 1).contiguous()
+            droid_backends.ba_interleaved(d.poses, d.disps, d.intr, d.sens, tg.unsqueeze(0), wg.unsqueeze(0), d.eta, d.ii,
+                                          d.jj, g.t0, g.t1, g.iters, g.lm, g.ep, False, False)
+        else:
+            droid_backends.ba(d.poses, d.disps, d.intr, d.sens, d.targets, d.weights, d.eta, d.ii, d.jj, g.t0, g.t1,
+                              g.iters, g.lm, g.ep, False, False)
+        torch.cuda.synchronize()
+        outs.append((d.poses.cpu().numpy(), d.disps.cpu().numpy()))
+    # per-pixel arithmetic is bit-identical; the sums are not bit-reproducible run to run (fp32 atomics
+    # merge the pixel splits of the Gram, fp64 atomics the closure tiles), hence a tolerance two orders
+    # below the parity bound instead of equality
+    assert rel(outs[1][0], outs[0][0]) < 1e-6 and rel(outs[1][1], outs[0][1]) < 1e-6
+    with pytest.raises(RuntimeError, match="ht,wd,2"):
+        d = to_dev(g)
+        droid_backends.ba_interleaved(d.poses, d.disps, d.intr, d.sens, d.targets, d.weights, d.eta, d.ii, d.jj, g.t0,
+                                      g.t1, 1, g.lm, g.ep, False, False)
+
+
 def test_argument_errors():
     import droid_backends
 
