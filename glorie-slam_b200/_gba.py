@@ -59,6 +59,10 @@ def lib():
         L.gba_depth_filter.restype = ci
         L.gba_align_scale_shift.argtypes = [vp] * 3 + [ci, ci, ci, vp, vp, vp, vp]
         L.gba_align_scale_shift.restype = ci
+        L.gba_iproj.argtypes = [vp] * 3 + [ci, ci, ci, vp, vp]
+        L.gba_iproj.restype = ci
+        L.gba_projmap.argtypes = [vp] * 5 + [ci, ci, ci, vp, vp, vp]
+        L.gba_projmap.restype = ci
         L.gba_set_timing.argtypes = [vp, ci]
         L.gba_get_timing.argtypes = [vp, ctypes.POINTER(cf), ctypes.POINTER(ci)]
         L.gba_set_timing.restype = ci

@@ -6,7 +6,9 @@
 //  rank 2: depth_filter, the multi-view consistency count behind the DSPO valid-depth mask
 //          (src/lib/droid_kernels.cu:661-775,1494-1518; caller src/depth_video.py:326-361), and
 //          align_scale_shift, the per-keyframe weighted scale/shift fit of the mono prior
-//          (src/utils/common.py:402-438; callers src/depth_video.py:233,308).
+//          (src/utils/common.py:402-438; callers src/depth_video.py:233,308);
+//  rank 4: iproj and projmap, the rest of the reference module's reprojection surface
+//          (src/lib/droid_kernels.cu:779-850,1520-1545 and :427-516,1466-1492; caller src/neural_point.py:156).
 #include <cuda_runtime.h>
 #include <stdio.h>
 
@@ -333,4 +335,109 @@ extern "C" int gba_align_scale_shift(const float *prediction, const float *targe
     return GBA_ECUDA;
   }
   return GBA_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// iproj / projmap
+// ---------------------------------------------------------------------------------------------
+#define PJ_NT 256
+
+// q * (x, y, 1) with the quaternion sandwich of the reference (actSO3, droid_kernels.cu:58-68)
+__device__ __forceinline__ void rot_xy1(const float *q, float x, float y, float &X, float &Y, float &Z) {
+  const float uvx = 2.f * (q[1] - q[2] * y), uvy = 2.f * (q[2] * x - q[0]), uvz = 2.f * (q[0] * y - q[1] * x);
+  X = x + q[3] * uvx + (q[1] * uvz - q[2] * uvy);
+  Y = y + q[3] * uvy + (q[2] * uvx - q[0] * uvz);
+  Z = 1.f + q[3] * uvz + (q[0] * uvy - q[1] * uvx);
+}
+
+// Thread per pixel, grid (pixel blocks, keyframes): points = (R (x, y, 1) + t d) / d.  The three
+// components of a pixel are stored by the thread that computed them (12 B stride; the reference does
+// the same, there is nothing to reuse).
+__global__ void __launch_bounds__(PJ_NT) k_iproj(const float *__restrict__ poses, const float *__restrict__ disps,
+                                                 const float *__restrict__ intr, int HW, int wd,
+                                                 float *__restrict__ points) {
+  const int b = blockIdx.y, k = blockIdx.x * PJ_NT + threadIdx.x;
+  if (k >= HW) return;
+  const float *P = poses + 7 * (size_t)b;
+  const float fx = intr[0], fy = intr[1], cx = intr[2], cy = intr[3];
+  const int i = k / wd, j = k - i * wd;
+  const float d = disps[(size_t)b * HW + k];
+  float X, Y, Z;
+  rot_xy1(P + 3, ((float)j - cx) / fx, ((float)i - cy) / fy, X, Y, Z);
+  float *o = points + ((size_t)b * HW + k) * 3;
+  o[0] = (X + d * P[0]) / d;
+  o[1] = (Y + d * P[1]) / d;
+  o[2] = (Z + d * P[2]) / d;
+}
+
+__global__ void __launch_bounds__(PJ_NT) k_projmap(const float *__restrict__ poses, const float *__restrict__ disps,
+                                                   const float *__restrict__ intr, const int64_t *__restrict__ ii,
+                                                   const int64_t *__restrict__ jj, int HW, int wd,
+                                                   float *__restrict__ coords, float *__restrict__ valid) {
+  __shared__ float s_rel[8];
+  const int n = blockIdx.y, ix = (int)ii[n], jx = (int)jj[n];
+  if (threadIdx.x == 0) {  // relSE3 (droid_kernels.cu:96-107)
+    const float *Pi = poses + 7 * (size_t)ix, *Pj = poses + 7 * (size_t)jx, *qi = Pi + 3, *qj = Pj + 3;
+    float qq[4];
+    qq[0] = -qj[3] * qi[0] + qj[0] * qi[3] - qj[1] * qi[2] + qj[2] * qi[1];
+    qq[1] = -qj[3] * qi[1] + qj[1] * qi[3] - qj[2] * qi[0] + qj[0] * qi[2];
+    qq[2] = -qj[3] * qi[2] + qj[2] * qi[3] - qj[0] * qi[1] + qj[1] * qi[0];
+    qq[3] = qj[3] * qi[3] + qj[0] * qi[0] + qj[1] * qi[1] + qj[2] * qi[2];
+    const float uv0 = 2.f * (qq[1] * Pi[2] - qq[2] * Pi[1]);
+    const float uv1 = 2.f * (qq[2] * Pi[0] - qq[0] * Pi[2]);
+    const float uv2 = 2.f * (qq[0] * Pi[1] - qq[1] * Pi[0]);
+    s_rel[0] = Pj[0] - (Pi[0] + qq[3] * uv0 + (qq[1] * uv2 - qq[2] * uv1));
+    s_rel[1] = Pj[1] - (Pi[1] + qq[3] * uv1 + (qq[2] * uv0 - qq[0] * uv2));
+    s_rel[2] = Pj[2] - (Pi[2] + qq[3] * uv2 + (qq[0] * uv1 - qq[1] * uv0));
+    s_rel[3] = qq[0]; s_rel[4] = qq[1]; s_rel[5] = qq[2]; s_rel[6] = qq[3];
+  }
+  __syncthreads();
+  const int k = blockIdx.x * PJ_NT + threadIdx.x;
+  if (k >= HW) return;
+  const float fx = intr[0], fy = intr[1], cx = intr[2], cy = intr[3];
+  const int i = k / wd, j = k - i * wd;
+  const float u = (float)j, v = (float)i, d = disps[(size_t)ix * HW + k];
+  float X, Y, Z;
+  rot_xy1(s_rel + 3, (u - cx) / fx, (v - cy) / fy, X, Y, Z);
+  X += d * s_rel[0]; Y += d * s_rel[1]; Z += d * s_rel[2];
+  float *c = coords + ((size_t)n * HW + k) * 3;
+  const bool front = Z > 0.01f;
+  c[0] = front ? fx * (X / Z) + cx : u;
+  c[1] = front ? fy * (Y / Z) + cy : v;
+  c[2] = 0.f;
+  valid[(size_t)n * HW + k] = (Z > 0.25f) ? 1.0f : 0.0f;
+}
+
+static int geom_launch_check(const char *what) {
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    snprintf(g_create_err, sizeof(g_create_err), "%s: %s", what, cudaGetErrorString(e));
+    return GBA_ECUDA;
+  }
+  return GBA_OK;
+}
+
+extern "C" int gba_iproj(const float *poses, const float *disps, const float *intrinsics, int n_frames, int ht, int wd,
+                         float *points, void *stream) {
+  if (n_frames == 0) return GBA_OK;
+  if (!poses || !disps || !intrinsics || !points || n_frames < 0 || n_frames > 65535 || ht < 1 || wd < 1) {
+    snprintf(g_create_err, sizeof(g_create_err), "gba_iproj: NULL array argument or bad sizes (n_frames <= 65535)");
+    return GBA_EINVAL;
+  }
+  k_iproj<<<dim3((ht * wd + PJ_NT - 1) / PJ_NT, n_frames), PJ_NT, 0, (cudaStream_t)stream>>>(poses, disps, intrinsics,
+                                                                                          ht * wd, wd, points);
+  return geom_launch_check("gba_iproj");
+}
+
+extern "C" int gba_projmap(const float *poses, const float *disps, const float *intrinsics, const int64_t *ii,
+                           const int64_t *jj, int n_pairs, int ht, int wd, float *coords, float *valid, void *stream) {
+  if (n_pairs == 0) return GBA_OK;
+  if (!poses || !disps || !intrinsics || !ii || !jj || !coords || !valid || n_pairs < 0 || n_pairs > 65535 || ht < 1 ||
+      wd < 1) {
+    snprintf(g_create_err, sizeof(g_create_err), "gba_projmap: NULL array argument or bad sizes (n_pairs <= 65535)");
+    return GBA_EINVAL;
+  }
+  k_projmap<<<dim3((ht * wd + PJ_NT - 1) / PJ_NT, n_pairs), PJ_NT, 0, (cudaStream_t)stream>>>(
+      poses, disps, intrinsics, ii, jj, ht * wd, wd, coords, valid);
+  return geom_launch_check("gba_projmap");
 }

@@ -8,8 +8,9 @@ sys.path and `import droid_backends` resolves here; depth_video.py stays unchang
 
 The work is done by libgba.so (hand-written sm_100a CUDA behind the C ABI in include/gba.h);
 torch only supplies device memory and the current stream.  Also provided: `frame_distance`,
-`depth_filter` and `ba_interleaved` (rank 3).  The remaining
-functions of the reference module (projmap, iproj, corr kernels) are outside this repository's scope; set GBA_REFERENCE_BACKENDS to a module name to forward them.
+`depth_filter`, `ba_interleaved` (rank 3), `iproj` and `projmap`
+(rank 4).  The remaining functions of the reference module (corr_index_*, altcorr_*) are outside this
+repository's scope; set GBA_REFERENCE_BACKENDS to a module name to forward them.
 """
 from __future__ import annotations
 
@@ -136,10 +137,49 @@ def depth_filter(poses, disps, intrinsics, ix, thresh):
     return counter
 
 
+def iproj(poses, disps, intrinsics):
+    """Drop-in for the reference's droid_backends.iproj (src/lib/droid.cpp:159-168,
+    src/lib/droid_kernels.cu:779-850,1520-1545; caller src/neural_point.py:156): every pixel of every
+    keyframe back-projected and transformed by its pose.  Returns points [N,ht,wd,3] f32."""
+    for t, n in ((poses, "poses"), (disps, "disps"), (intrinsics, "intrinsics")):
+        _chk(t, n, torch.float32)
+    N, ht, wd = disps.shape
+    if poses.shape[0] < N:
+        raise ValueError("poses must hold one row per disparity map")
+    dev = disps.device
+    points = torch.empty((N, ht, wd, 3), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        rc = _gba.lib().gba_iproj(poses.data_ptr(), disps.data_ptr(), intrinsics.data_ptr(), N, ht, wd, points.data_ptr(),
+                                  torch.cuda.current_stream(dev).cuda_stream)
+        _gba.check(None, rc)
+    return points
+
+
+def projmap(poses, disps, intrinsics, ii, jj):
+    """Drop-in for the reference's droid_backends.projmap (src/lib/droid.cpp:141-156,
+    src/lib/droid_kernels.cu:427-516,1466-1492): where the pixels of keyframe ii[n] land in keyframe
+    jj[n].  Returns [coords [num,ht,wd,3], valid [num,ht,wd,1]] like the reference."""
+    for t, n in ((poses, "poses"), (disps, "disps"), (intrinsics, "intrinsics")):
+        _chk(t, n, torch.float32)
+    _chk(ii, "ii", torch.int64)
+    _chk(jj, "jj", torch.int64)
+    _, ht, wd = disps.shape
+    num = int(ii.shape[0])
+    dev = poses.device
+    coords = torch.empty((num, ht, wd, 3), dtype=torch.float32, device=dev)
+    valid = torch.empty((num, ht, wd, 1), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        rc = _gba.lib().gba_projmap(poses.data_ptr(), disps.data_ptr(), intrinsics.data_ptr(), ii.data_ptr(), jj.data_ptr(),
+                                    num, ht, wd, coords.data_ptr(), valid.data_ptr(),
+                                    torch.cuda.current_stream(dev).cuda_stream)
+        _gba.check(None, rc)
+    return [coords, valid]
+
+
 def __getattr__(name):
     fwd = os.environ.get("GBA_REFERENCE_BACKENDS")
     if fwd:
         return getattr(importlib.import_module(fwd), name)
     raise AttributeError(
-        "droid_backends.%s is outside the B200 hot path (only `ba`, `frame_distance` and `depth_filter` are provided); set GBA_REFERENCE_BACKENDS "
+        "droid_backends.%s is outside the B200 hot path (provided: ba, ba_interleaved, frame_distance, depth_filter, iproj, projmap); set GBA_REFERENCE_BACKENDS "
         "to the reference extension's module name to forward it" % name)

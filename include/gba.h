@@ -196,6 +196,22 @@ int gba_depth_filter(const float *poses, const float *disps, const float *intrin
 int gba_align_scale_shift(const float *prediction, const float *target, const float *weights, int n, int ht, int wd,
                           float *scale, float *shift, float *avg_error, void *stream);
 
+/* ---- iproj / projmap ------------------------------------------------
+ * Replace droid_backends.iproj (src/lib/droid.cpp:159-168 -> src/lib/droid_kernels.cu:779-850,
+ * 1520-1545; caller src/neural_point.py:156) and droid_backends.projmap (src/lib/droid.cpp:
+ * 141-156 -> src/lib/droid_kernels.cu:427-516,1466-1492).
+ * gba_iproj: points [n_frames,ht,wd,3] = (R_b (x, y, 1) + t_b d) / d for every pixel of every
+ * keyframe b, pose b as given (the caller passes inverse poses to get world points); d = 0 gives
+ * inf / nan like the reference.
+ * gba_projmap: for pair n the pixels of keyframe ii[n] reprojected into keyframe jj[n]:
+ * coords [n_pairs,ht,wd,3] = (u', v', 0), the pixel's own (u, v) where Z <= 0.01;
+ * valid [n_pairs,ht,wd,1] = 1 where Z > 0.25, else 0.  Both outputs are fully written.
+ * Device pointers, asynchronous on `stream`, no gba_ctx; n_frames, n_pairs <= 65535. */
+int gba_iproj(const float *poses, const float *disps, const float *intrinsics, int n_frames, int ht, int wd,
+              float *points, void *stream);
+int gba_projmap(const float *poses, const float *disps, const float *intrinsics, const int64_t *ii, const int64_t *jj,
+                int n_pairs, int ht, int wd, float *coords, float *valid, void *stream);
+
 /* ---- per-edge pose blocks for callers that cannot allocate --------------------------------
  * No counterpart in the reference: there, these numbers only exist inside ba_cuda.
  *

@@ -830,6 +830,64 @@ int FN(oracle_align_scale_shift)(const REAL *pred, const REAL *target, const REA
   return 0;
 }
 
+/*
+ * iproj: back-projection of every pixel of every keyframe, transformed by the given pose:
+ * points = (R (x, y, 1) + t d) / d.  src/lib/droid_kernels.cu:779-850,1520-1545; caller
+ * src/neural_point.py:156 (passes the INVERSE poses to get world points).
+ */
+int FN(oracle_iproj)(const REAL *poses, const REAL *disps, const float *intr_f, int n_frames, int ht, int wd, REAL *points) {
+  const int HW = ht * wd;
+  const REAL fx = (REAL)intr_f[0], fy = (REAL)intr_f[1], cx = (REAL)intr_f[2], cy = (REAL)intr_f[3];
+  int b;
+#pragma omp parallel for schedule(static)
+  for (b = 0; b < n_frames; b++) {
+    int k;
+    for (k = 0; k < HW; k++) {
+      REAL Xi[4], Xj[3];
+      Xi[0] = ((REAL)(k % wd) - cx) / fx; Xi[1] = ((REAL)(k / wd) - cy) / fy; Xi[2] = 1; Xi[3] = disps[(size_t)b * HW + k];
+      FN(act_so3)(poses + 7 * b + 3, Xi, Xj);
+      points[((size_t)b * HW + k) * 3 + 0] = (Xj[0] + Xi[3] * poses[7 * b + 0]) / Xi[3];
+      points[((size_t)b * HW + k) * 3 + 1] = (Xj[1] + Xi[3] * poses[7 * b + 1]) / Xi[3];
+      points[((size_t)b * HW + k) * 3 + 2] = (Xj[2] + Xi[3] * poses[7 * b + 2]) / Xi[3];
+    }
+  }
+  return 0;
+}
+
+/*
+ * projmap: where the pixels of keyframe ii[n] land in keyframe jj[n].  coords [n,ht,wd,3]: (u', v', 0),
+ * the pixel's own (u, v) when Z <= 0.01; valid [n,ht,wd,1] = Z > 0.25.
+ * src/lib/droid_kernels.cu:427-516,1466-1492.
+ */
+int FN(oracle_projmap)(const REAL *poses, const REAL *disps, const float *intr_f, const int64_t *ii, const int64_t *jj,
+                       int n_pairs, int ht, int wd, REAL *coords, REAL *valid) {
+  const int HW = ht * wd;
+  const REAL fx = (REAL)intr_f[0], fy = (REAL)intr_f[1], cx = (REAL)intr_f[2], cy = (REAL)intr_f[3];
+  int n;
+#pragma omp parallel for schedule(static)
+  for (n = 0; n < n_pairs; n++) {
+    const int ix = (int)ii[n], jx = (int)jj[n];
+    REAL tij[3], qij[4];
+    int k;
+    FN(rel_se3)(poses + 7 * ix, poses + 7 * ix + 3, poses + 7 * jx, poses + 7 * jx + 3, tij, qij);
+    for (k = 0; k < HW; k++) {
+      REAL Xi[4], Xj[3], u = (REAL)(k % wd), v = (REAL)(k / wd), Z;
+      REAL *c = coords + ((size_t)n * HW + k) * 3;
+      Xi[0] = (u - cx) / fx; Xi[1] = (v - cy) / fy; Xi[2] = 1; Xi[3] = disps[(size_t)ix * HW + k];
+      FN(act_so3)(qij, Xi, Xj);
+      Xj[0] += Xi[3] * tij[0]; Xj[1] += Xi[3] * tij[1]; Xj[2] += Xi[3] * tij[2];
+      Z = Xj[2];
+      c[0] = u; c[1] = v; c[2] = 0;
+      if (Z > (REAL)0.01) {
+        c[0] = fx * (Xj[0] / Z) + cx;
+        c[1] = fy * (Xj[1] / Z) + cy;
+      }
+      valid[(size_t)n * HW + k] = (Z > (REAL)0.25) ? 1 : 0;
+    }
+  }
+  return 0;
+}
+
 #undef FN
 #undef FN1
 #undef FN2

@@ -172,3 +172,31 @@ def align_scale_and_shift(prediction, target, weights, precision="f32"):
     s, q, e = (np.zeros((n,), dtype=real) for _ in range(3))
     fn(_p(p_), _p(t_), _p(w_), ctypes.c_int(n), ctypes.c_int(ht * wd), _p(s), _p(q), _p(e))
     return s, q, e
+
+
+def iproj(poses, disps, intrinsics, precision="f32"):
+    """reference droid_backends.iproj (src/lib/droid_kernels.cu:779-850,1520-1545) -> points [N,ht,wd,3]"""
+    real = np.float32 if precision == "f32" else np.float64
+    fn = getattr(lib(), "oracle_iproj_" + precision)
+    fn.restype = ctypes.c_int
+    N, ht, wd = disps.shape
+    po, di = np.ascontiguousarray(poses, dtype=real), np.ascontiguousarray(disps, dtype=real)
+    intr = np.ascontiguousarray(intrinsics, dtype=np.float32)
+    out = np.zeros((N, ht, wd, 3), dtype=real)
+    fn(_p(po), _p(di), _p(intr), ctypes.c_int(N), ctypes.c_int(ht), ctypes.c_int(wd), _p(out))
+    return out
+
+
+def projmap(poses, disps, intrinsics, ii, jj, precision="f32"):
+    """reference droid_backends.projmap (src/lib/droid_kernels.cu:427-516,1466-1492) -> coords [n,ht,wd,3], valid [n,ht,wd,1]"""
+    real = np.float32 if precision == "f32" else np.float64
+    fn = getattr(lib(), "oracle_projmap_" + precision)
+    fn.restype = ctypes.c_int
+    N, ht, wd = disps.shape
+    po, di = np.ascontiguousarray(poses, dtype=real), np.ascontiguousarray(disps, dtype=real)
+    intr = np.ascontiguousarray(intrinsics, dtype=np.float32)
+    ii64, jj64 = np.ascontiguousarray(ii, dtype=np.int64), np.ascontiguousarray(jj, dtype=np.int64)
+    n = ii64.shape[0]
+    coords, valid = np.zeros((n, ht, wd, 3), dtype=real), np.zeros((n, ht, wd, 1), dtype=real)
+    fn(_p(po), _p(di), _p(intr), _p(ii64), _p(jj64), ctypes.c_int(n), ctypes.c_int(ht), ctypes.c_int(wd), _p(coords), _p(valid))
+    return coords, valid

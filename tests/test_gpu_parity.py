@@ -568,6 +568,44 @@ def test_depth_filter_empty_and_errors():
         droid_backends.depth_filter(tp.cpu(), td, ti, torch.zeros(1, dtype=torch.int64).cuda(), torch.zeros(1).cuda())
 
 
+# ------------------------------------------------------------------------------------------
+# iproj + projmap
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["A", "C"])
+def test_iproj_and_projmap_match_oracle_and_reference(name):
+    import droid_backends
+
+    g = small_graphs()["A"] if name == "A" else synth.make_config("C")
+    poses = g.poses.copy()
+    poses[1, 3:] = [0.0, 1.0, 0.0, 0.0]  # keyframe 1 looks the other way: its pairs land behind the camera
+    tp, td, ti = (torch.from_numpy(np.ascontiguousarray(a)).cuda() for a in (poses, g.disps, g.intrinsics))
+    tii, tjj = torch.from_numpy(g.ii).cuda(), torch.from_numpy(g.jj).cuda()
+    want = oracle.iproj(poses, g.disps, g.intrinsics, precision="f64")
+    got = droid_backends.iproj(tp, td, ti).cpu().numpy()
+    assert got.shape == want.shape and got.dtype == np.float32
+    np.testing.assert_allclose(got, want, rtol=2e-5, atol=2e-5)
+    wc, wv = oracle.projmap(poses, g.disps, g.intrinsics, g.ii, g.jj, precision="f64")
+    gc, gv = droid_backends.projmap(tp, td, ti, tii, tjj)
+    gc, gv = gc.cpu().numpy(), gv.cpu().numpy()
+    assert gc.shape == wc.shape and gv.shape == wv.shape
+    assert 0 < (wv == 0).sum() < wv.size  # both branches of the validity test are exercised
+    same = gv == wv
+    assert same.mean() > 0.9999  # a pixel exactly on Z = 0.25 may round either way
+    ok = np.broadcast_to(same & (np.abs(wc[..., :1]) < 1e4), wc.shape)
+    np.testing.assert_allclose(gc[ok], wc[ok], rtol=1e-4, atol=2e-3)
+    np.testing.assert_array_equal(gc[..., 2], 0.0)
+    ref = _load_reference_so()
+    if ref is not None:
+        np.testing.assert_allclose(got, ref.iproj(tp, td, ti).cpu().numpy(), rtol=2e-5, atol=2e-5)
+        rc, rv = ref.projmap(tp, td, ti, tii, tjj)
+        rc, rv = rc.cpu().numpy(), rv.cpu().numpy()
+        same = gv == rv
+        assert same.mean() > 0.9999
+        ok = np.broadcast_to(same & (np.abs(rc[..., :1]) < 1e4), rc.shape)
+        np.testing.assert_allclose(gc[ok], rc[ok], rtol=1e-4, atol=2e-3)
+    assert droid_backends.projmap(tp, td, ti, tii[:0], tjj[:0])[0].shape == (0,) + g.disps.shape[1:] + (3,)
+
+
 def _torch_align(prediction, target, weights):
     """float64 torch restatement of src/utils/common.py:402-438"""
     p, t, w = prediction.double(), target.double(), weights.double()

@@ -157,3 +157,24 @@ def test_align_scale_shift_oracle_recovers_affine():
     t2 = t + (rng.normal(0, 0.05, p.shape) * w).astype(np.float32)
     s2, q2, e2 = oracle.align_scale_and_shift(p, t2, w, precision="f64")
     assert 0.02 < e2.mean() < 0.06 and abs(s2 - 1.7).max() < 0.05
+
+
+def test_iproj_projmap_oracle_basics():
+    """droid_kernels.cu:779-850 and :427-516: the identity pose gives (x, y, 1) / d; a keyframe maps onto
+    itself; projmap agrees with the reprojection that generated the synthetic targets"""
+    import synth
+
+    g = synth.make_config("A")
+    pts = oracle.iproj(g.poses, g.disps, g.intrinsics, precision="f64")
+    fx, fy, cx, cy = g.intrinsics
+    v, u = np.meshgrid(np.arange(g.disps.shape[1]), np.arange(g.disps.shape[2]), indexing="ij")
+    np.testing.assert_allclose(pts[0, ..., 0], (u - cx) / fx / g.disps[0], rtol=1e-6)  # pose 0 is the identity
+    np.testing.assert_allclose(pts[0, ..., 2], 1.0 / g.disps[0], rtol=1e-6)
+    c, val = oracle.projmap(g.poses, g.disps, g.intrinsics, np.array([3]), np.array([3]), precision="f64")
+    np.testing.assert_allclose(c[0, ..., 0], u, atol=1e-9)
+    np.testing.assert_allclose(c[0, ..., 1], v, atol=1e-9)
+    assert (val == 1).all() and (c[..., 2] == 0).all()
+    c2, _ = oracle.projmap(g.poses_gt, g.disps_gt, g.intrinsics, g.ii, g.jj, precision="f64")
+    tg = synth.project(g.poses_gt, g.disps_gt, g.intrinsics, g.ii, g.jj)  # [E,2,ht,wd]
+    np.testing.assert_allclose(c2[..., 0], tg[:, 0], rtol=1e-4, atol=1e-3)
+    np.testing.assert_allclose(c2[..., 1], tg[:, 1], rtol=1e-4, atol=1e-3)
