@@ -96,7 +96,7 @@ def ba_interleaved(poses, disps, intrinsics, disps_sens, targets, weights, eta, 
 
 
 def frame_distance(poses, disps, intrinsics, ii, jj, beta):
-    """Drop-in for the reference's droid_backends.frame_distance (src/lib/droid.cpp:122-135,
+    """Drop-in for the reference's droid_backends.frame_distance (src/lib/droid.cpp:122-138,
     src/lib/droid_kernels.cu:518-657): mean induced flow of every keyframe pair (ii[n] -> jj[n]),
     1000 where fewer than 75 % of the pixels stay in front of the target camera.  Returns [num] f32."""
     for t, n in ((poses, "poses"), (disps, "disps"), (intrinsics, "intrinsics")):
@@ -116,7 +116,7 @@ def frame_distance(poses, disps, intrinsics, ii, jj, beta):
 
 
 def depth_filter(poses, disps, intrinsics, ix, thresh):
-    """Drop-in for the reference's droid_backends.depth_filter (src/lib/droid.cpp:138-146,
+    """Drop-in for the reference's droid_backends.depth_filter (src/lib/droid.cpp:222-236,
     src/lib/droid_kernels.cu:661-775,1494-1518; caller src/depth_video.py:349): per listed keyframe and
     pixel, the number of neighbouring keyframes (ix-1,-2,-3,+3,+4,+5) whose depth agrees with the
     reprojection within thresh.  Returns counter [len(ix), ht, wd] f32."""

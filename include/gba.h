@@ -165,7 +165,7 @@ int gba_set_timing(gba_ctx *ctx, int enable);
 int gba_get_timing(gba_ctx *ctx, float *ms /* [GBA_N_STAGES] */, int *launches /* [GBA_N_STAGES] */);
 
 /* ---- frame_distance -------------------------------------------------
- * Replaces droid_backends.frame_distance (src/lib/droid.cpp:122-135 ->
+ * Replaces droid_backends.frame_distance (src/lib/droid.cpp:122-138 ->
  * src/lib/droid_kernels.cu:518-657,1441-1463): for every pair (ii[n] -> jj[n]) the mean
  * induced-flow magnitude, beta * full relative motion + (1 - beta) * translation only, over
  * the pixels that land in front of the target camera; 1000 when fewer than 75 % do.
@@ -175,7 +175,7 @@ int gba_frame_distance(const float *poses, const float *disps, const float *intr
                        const int64_t *jj, int n_pairs, int ht, int wd, float beta, float *dist, void *stream);
 
 /* ---- depth_filter ---------------------------------------------------
- * Replaces droid_backends.depth_filter (src/lib/droid.cpp:138-146 ->
+ * Replaces droid_backends.depth_filter (src/lib/droid.cpp:222-236 ->
  * src/lib/droid_kernels.cu:661-775,1494-1518; caller src/depth_video.py:326-361): for every
  * listed keyframe inds[b] and pixel, how many of the 6 neighbouring keyframes (inds[b]-1,-2,-3,
  * +3,+4,+5, those inside [0, n_frames)) hold, at one of the 4 pixels around the reprojection,
