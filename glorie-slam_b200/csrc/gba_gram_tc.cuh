@@ -542,22 +542,20 @@ __global__ void __launch_bounds__(GT_NT, 1) k_gram_tc(BaParams p) {
       const int start = (tile0 + j * GT_TPI) * GT_K;
       const int npx = min(min(GT_IPX, HW - start), (nloc - j * GT_TPI) * GT_K);  // HW % 4 == 0: whole 16 B pieces
       const uint32_t dst0 = tc::smem_u32(s_in) + (uint32_t)is * GT_IN_BYTES + (uint32_t)c4 * 4u;
-      if (!IL) {
-        if (c4 < npx) {
-#pragma unroll 4
-          for (int c = sub; c < nrow; c += 2) tc::cp_async16(dst0 + (uint32_t)c * (GT_IPX * 4), s_row[c] + start + c4);
-        }
-      } else {
-        const int nedge = 4 * deg;  // edge rows advance 2 floats per pixel, keyframe rows 1
-#pragma unroll 4
-        for (int c = sub; c < nrow; c += 2) {
-          if (c < nedge) {
-            if ((c & 1) * GT_IPX + c4 < 2 * npx) tc::cp_async16(dst0 + (uint32_t)c * (GT_IPX * 4), s_row[c] + 2 * start + c4);
-          } else if (c4 < npx) {
-            tc::cp_async16(dst0 + (uint32_t)c * (GT_IPX * 4), s_row[c] + start + c4);
-          }
-        }
+      // edge rows (targets / weights), then the three keyframe rows.  Both loops are straight-line
+      // (no test inside) so that the row-pointer loads of the unrolled iterations overlap: this warp is
+      // a latency chain, a branch or a predicate in the body costs the whole kernel 15-60 %.
+      const int nedge = 4 * deg;
+      const int estart = IL ? 2 * start : start;  // interleaved: an edge row advances 2 floats per pixel
+      const int elim = IL ? 2 * npx : npx;
+      // c = sub, sub + 2, ...: the parity of c is this lane's `sub`, so the bound test leaves the loop
+      const int eoff = IL ? sub * GT_IPX + c4 : c4;  // interleaved: rows 4q, 4q+1 are halves of one run
+      if (eoff < elim) {
+#pragma unroll 8
+        for (int c = sub; c < nedge; c += 2) tc::cp_async16(dst0 + (uint32_t)c * (GT_IPX * 4), s_row[c] + estart + c4);
       }
+      if (c4 < npx)
+        for (int c = nedge + sub; c < nrow; c += 2) tc::cp_async16(dst0 + (uint32_t)c * (GT_IPX * 4), s_row[c] + start + c4);
       tc::cp_async_arrive(infull_bar(is));  // fires when this lane's copies above have landed
     }
   } else {
