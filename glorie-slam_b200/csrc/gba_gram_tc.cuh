@@ -49,10 +49,13 @@
 #include "gba_common.cuh"
 
 #define GT_MAXDEG 21                // 6 * 21 + 1 = 127 rows <= 128
-#define GT_NPW 14                   // producer warps 0-13
-#define GT_LOADW 14                 // loader warp
-#define GT_MMAW 15                  // MMA-issue warp
-#define GT_NT 512
+#ifndef GT_NPW
+#define GT_NPW 14                   // producer warps 0 .. GT_NPW-1 (>= 13: the drain chunks sit on warps 0-12); 18 warps at
+#endif                              // 96 registers measured 4 % slower, 20 spill
+#define GT_ROT (GT_NPW == 14 ? 5 : 7) // slot-to-slot rotation of the edge assignment, coprime with GT_NPW
+#define GT_LOADW GT_NPW             // loader warp
+#define GT_MMAW (GT_NPW + 1)        // MMA-issue warp
+#define GT_NT (32 * (GT_NPW + 2))
 #define GT_K 32                     // pixels per operand stage (= producer lanes)
 #define GT_STAGES 4                 // operand ring
 #define GT_TPI 2                    // tiles per input stage
@@ -387,7 +390,7 @@ __global__ void __launch_bounds__(GT_NT, 1) k_gram_tc(BaParams p) {
     };
     const int nslot = (nloc + GT_TPI - 1) / GT_TPI;
     for (int j = 0; j < nslot; j++) {
-      const int b0 = (warp + 5 * j) % GT_NPW;  // 5 and 14 are coprime: the heavy slots of a warp are spread out
+      const int b0 = (warp + GT_ROT * j) % GT_NPW;  // coprime rotation: the heavy slots of a warp are spread out
       const int is = j % GT_IS;
       const int it0 = j * GT_TPI, nt = min(GT_TPI, nloc - it0);
       // Every warp takes part in the input ring of every slot, also when it has no edge in it
