@@ -267,7 +267,8 @@ def test_tensor_core_gram_matches_cuda_core_gram(n, ht, wd, monkeypatch):
     assert deg0.max() > 21 and (deg0 <= 6).any() and ((deg0 > 14) & (deg0 <= 21)).any()
     for k in range(len(G0)):
         scale = np.abs(G0[k]).max() + 1e-30
-        assert np.abs(G1[k] - G0[k]).max() / scale < 5e-6, (k, deg0[k])
+        # 870 random graphs: worst 4.8e-6 (both sides carry fp32 rounding of ~3000-term sums)
+        assert np.abs(G1[k] - G0[k]).max() / scale < 1e-5, (k, deg0[k])
     o = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj, g.t0, g.t1,
                   g.iters, g.lm, g.ep, precision="f64")
     r = run_ba(g)
