@@ -51,3 +51,20 @@ def test_product_path_does_not_import_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 txt = open(os.path.join(dp, f)).read()
                 assert "import oracle" not in txt and "from oracle" not in txt and "liboracle" not in txt, f
+
+
+def test_python_mirror_has_the_reference_call_surface():
+    """droid_backends.py mirrors the reference extension's exports on the path (src/lib/droid.cpp:241-245):
+    same names, same positional argument counts."""
+    import inspect
+
+    import common
+    import droid_backends
+
+    want = {"ba": 16, "frame_distance": 6, "projmap": 5, "depth_filter": 5, "iproj": 3}
+    for name, n in want.items():
+        fn = getattr(droid_backends, name)
+        pos = [p for p in inspect.signature(fn).parameters.values() if not p.name.startswith("_")]
+        assert len(pos) == n, (name, len(pos))
+    assert len(inspect.signature(droid_backends.ba_interleaved).parameters) == 16
+    assert list(inspect.signature(common.align_scale_and_shift).parameters) == ["prediction", "target", "weights"]
