@@ -25,7 +25,7 @@ _ctx = {}
 class Info(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int) for n in (
         "n_depth_frames", "n_poses", "max_out_degree", "chol_failures", "n_tiles", "n_active_tiles",
-        "kernel_launches", "chain_columns")]
+        "kernel_launches", "chain_columns", "last_fail_code", "watchdog_trips")]
 
 
 def lib():
@@ -51,6 +51,8 @@ def lib():
         L.gba_ba_end.argtypes = [vp, vp, vp]
         L.gba_query.argtypes = [vp, ctypes.POINTER(Info)]
         L.gba_get.argtypes = [vp, ci, vp, ctypes.c_size_t]
+        L.gba_last_depth_frames.argtypes = [vp]
+        L.gba_last_depth_frames.restype = ci
         L.gba_edge_blocks_static.argtypes = [vp] * 7 + [ci] * 5 + [vp, vp]
         L.gba_edge_blocks_static.restype = ci
         L.gba_frame_distance.argtypes = [vp] * 5 + [ci, ci, ci, cf, vp, vp]

@@ -239,10 +239,10 @@ extern "C" int gba_create(gba_ctx **out, int device, int max_frames, int max_edg
 
 // ---- index build shared by BA and DSPO ---------------------------------------------------------
 // CSR of the edges in p.ii / p.jj by source keyframe
-static int build_csr(gba_ctx *c, const int64_t *kx_global, int n_kx) {
+static int build_csr(gba_ctx *c, const int64_t *kx_global, int n_kx, bool first_pass = true) {
   BaParams &p = c->p;
   cudaStream_t s = c->stream;
-  k_prep_frames<<<1, 1024, 0, s>>>(p, kx_global, n_kx);
+  k_prep_frames<<<1, 1024, 0, s>>>(p, kx_global, n_kx, first_pass ? 1 : 0);
   LAUNCH_CHECK("k_prep_frames");
   if (p.E > 0) {
     k_prep_edges<<<(p.E + 255) / 256, 256, 0, s>>>(p);
@@ -278,7 +278,7 @@ static int build_index(gba_ctx *c, const int64_t *kx_global, int n_kx, bool want
     k_order<<<1, 1024, (size_t)((p.P + 3) / 4) * 4, s>>>(p, c->pos_cap);
     LAUNCH_CHECK("k_order");
     CK(cudaMemsetAsync(c->sb.tbits, 0, (size_t)p.nT * TS_WORDS * sizeof(unsigned int), s));
-    k_tile_mark<<<p.N, 128, 0, s>>>(p, c->sb.tbits);
+    k_tile_mark<false><<<p.N, 128, 0, s>>>(p, c->sb.tbits);
     LAUNCH_CHECK("k_tile_mark");
     k_tile_fill<<<1, 512, 0, s>>>(p, c->sb);
     LAUNCH_CHECK("k_tile_fill");
@@ -287,8 +287,11 @@ static int build_index(gba_ctx *c, const int64_t *kx_global, int n_kx, bool want
     p.ii = ii_loc;
     p.jj = jj_loc;
     p.E = E_loc;
-    rc = build_csr(c, kx_global, n_kx);
+    rc = build_csr(c, kx_global, n_kx, false);
     if (rc) return rc;
+    // every tile a local edge will add to must exist in the structure derived from the whole graph
+    k_tile_mark<true><<<p.N, 128, 0, s>>>(p, c->sb.tbits);
+    LAUNCH_CHECK("k_tile_mark<check>");
   }
   stage_end(c);
   CK(cudaMemcpyAsync(c->st_h, c->st_d, sizeof(Status), cudaMemcpyDeviceToHost, s));
@@ -300,6 +303,7 @@ static int build_index(gba_ctx *c, const int64_t *kx_global, int n_kx, bool want
   const Status &st = *c->st_h;
   if (st.err & 1) return fail_msg(c, GBA_EINVAL, "ii/jj (or kx) contain keyframe indices outside [0,%d)", p.N);
   if (st.err & 4) return fail_msg(c, GBA_EINVAL, "an edge's source keyframe is missing from kx_global");
+  if (st.err & 8) return fail_msg(c, GBA_EINVAL, "a local edge is missing from ii_all / jj_all (the whole-graph edge list)");
   return GBA_OK;
 }
 
@@ -322,6 +326,11 @@ extern "C" int gba_ba_begin(gba_ctx *c, float *poses, float *disps, const float 
     return fail_msg(c, GBA_EINVAL, "optimised window [%d,%d) not inside [0,%d)", t0, t1, n_frames);
   if ((mode & ~GBA_LAYOUT_INTERLEAVED) != GBA_MODE_DROID_CUDA && (mode & ~GBA_LAYOUT_INTERLEAVED) != GBA_MODE_GEOM_PY)
     return fail_msg(c, GBA_EINVAL, "unknown mode %d", mode);
+  // every per-pixel array is read with 16-byte vector loads (and 16-byte bulk copies in k_gram_tc)
+  if ((((uintptr_t)disps | (uintptr_t)disps_sens | (uintptr_t)targets | (uintptr_t)weights | (uintptr_t)eta) & 15) != 0)
+    return fail_msg(c, GBA_EINVAL, "disps, disps_sens, targets, weights and eta must be 16-byte aligned");
+  if ((((uintptr_t)poses | (uintptr_t)intrinsics) & 3) != 0 || (((uintptr_t)ii | (uintptr_t)jj) & 7) != 0)
+    return fail_msg(c, GBA_EINVAL, "misaligned poses / intrinsics / ii / jj pointer");
   CK(cudaSetDevice(c->device));
   c->stream = (cudaStream_t)stream;
   c->launches = 0;
@@ -344,8 +353,6 @@ extern "C" int gba_ba_begin(gba_ctx *c, float *poses, float *disps, const float 
     p.tc_maxdeg = (e && e[0] == '0') ? 0 : GT_MAXDEG;
     p.wdog = c->wdog;
     p.fail = c->sb.fail;
-    // the bulk copies of k_gram_tc need 16-byte aligned rows (HW % 4 == 0 is already required)
-    if ((((uintptr_t)p.targets | (uintptr_t)p.weights | (uintptr_t)p.disps) & 15) != 0) p.tc_maxdeg = 0;
   }
   p.ld = 0;
   c->last_P = p.P;
@@ -591,6 +598,10 @@ extern "C" int gba_ba_solve(gba_ctx *c) {
     else GBA_LAUNCH_K_BACKSUB(1, true);
 #undef GBA_LAUNCH_K_BACKSUB
     LAUNCH_CHECK("k_backsub");
+    if (p.mode == GBA_MODE_GEOM_PY && st.K < p.N) {  // ba.py:119 clamps every row, k_backsub the rows in kx
+      k_clamp_rest<<<dim3((c->HW / 4 + 127) / 128, p.N), 128, 0, s>>>(p.disps, c->fmap, c->HW);
+      LAUNCH_CHECK("k_clamp_rest");
+    }
     stage_end(c);
   }
   if (p.motion_only || !p.depth_only) {
@@ -641,6 +652,9 @@ extern "C" int gba_dspo(gba_ctx *c, const float *poses, float *disps, const floa
   if (n_frames < 1 || n_frames > c->N_max)
     return fail_msg(c, GBA_ECAPACITY, "n_frames %d outside [1,%d]", n_frames, c->N_max);
   if (n_edges < 1 || n_edges > c->E_max) return fail_msg(c, GBA_ECAPACITY, "n_edges %d outside [1,%d]", n_edges, c->E_max);
+  if ((((uintptr_t)disps | (uintptr_t)targets | (uintptr_t)weights | (uintptr_t)eta | (uintptr_t)mono_disps) & 15) != 0 ||
+      ((uintptr_t)valid_mask & 3) != 0)
+    return fail_msg(c, GBA_EINVAL, "disps, targets, weights, eta and mono_disps must be 16-byte aligned, valid_mask 4-byte aligned");
   CK(cudaSetDevice(c->device));
   c->stream = (cudaStream_t)stream;
   c->launches = 0;
@@ -678,6 +692,10 @@ extern "C" int gba_dspo(gba_ctx *c, const float *poses, float *disps, const floa
   LAUNCH_CHECK("k_dspo_solve");
   k_dspo_update<128><<<grid, 128, 0, s>>>(d);
   LAUNCH_CHECK("k_dspo_update");
+  if (st.K < n_frames) {
+    k_clamp_rest<<<dim3((c->HW / 4 + 127) / 128, n_frames), 128, 0, s>>>(disps, c->fmap, c->HW);
+    LAUNCH_CHECK("k_clamp_rest");
+  }
   stage_end(c);
   return GBA_OK;
 }
@@ -713,6 +731,8 @@ extern "C" int gba_get_timing(gba_ctx *c, float *ms, int *launches) {
 }
 
 // ---- introspection ------------------------------------------------------------------------------
+extern "C" int gba_last_depth_frames(const gba_ctx *c) { return (c && c->st_h) ? c->st_h->K : GBA_EINVAL; }
+
 extern "C" int gba_query(gba_ctx *c, gba_info *info) {
   if (!c || !info) return GBA_EINVAL;
   CK(cudaSetDevice(c->device));
@@ -728,6 +748,10 @@ extern "C" int gba_query(gba_ctx *c, gba_info *info) {
   info->kernel_launches = c->launches;
   // sequential tile columns of the factorisation: one band segment's worth plus the closure block
   info->chain_columns = (st.n_seg > 1 ? st.seg_tiles : 0) + (st.n_tiles - (st.n_seg > 1 ? st.n_seg * st.seg_tiles : 0));
+  info->last_fail_code = st.last_fail;
+  int wd0 = 0;
+  CK(cudaMemcpy(&wd0, c->wdog, sizeof(int), cudaMemcpyDeviceToHost));
+  info->watchdog_trips = wd0;
   return GBA_OK;
 }
 

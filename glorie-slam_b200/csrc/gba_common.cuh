@@ -26,7 +26,8 @@ static_assert(sizeof(EdgeGeo) == 64, "EdgeGeo must be 64 bytes");
 struct Status {          // device -> host after the index build
   int K;                 // depth keyframes
   int max_deg;           // largest out-degree
-  int err;               // bit0 index out of range, bit1 capacity, bit2 kx_global mismatch
+  int err;               // bit0 index out of range, bit1 capacity, bit2 kx_global mismatch, bit3 a local edge
+                         // needs a tile that the whole-graph edge list (ii_all / jj_all) does not have
   int n_tiles;           // tile rows
   int n_slots;           // active lower tiles after fill
   int max_col;           // max active sub-diagonal tiles in a tile column
@@ -37,7 +38,7 @@ struct Status {          // device -> host after the index build
   int n_seg;             // independent band segments (nested dissection); 1 = plain band
   int seg_tiles;         // tile columns per segment
   int n_pos;             // pose positions of the reduced system incl. padding
-  int pad2;
+  int last_fail;         // code of the most recent failed factorisation: 1 pivot <= 0, 3 / 4 a pipeline watchdog
   unsigned long long gram_floats;  // total size of the per-frame Gram buffers
 };
 

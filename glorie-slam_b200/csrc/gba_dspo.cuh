@@ -219,3 +219,4 @@ __global__ void __launch_bounds__(NT) k_dspo_update(DspoParams p) {
     p.shifts[frame] += dq;
   }
 }
+

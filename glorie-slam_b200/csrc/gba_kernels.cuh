@@ -9,13 +9,14 @@
 // ============================================================================================
 
 // one CTA: depth-keyframe list kx (sorted unique of [t0,t1) U ii), frame -> k map
-__global__ void __launch_bounds__(1024) k_prep_frames(BaParams p, const int64_t *kx_global, int n_kx) {
+__global__ void __launch_bounds__(1024) k_prep_frames(BaParams p, const int64_t *kx_global, int n_kx, int first_pass) {
   __shared__ int s_carry;
   __shared__ int s_warp[32];
   const int tid = threadIdx.x;
-  if (tid == 0) {
+  if (tid == 0 && first_pass) {  // a sharded begin builds the CSR twice: errors of the first pass must survive
     p.st->err = 0;
     p.st->chol_fail = 0;
+    p.st->last_fail = 0;
   }
   for (int f = tid; f < p.N; f += blockDim.x) p.fmap[f] = 0;
   __syncthreads();
@@ -969,6 +970,20 @@ __global__ void __launch_bounds__(NT) k_backsub(BaParams p) {
     if (p.dz_out)
       *reinterpret_cast<float4 *>(p.dz_out + (size_t)k * HW + px[g]) = make_float4(dzv[0], dzv[1], dzv[2], dzv[3]);
   }
+}
+
+// src/geom/ba.py:119 and :214 clamp the WHOLE disparity tensor at 0 after the update, also the keyframes
+// the solve never touches (no out-edge): those rows (fmap < 0) are clamped here, the rows in kx by the
+// update kernels themselves.  geom_py semantics and DSPO only; ba_cuda does not clamp.
+__global__ void __launch_bounds__(128) k_clamp_rest(float *disps, const int *fmap, int HW) {
+  const int frame = blockIdx.y;
+  if (fmap[frame] >= 0) return;
+  const int px = (blockIdx.x * 128 + threadIdx.x) * 4;
+  if (px >= HW) return;
+  float4 *q = reinterpret_cast<float4 *>(disps + (size_t)frame * HW + px);
+  const float4 z = *q;
+  if (z.x < 0.f || z.y < 0.f || z.z < 0.f || z.w < 0.f)
+    *q = make_float4(fmaxf(z.x, 0.f), fmaxf(z.y, 0.f), fmaxf(z.z, 0.f), fmaxf(z.w, 0.f));
 }
 
 // SE3 retraction T <- Exp(xi) T for the optimised poses.

@@ -164,6 +164,9 @@ extern "C" int gba_edge_blocks_static(const float *poses, const float *disps, co
   if (mode != GBA_MODE_DROID_CUDA && mode != GBA_MODE_GEOM_PY) return fail(GBA_EINVAL, "unknown mode");
   const long long hw = (long long)ht * wd;
   if (hw % 4 != 0) return fail(GBA_EINVAL, "ht*wd must be a multiple of 4");
+  // the kernel reads disps / targets / weights with 16-byte vector loads
+  if ((((uintptr_t)disps | (uintptr_t)targets | (uintptr_t)weights) & 15) != 0)
+    return fail(GBA_EINVAL, "disps, targets and weights must be 16-byte aligned");
   if (n_edges > GBA_STATIC_MAX_EDGES || hw > GBA_STATIC_MAX_PIXELS) {
     char msg[256];
     snprintf(msg, sizeof(msg),

@@ -208,6 +208,7 @@ __global__ void __launch_bounds__(1024) k_order(BaParams p, int pos_cap) {
 // Mark the tiles touched by the pose pairs of one depth keyframe (its own pose and the
 // destination poses of its out-edges are all mutually coupled through the Schur complement;
 // the pose-pose Hessian blocks (ii,ii),(ii,jj),(jj,jj) are a subset).
+template <bool CHECK>
 __global__ void k_tile_mark(BaParams p, unsigned int *tbits) {
   const int k = blockIdx.x;
   if (k >= p.st->K) return;
@@ -224,7 +225,10 @@ __global__ void k_tile_mark(BaParams p, unsigned int *tbits) {
     const int c0 = (6 * b) / GBA_NB, c1 = (6 * b + 5) / GBA_NB;
     for (int r = r0; r <= r1; r++)
       for (int c = c0; c <= c1; c++)
-        if (r >= c) atomicOr(&tbits[r * TS_WORDS + (c >> 5)], 1u << (c & 31));
+        if (r >= c) {
+          if (!CHECK) atomicOr(&tbits[r * TS_WORDS + (c >> 5)], 1u << (c & 31));
+          else if (!((tbits[r * TS_WORDS + (c >> 5)] >> (c & 31)) & 1u)) atomicOr(&p.st->err, 8);
+        }
   }
 }
 
@@ -1026,6 +1030,7 @@ __global__ void k_dx_out(BaParams p, SolverBufs sb) {
 __global__ void k_fail_account(BaParams p, SolverBufs sb) {
   if (*sb.fail) {
     p.st->chol_fail += 1;
+    p.st->last_fail = *sb.fail;
     *sb.fail = 0;
   }
 }

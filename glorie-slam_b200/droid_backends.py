@@ -24,9 +24,14 @@ import _gba
 # "droid_cuda" reproduces ba_cuda (default for the drop-in); "geom_py" reproduces
 # src/geom/ba.py::BA (SURVEY.md section 8.1 lists the differences).
 SEMANTICS = os.environ.get("GBA_SEMANTICS", "droid_cuda")
-# The reference returns [dx, dz]; GlORIE-SLAM discards them.  Sizing dz needs K on the host,
-# which costs one stream synchronisation after the call; set False to skip it.
+# The reference returns [dx, dz]; GlORIE-SLAM discards them.  K (the row count of dz) is on the host
+# once the index build has read its status back, so returning them costs no extra synchronisation;
+# set False to skip the dz buffer altogether.
 RETURN_UPDATES = True
+# A pipeline watchdog that fires (GBA_GET_WATCHDOG) ends an iteration like a failed factorisation:
+# zero pose update.  That must never happen in a healthy process, so it is not silent: the count is
+# checked whenever the caller synchronises anyway (`check_health`), and raises.
+_watchdog_seen = {}
 
 
 def _chk(t, name, dtype):
@@ -79,8 +84,26 @@ def ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, 
                                dz.data_ptr() if dz is not None else None, stream)
         _gba.check(ctx, rc)
         if dz is not None:
-            dz = dz[: _gba.query(ctx).n_depth_frames]
+            dz = dz[: _gba.lib().gba_last_depth_frames(ctx)]
     return [dx, dz]
+
+
+def check_health(device=None):
+    """Synchronises and raises if a kernel-internal watchdog fired since the last check (a pose update
+    was then silently zero, like a failed factorisation).  Returns gba_info of the device's context."""
+    out = None
+    for key, (ctx, _, _) in list(_gba._ctx.items()):
+        if device is not None and key[0] != torch.device(device).index:
+            continue
+        info = _gba.query(ctx)
+        seen = _watchdog_seen.get(key, 0)
+        _watchdog_seen[key] = info.watchdog_trips
+        if info.watchdog_trips > seen:
+            raise RuntimeError("libgba: %d kernel-internal wait(s) exceeded the watchdog (last failure code %d); the "
+                               "affected iterations applied a zero pose update" % (info.watchdog_trips - seen,
+                                                                                    info.last_fail_code))
+        out = info
+    return out
 
 
 def ba_interleaved(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1, iterations, lm, ep,

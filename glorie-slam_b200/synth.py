@@ -253,3 +253,82 @@ def make_config(name: str, seed=0, **over) -> Graph:
     if name == "D":
         with_mono_prior(g, seed=seed + 1)
     return g
+
+
+# ----------------------------------------------------------------------------
+# Edge cases the reference has code for
+# ----------------------------------------------------------------------------
+EDGE_CASES = ("near", "stereo", "step4", "step6")
+
+
+def reprojected_depth(g: Graph):
+    """Z_j of every edge pixel at the graph's START state, float64 [E,ht,wd]: which side of the
+    MIN_DEPTH tests (droid_kernels.cu:302-306, projective_ops.py:44,112) a pixel falls on."""
+    n, ht, wd = g.disps.shape
+    fx, fy, cx, cy = [float(v) for v in g.intrinsics]
+    v, u = np.meshgrid(np.arange(ht, dtype=np.float64), np.arange(wd, dtype=np.float64), indexing="ij")
+    x0, y0 = ((u - cx) / fx).reshape(-1), ((v - cy) / fy).reshape(-1)
+    t, q = g.poses[:, :3].astype(np.float64), g.poses[:, 3:].astype(np.float64)
+    tinv, qinv = se3_inv(t[g.ii], q[g.ii])
+    tij, qij = se3_mul(t[g.jj], q[g.jj], tinv, qinv)
+    z = g.disps[g.ii].reshape(len(g.ii), -1).astype(np.float64)
+    pts = np.stack([np.broadcast_to(x0, z.shape), np.broadcast_to(y0, z.shape), np.ones_like(z)], axis=-1)
+    xj = quat_rot(qij[:, None, :], pts) + tij[:, None, :] * z[..., None]
+    return xj[..., 2].reshape(len(g.ii), ht, wd)
+
+
+def make_edge_case(name: str) -> Graph:
+    """Small graphs (16 x 24 pixels) that drive the branches ordinary synthetic graphs never reach.
+
+    near    4 % of the pixels are very close points (disparity 4..40): their reprojected depth Z_j
+            lands below 0.1, in 0.1..0.2, in 0.2..0.25 and above, and behind the camera
+    stereo  three stereo self edges ii == jj among ordinary ones (droid_kernels.cu:219-229,323,356)
+    step4   nearly converged: the rotation update |phi| straddles 1e-4, i.e. theta^2 < 1e-8 and
+            theta > 1e-4 both occur in the hand-rolled exponential (droid_kernels.cu:119,162)
+    step6   converged further: |phi| straddles lietorch's EPS = 1e-6 (so3.h:153-170)
+    """
+    ht, wd = 16, 24
+    if name == "near":
+        g = make_graph(8, 24, 2, iters=2, seed=21, ht=ht, wd=wd)
+        rng = np.random.default_rng(121)
+        # the camera advances 0.07 per keyframe along its optical axis, so that close points
+        # (a quarter of the pixels, disparity 2..16) come within MIN_DEPTH of the neighbouring cameras
+        pgt = g.poses_gt.astype(np.float64)
+        pgt[:, 2] -= 0.07 * np.arange(g.n_frames)
+        mask = rng.uniform(size=g.disps.shape) < 0.25
+        big = rng.uniform(2.0, 16.0, size=g.disps.shape)
+        dgt = g.disps_gt.astype(np.float64)
+        dgt[mask] = big[mask]
+        tg = np.clip(project(pgt, dgt, g.intrinsics, g.ii, g.jj).astype(np.float64), -1e3, 1e3)
+        g.targets = (tg + rng.normal(0.0, 0.5, size=tg.shape)).astype(np.float32)
+        g.poses_gt, g.disps_gt = pgt.astype(np.float32), dgt.astype(np.float32)
+        poses = pgt.copy()
+        poses[1:] = se3_retr(rng.normal(0.0, 0.01, size=(g.n_frames - 1, 6)), pgt[1:])
+        g.poses = poses.astype(np.float32)
+        g.disps = (dgt * rng.uniform(0.9, 1.1, size=dgt.shape)).astype(np.float32)
+        return g
+    if name == "stereo":
+        g = make_graph(8, 24, 2, iters=2, seed=22, ht=ht, wd=wd)
+        rng = np.random.default_rng(122)
+        selfs = np.array([2, 5, 6], dtype=np.int64)
+        fx, cx = float(g.intrinsics[0]), float(g.intrinsics[2])
+        v, u = np.meshgrid(np.arange(ht, dtype=np.float64), np.arange(wd, dtype=np.float64), indexing="ij")
+        tg = np.zeros((len(selfs), 2, ht, wd))
+        for a, k in enumerate(selfs):  # G_ij = (t = (-0.1, 0, 0), q = identity): u shifts by -0.1 fx z
+            tg[a, 0] = u - 0.1 * fx * g.disps_gt[k]
+            tg[a, 1] = v
+        tg += rng.normal(0.0, 0.5, size=tg.shape)
+        where = [3, 11, 20]  # positions inside the edge list
+        ii, jj, T, W = list(g.ii), list(g.jj), list(g.targets), list(g.weights)
+        for a, pos in enumerate(where):
+            ii.insert(pos, int(selfs[a])); jj.insert(pos, int(selfs[a]))
+            T.insert(pos, tg[a].astype(np.float32))
+            W.insert(pos, rng.uniform(0.0, 1.0, size=tg[a].shape).astype(np.float32))
+        g.ii, g.jj = np.asarray(ii, dtype=np.int64), np.asarray(jj, dtype=np.int64)
+        g.targets, g.weights = np.stack(T).astype(np.float32), np.stack(W).astype(np.float32)
+        return g
+    if name in ("step4", "step6"):
+        s = 1e-4 if name == "step4" else 1e-6
+        return make_graph(8, 24, 2, iters=2, seed=23 if name == "step4" else 24, ht=ht, wd=wd, pose_noise=s,
+                          disp_noise=s, pixel_noise=0.0)
+    raise KeyError(name)

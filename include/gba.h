@@ -18,6 +18,9 @@
  *     iterations is reported by gba_query().
  *   - a context is bound to one device and is not re-entrant; calls are asynchronous on
  *     `stream` except for one small status read-back after the index build.
+ *   - per-pixel arrays (disps, disps_sens, targets, weights, eta, mono_disps, Q, W) are read with
+ *     16-byte vector loads: their base pointers must be 16-byte aligned (torch allocations are);
+ *     a misaligned pointer is refused with GBA_EINVAL.
  *   - no CPU fallback exists: every entry point fails with GBA_ECUDA when no device is usable.
  */
 #ifndef GBA_H_
@@ -122,8 +125,15 @@ typedef struct gba_info {
   int n_active_tiles;   /* lower-triangular tiles touched after symbolic fill */
   int kernel_launches;  /* kernels launched by the last gba_ba / gba_dspo call */
   int chain_columns;    /* tile columns on the factorisation's critical path: one band segment + the closure block */
+  int last_fail_code;   /* why the most recent failed factorisation failed: 1 = pivot <= 0 (the reference's
+                           NumericalIssue, droid_kernels.cu:1202-1210), 3 / 4 = an in-kernel wait of the tile
+                           Cholesky / the tensor-core Gram pipeline exceeded its watchdog; 0 = none since begin */
+  int watchdog_trips;   /* GBA_GET_WATCHDOG[0]: watchdog records since gba_create (0 in a healthy process)       */
 } gba_info;
 int gba_query(gba_ctx *ctx, gba_info *info);
+/* K = number of depth keyframes of the last gba_ba / gba_ba_begin / gba_dspo call on this context, from the host copy
+ * of the status the index build already read back: no device access, no synchronisation.  Sizes dz_out. */
+int gba_last_depth_frames(const gba_ctx *ctx);
 
 /* Copies an internal device array of the last call to HOST memory `dst` (capacity `bytes`).
  * what: */
@@ -233,6 +243,7 @@ int gba_projmap(const float *poses, const float *disps, const float *intrinsics,
  *   - All calls share the one array: calls whose kernels may overlap on the GPU (different
  *     streams, different threads) race with each other.  Serialise them on one stream.
  *   - ii / jj must lie in [0, n_frames); an edge that does not gets an all-zero block.
+ *   - disps / targets / weights must be 16-byte aligned (vector loads); otherwise GBA_EINVAL.
  *   - Asynchronous on `stream`, like gba_ba. */
 #define GBA_STATIC_MAX_EDGES 4096
 #define GBA_STATIC_MAX_PIXELS 4800 /* ht*wd, e.g. 60 x 80 */

@@ -535,9 +535,13 @@ int FN(oracle_ba)(REAL *poses, REAL *disps, const float *intr_f, const float *di
         int k2;
         for (k2 = 0; k2 < HW; k2++) {
           REAL dnew = disps[(size_t)kx[f] * HW + k2] + (REAL)dz[(size_t)f * HW + k2];
-          if (mode == 1 && dnew < 0) dnew = 0; /* ba.py:119 clamp(min=0) */
           disps[(size_t)kx[f] * HW + k2] = dnew;
         }
+      }
+      if (mode == 1) { /* ba.py:119 disps.clamp(min=0.0): the whole tensor, not only the rows in kx */
+        size_t q;
+        for (q = 0; q < (size_t)N * HW; q++)
+          if (disps[q] < 0) disps[q] = 0;
       }
     }
   }
@@ -698,12 +702,15 @@ int FN(oracle_dspo)(const REAL *poses, REAL *disps, const float *intr_f, const f
     const size_t fr = (size_t)kx[f];
     int k;
     for (k = 0; k < HW; k++) {
-      REAL dnew = disps[fr * HW + k] + (REAL)dzv[(size_t)f * HW + k];
-      if (dnew < 0) dnew = 0;
-      disps[fr * HW + k] = dnew;
+      disps[fr * HW + k] = disps[fr * HW + k] + (REAL)dzv[(size_t)f * HW + k];
     }
     scales[fr] += (REAL)dwq[2 * f];
     shifts[fr] += (REAL)dwq[2 * f + 1];
+  }
+  { /* ba.py:214 disps.clamp(min=0.0): the whole tensor, not only the rows in kx */
+    size_t q;
+    for (q = 0; q < (size_t)N * HW; q++)
+      if (disps[q] < 0) disps[q] = 0;
   }
   if (dz_out) memcpy(dz_out, dzv, sizeof(double) * (size_t)M * HW);
   if (dwq_out) memcpy(dwq_out, dwq, sizeof(double) * (size_t)M * 2);

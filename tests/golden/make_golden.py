@@ -38,8 +38,54 @@ CASES = {
 }
 
 
+def dspo_neg_graph():
+    """DSPO input with negative disparities, also on a keyframe WITHOUT out-edges (not in unique(ii)):
+    ba.py:214 clamps the whole tensor, not only the rows it solved for."""
+    g = synth.make_graph(7, 16, 2, iters=2, lm=1e-4, ep=0.1, seed=31, ht=16, wd=24)
+    keep = g.ii != 4  # keyframe 4 keeps only in-edges
+    g.ii, g.jj, g.targets, g.weights = g.ii[keep], g.jj[keep], g.targets[keep], g.weights[keep]
+    g.eta = g.eta[: len(np.unique(g.ii))]
+    synth.with_mono_prior(g, seed=32)
+    rng = np.random.default_rng(33)
+    neg = rng.uniform(size=g.disps.shape) < 0.05
+    g.disps[neg] = -g.disps[neg] * 0.3
+    return g
+
+
+EXTRA = {
+    # name: builder -- branches ordinary graphs never reach (synth.make_edge_case)
+    "near": lambda: synth.make_edge_case("near"),
+    "step6": lambda: synth.make_edge_case("step6"),
+}
+
+
 def main():
+    import sys as _sys
+
+    only = _sys.argv[1:]
+    for name, build in EXTRA.items():
+        if only and name not in only:
+            continue
+        g = build()
+        out = dict(checksum=checksum(g))
+        for tag, dt in (("f32", torch.float32), ("f64", torch.float64)):
+            p, d = ref_harness.run_BA(g, dtype=dt)
+            out["poses_" + tag] = p
+            out["disps_" + tag] = d
+        np.savez_compressed(os.path.join(HERE, "geom_%s.npz" % name), **out)
+        print("wrote geom_%s.npz" % name, {k: v.shape for k, v in out.items()})
+    if not only or "dspo_neg" in only:
+        g = dspo_neg_graph()
+        out = dict(checksum=checksum(g))
+        for tag, dt in (("f32", torch.float32), ("f64", torch.float64)):
+            d, wq = ref_harness.run_DSPO(g, iters=2, dtype=dt)
+            out["dspo_disps_" + tag] = d
+            out["dspo_wqs_" + tag] = wq
+        np.savez_compressed(os.path.join(HERE, "geom_dspo_neg.npz"), **out)
+        print("wrote geom_dspo_neg.npz", {k: v.shape for k, v in out.items()})
     for name, kw in CASES.items():
+        if only and name not in only:
+            continue
         g = synth.make_graph(**kw)
         out = dict(checksum=checksum(g))
         for tag, dt in (("f32", torch.float32), ("f64", torch.float64)):

@@ -36,14 +36,122 @@ GOLDEN_CASES = {
 }
 
 
+def dspo_neg_graph():
+    """DSPO input with negative disparities, also on a keyframe WITHOUT out-edges (ba.py:214 clamps the
+    whole tensor); must stay identical to tests/golden/make_golden.py::dspo_neg_graph"""
+    import synth
+
+    g = synth.make_graph(7, 16, 2, iters=2, lm=1e-4, ep=0.1, seed=31, ht=16, wd=24)
+    keep = g.ii != 4
+    g.ii, g.jj, g.targets, g.weights = g.ii[keep], g.jj[keep], g.targets[keep], g.weights[keep]
+    g.eta = g.eta[: len(np.unique(g.ii))]
+    synth.with_mono_prior(g, seed=32)
+    rng = np.random.default_rng(33)
+    neg = rng.uniform(size=g.disps.shape) < 0.05
+    g.disps[neg] = -g.disps[neg] * 0.3
+    return g
+
+
 def load_golden(name):
     import synth
 
-    kw = GOLDEN_CASES[name]
-    g = synth.make_graph(**kw)
+    if name in ("near", "step6"):
+        g, kw = synth.make_edge_case(name), {}
+    elif name == "dspo_neg":
+        g, kw = dspo_neg_graph(), {}
+    else:
+        kw = GOLDEN_CASES[name]
+        g = synth.make_graph(**kw)
     z = np.load(os.path.join(GOLDEN, "geom_%s.npz" % name))
     np.testing.assert_allclose(checksum(g), z["checksum"], rtol=1e-9, err_msg="synthetic generator drifted")
     return g, z, kw
+
+
+def small_graphs():
+    import synth
+
+    return {
+        "A": synth.make_config("A"),
+        "R": synth.make_graph(6, 14, 2, iters=2, lm=1e-5, ep=1e-2, seed=3, ht=30, wd=40, t0=2),
+        "tiny": synth.make_graph(5, 8, 1, iters=2, seed=2, ht=8, wd=12),
+        "B": synth.make_config("B"),
+    }
+
+
+# ---- fixtures produced by the reference's own CUDA extension (tests/golden/make_golden_cuda.py) ----
+# name -> (graph builder, keyword arguments of the ba call, stride of the stored disparity keyframes)
+def droid_case(name):
+    import synth
+
+    if name in ("A", "R", "tiny", "B"):
+        return small_graphs()[name], {}, 1
+    if name == "C":
+        return synth.make_config("C"), {}, 4
+    if name == "E":
+        return synth.make_config("E"), {}, 20
+    if name in synth.EDGE_CASES:
+        return synth.make_edge_case(name), {}, 1
+    if name == "R_motion":
+        return small_graphs()["R"], dict(motion_only=True), 1
+    if name == "R_depth":
+        return small_graphs()["R"], dict(depth_only=True), 1
+    if name == "tiny_sens":
+        g = small_graphs()["tiny"]
+        rng = np.random.default_rng(4)
+        g.disps_sens = (g.disps_gt * (rng.uniform(size=g.disps.shape) < 0.5)).astype(np.float32)
+        return g, {}, 1
+    raise KeyError(name)
+
+
+DROID_CASES = ("A", "R", "tiny", "B", "C", "E", "near", "stereo", "step4", "R_motion", "R_depth", "tiny_sens")
+
+
+def checksum_full(g):
+    return np.array([float(np.sum(np.asarray(a).astype(np.float64))) for a in
+                     (g.poses, g.disps, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj, g.intrinsics)])
+
+
+def load_droid_golden(name):
+    """(graph, call kwargs, stride, fixture) of one reference-CUDA fixture; checks that the seeded
+    generator still produces the inputs the fixture was computed from."""
+    g, kw, stride = droid_case(name)
+    z = np.load(os.path.join(GOLDEN, "droid_%s.npz" % name))
+    np.testing.assert_allclose(checksum_full(g), z["checksum"], rtol=1e-9, err_msg="synthetic generator drifted")
+    return g, kw, stride, z
+
+
+def frame_distance_case(name):
+    """inputs of the frame_distance fixtures: every ordered keyframe pair, one keyframe looking the other way"""
+    import synth
+
+    g = small_graphs()[name] if name != "C" else synth.make_config("C")
+    n = g.n_frames
+    ii, jj = np.meshgrid(np.arange(n), np.arange(n), indexing="ij")
+    poses = g.poses.copy()
+    poses[n // 2, 3:] = [0.0, 1.0, 0.0, 0.0]
+    return g, poses, ii.reshape(-1).astype(np.int64), jj.reshape(-1).astype(np.int64)
+
+
+DEPTH_FILTER_CASES = [(12, 24, 32, 0.0), (40, 48, 64, 0.01), (9, 21, 30, 0.02)]
+
+
+def depth_filter_case(n, ht, wd, noise):
+    poses, disps, intr = planar_scene(n, ht, wd, seed=n, noise=noise)
+    thresh = (0.02 * (1.0 / disps).mean(axis=(1, 2))).astype(np.float32)
+    inds = np.concatenate([np.arange(n), [3, 0]]).astype(np.int64)  # repeated / unordered entries are legal
+    th = np.concatenate([thresh, thresh[[3, 0]] * 0.1]).astype(np.float32)
+    return poses, disps, intr, inds, th
+
+
+def reproj_case(name):
+    """inputs of the iproj / projmap fixtures; returns graph, poses (keyframe 1 looks the other way),
+    keyframe stride of the stored iproj rows, edge stride of the stored projmap rows"""
+    import synth
+
+    g = small_graphs()["A"] if name == "A" else synth.make_config("C")
+    poses = g.poses.copy()
+    poses[1, 3:] = [0.0, 1.0, 0.0, 0.0]
+    return g, poses, (1 if name == "A" else 8), (1 if name == "A" else 100)
 
 
 def planar_scene(n_frames, ht, wd, seed=0, noise=0.0):
@@ -73,3 +181,34 @@ def planar_scene(n_frames, ht, wd, seed=0, noise=0.0):
     if noise > 0:
         disps *= 1.0 + rng.normal(0, noise, disps.shape)
     return poses.astype(np.float32), disps.astype(np.float32), intr.astype(np.float32)
+
+
+def dispatcher_case(seed=0, n=24, e=140, r=4, ht=24, wd=32, buf=32):
+    """Inputs for the call-site tests: a multi-view-consistent scene (planar_scene), so that depth_filter lets
+    most pixels through, a mono prior with one keyframe that has none, in a video buffer longer than the
+    keyframes in use.  Returns (graph, poses [buf,7], disps [buf,ht,wd], mono_disps [buf,ht,wd])."""
+    import synth
+
+    rng = np.random.default_rng(600 + seed)
+    pgt, dgt, intr = planar_scene(n, ht, wd, seed=70 + seed)
+    ii, jj = synth.make_edges(n, e, r, rng)
+    tg = synth.project(pgt, dgt, intr, ii, jj) + rng.normal(0.0, 0.3, size=(len(ii), 2, ht, wd))
+    poses = pgt.astype(np.float64).copy()
+    poses[1:] = synth.se3_retr(rng.normal(0.0, 0.003, size=(n - 1, 6)), poses[1:])
+    disps = dgt * rng.uniform(0.98, 1.02, size=dgt.shape)
+    kx = np.unique(np.concatenate([np.arange(1, n), ii]))
+    eta = (0.2 * rng.uniform(0.0, 0.01, size=(len(kx), ht, wd)) + 1e-7).astype(np.float32)
+    g = synth.Graph(poses=poses.astype(np.float32), disps=disps.astype(np.float32), intrinsics=intr,
+                    disps_sens=np.zeros_like(dgt), targets=tg.astype(np.float32),
+                    weights=rng.uniform(0.0, 1.0, size=tg.shape).astype(np.float32), eta=eta, ii=ii, jj=jj, t0=1, t1=n,
+                    iters=2, lm=1e-4, ep=0.1, poses_gt=pgt, disps_gt=dgt)
+    synth.with_mono_prior(g, seed=601 + seed)
+    # a clean affine prior (no dropped pixels: the scale fit of depth_video.py:233 does not mask them and would be
+    # ill-conditioned on this nearly fronto-parallel scene) ...
+    sc, sh = rng.uniform(0.7, 1.3, size=(n, 1, 1)), rng.normal(0.0, 0.02, size=(n, 1, 1))
+    g.mono_disps = ((dgt.astype(np.float64) - sh) / sc).astype(np.float32)
+    g.mono_disps[5] = 0.0  # ... except keyframe 5, which has none: the mono_thres filter drops its edges
+    pad = lambda a: np.concatenate([a, np.zeros((buf - a.shape[0],) + a.shape[1:], a.dtype)], 0)
+    pbuf = pad(g.poses)
+    pbuf[n:, 6] = 1.0
+    return g, pbuf, pad(g.disps), pad(g.mono_disps)

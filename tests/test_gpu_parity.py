@@ -9,22 +9,14 @@ import pytest
 import torch
 
 import synth
-from helpers import STATE_RTOL, load_golden, rel, sign_normalise
+import helpers
+from helpers import STATE_RTOL, load_golden, rel, sign_normalise, small_graphs
 from oracle import oracle
 
 pytestmark = pytest.mark.gpu
 
 import _gba  # noqa: E402
 from gba_run import get_array, run_ba, split_phase, to_dev  # noqa: E402
-
-
-def small_graphs():
-    return {
-        "A": synth.make_config("A"),
-        "R": synth.make_graph(6, 14, 2, iters=2, lm=1e-5, ep=1e-2, seed=3, ht=30, wd=40, t0=2),
-        "tiny": synth.make_graph(5, 8, 1, iters=2, seed=2, ht=8, wd=12),
-        "B": synth.make_config("B"),
-    }
 
 
 # ------------------------------------------------------------------------------------------
@@ -120,7 +112,7 @@ def test_state_matches_oracle(name, mode):
     np.testing.assert_array_equal(r.poses[: g.t0], g.poses[: g.t0])  # fixed poses never move
 
 
-@pytest.mark.parametrize("name", ["A", "R"])
+@pytest.mark.parametrize("name", ["A", "R", "near", "step6"])
 def test_geom_mode_matches_reference_golden(name):
     """golden vectors = the reference's own src/geom/ba.py::BA run on CPU (tests/golden/make_golden.py)"""
     g, z, kw = load_golden(name)
@@ -474,31 +466,21 @@ def test_full_size_properties(name):
 # ------------------------------------------------------------------------------------------
 # frame_distance
 # ------------------------------------------------------------------------------------------
-def _load_reference_so():
-    import importlib.util
+@pytest.fixture(scope="module")
+def geomfn():
+    """outputs of the reference's own CUDA frame_distance / depth_filter / iproj / projmap, written on a
+    B200 by tests/golden/make_golden_cuda.py"""
     import os
 
-    from helpers import ROOT
-
-    so = os.path.join(ROOT, "oracle", "_ref", "ref_droid_backends.so")
-    if not os.path.exists(so):
-        return None
-    spec = importlib.util.spec_from_file_location("ref_droid_backends", so)
-    ref = importlib.util.module_from_spec(spec)
-    spec.loader.exec_module(ref)
-    return ref
+    return np.load(os.path.join(helpers.GOLDEN, "geomfn.npz"))
 
 
 @pytest.mark.parametrize("name,hw", [("A", None), ("R", None), ("C", None)])
-def test_frame_distance_matches_oracle_and_reference(name, hw):
+def test_frame_distance_matches_oracle_and_reference(name, hw, geomfn):
     import droid_backends
 
-    g = small_graphs()[name] if name != "C" else synth.make_config("C")
+    g, poses, ii, jj = helpers.frame_distance_case(name)  # one keyframe looks the other way: its pairs return 1000
     n = g.n_frames
-    ii, jj = np.meshgrid(np.arange(n), np.arange(n), indexing="ij")
-    ii, jj = ii.reshape(-1), jj.reshape(-1)
-    poses = g.poses.copy()
-    poses[n // 2, 3:] = [0.0, 1.0, 0.0, 0.0]  # one keyframe looks the other way: its pairs return 1000
     want = oracle.frame_distance(poses, g.disps, g.intrinsics, ii, jj, 0.3, precision="f64")
     d = to_dev(g)
     tp = torch.from_numpy(poses).cuda()
@@ -510,10 +492,7 @@ def test_frame_distance_matches_oracle_and_reference(name, hw):
         assert (w == 1000.0).sum() >= n - 1
         ok = w != 1000.0
         np.testing.assert_allclose(got[ok], w[ok], rtol=1e-4, atol=1e-4)
-    ref = _load_reference_so()
-    if ref is not None:
-        r = ref.frame_distance(tp, d.disps, d.intr, ti, tj, 0.3).cpu().numpy()
-        got = droid_backends.frame_distance(tp, d.disps, d.intr, ti, tj, 0.3).cpu().numpy()
+        r = geomfn["fd_%s_%s" % (name, "ij" if a is ti else "ji")]  # the reference's CUDA kernel, same inputs
         np.testing.assert_array_equal(got == 1000.0, r == 1000.0)
         ok = r != 1000.0
         np.testing.assert_allclose(got[ok], r[ok], rtol=1e-4, atol=1e-4)
@@ -528,15 +507,11 @@ def test_frame_distance_matches_oracle_and_reference(name, hw):
 DEPTH_FILTER_MAX_FLIPS = 2e-3
 
 
-@pytest.mark.parametrize("n,ht,wd,noise", [(12, 24, 32, 0.0), (40, 48, 64, 0.01), (9, 21, 30, 0.02)])
-def test_depth_filter_matches_oracle_and_reference(n, ht, wd, noise):
+@pytest.mark.parametrize("n,ht,wd,noise", helpers.DEPTH_FILTER_CASES)
+def test_depth_filter_matches_oracle_and_reference(n, ht, wd, noise, geomfn):
     import droid_backends
-    from helpers import planar_scene
 
-    poses, disps, intr = planar_scene(n, ht, wd, seed=n, noise=noise)
-    thresh = (0.02 * (1.0 / disps).mean(axis=(1, 2))).astype(np.float32)
-    inds = np.concatenate([np.arange(n), [3, 0]])  # repeated / unordered entries are legal
-    th = np.concatenate([thresh, thresh[[3, 0]] * 0.1]).astype(np.float32)
+    poses, disps, intr, inds, th = helpers.depth_filter_case(n, ht, wd, noise)
     want = oracle.depth_filter(poses, disps, intr, inds, th)
     tp, td, ti = (torch.from_numpy(a).cuda() for a in (poses, disps, intr))
     tix, tth = torch.from_numpy(inds).cuda(), torch.from_numpy(th).cuda()
@@ -549,11 +524,9 @@ def test_depth_filter_matches_oracle_and_reference(n, ht, wd, noise):
     tp_long = torch.cat([tp, tp[:5]], 0)
     got2 = droid_backends.depth_filter(tp_long, td, ti, tix, tth).cpu().numpy()
     np.testing.assert_array_equal(got2, got)
-    ref = _load_reference_so()
-    if ref is not None:
-        r = ref.depth_filter(tp, td, ti, tix, tth).cpu().numpy()
-        d = np.abs(got - r)
-        assert d.max() <= 1 and (d > 0).mean() <= DEPTH_FILTER_MAX_FLIPS
+    r = geomfn["df_%d" % n].astype(np.float32)  # the reference's CUDA kernel, same inputs
+    d = np.abs(got - r)
+    assert d.max() <= 1 and (d > 0).mean() <= DEPTH_FILTER_MAX_FLIPS
 
 
 def test_depth_filter_empty_and_errors():
@@ -574,12 +547,10 @@ def test_depth_filter_empty_and_errors():
 # iproj + projmap
 # ------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("name", ["A", "C"])
-def test_iproj_and_projmap_match_oracle_and_reference(name):
+def test_iproj_and_projmap_match_oracle_and_reference(name, geomfn):
     import droid_backends
 
-    g = small_graphs()["A"] if name == "A" else synth.make_config("C")
-    poses = g.poses.copy()
-    poses[1, 3:] = [0.0, 1.0, 0.0, 0.0]  # keyframe 1 looks the other way: its pairs land behind the camera
+    g, poses, ks, es = helpers.reproj_case(name)  # keyframe 1 looks the other way: its pairs land behind the camera
     tp, td, ti = (torch.from_numpy(np.ascontiguousarray(a)).cuda() for a in (poses, g.disps, g.intrinsics))
     tii, tjj = torch.from_numpy(g.ii).cuda(), torch.from_numpy(g.jj).cuda()
     want = oracle.iproj(poses, g.disps, g.intrinsics, precision="f64")
@@ -596,15 +567,13 @@ def test_iproj_and_projmap_match_oracle_and_reference(name):
     ok = np.broadcast_to(same & (np.abs(wc[..., :1]) < 1e4), wc.shape)
     np.testing.assert_allclose(gc[ok], wc[ok], rtol=1e-4, atol=2e-3)
     np.testing.assert_array_equal(gc[..., 2], 0.0)
-    ref = _load_reference_so()
-    if ref is not None:
-        np.testing.assert_allclose(got, ref.iproj(tp, td, ti).cpu().numpy(), rtol=2e-5, atol=2e-5)
-        rc, rv = ref.projmap(tp, td, ti, tii, tjj)
-        rc, rv = rc.cpu().numpy(), rv.cpu().numpy()
-        same = gv == rv
-        assert same.mean() > 0.9999
-        ok = np.broadcast_to(same & (np.abs(rc[..., :1]) < 1e4), rc.shape)
-        np.testing.assert_allclose(gc[ok], rc[ok], rtol=1e-4, atol=2e-3)
+    # the reference's CUDA kernels on the same inputs (every ks-th keyframe / es-th edge is stored)
+    np.testing.assert_allclose(got[::ks], geomfn["iproj_%s" % name], rtol=2e-5, atol=2e-5)
+    rc, rv = geomfn["projmap_%s_coords" % name], geomfn["projmap_%s_valid" % name].astype(np.float32)
+    same = gv[::es] == rv
+    assert same.mean() > 0.9999
+    ok = np.broadcast_to(same & (np.abs(rc[..., :1]) < 1e4), rc.shape)
+    np.testing.assert_allclose(gc[::es][ok], rc[ok], rtol=1e-4, atol=2e-3)
     assert droid_backends.projmap(tp, td, ti, tii[:0], tjj[:0])[0].shape == (0,) + g.disps.shape[1:] + (3,)
 
 
@@ -657,26 +626,215 @@ def test_moba_mirror_matches_oracle():
     assert rel(sign_normalise(poses[0].cpu().numpy()), sign_normalise(o.poses)) < STATE_RTOL
 
 
-def test_reference_cuda_backend_if_present():
-    """On the B200 box: the reference's own droid_backends.ba (oracle/_ref, built by
-    oracle/build_ref.py from the unmodified sources) against libgba on configs A, R and B."""
-    import importlib.util
-    import os
+# ------------------------------------------------------------------------------------------
+# THE parity gate of the default semantics: the reference's own CUDA droid_backends.ba.  The fixtures
+# were written on a B200 by the unmodified reference extension (tests/golden/make_golden_cuda.py):
+# configs A, B, C and E of BASELINE.json, the ragged / tiny graphs, pixels on every side of the
+# MIN_DEPTH test, stereo self edges, rotation updates around the 1e-4 thresholds of the hand-rolled
+# exponential, motion_only, depth_only and the sensor-depth prior.
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", helpers.DROID_CASES)
+def test_droid_mode_matches_reference_cuda_golden(name):
+    g, kw, stride, z = helpers.load_droid_golden(name)
+    r = run_ba(g, **kw)
+    assert r.info.chol_failures == 0 and r.info.watchdog_trips == 0
+    assert rel(sign_normalise(r.poses), sign_normalise(z["poses"])) < STATE_RTOL
+    assert rel(r.disps[::stride], z["disps"]) < STATE_RTOL
+    # the returned updates of the last iteration (small numbers: looser bound, informative only)
+    tol = 2e-2 if name == "step4" else 2e-3
+    assert rel(r.dx, z["dx"]) < tol
+    if "dz" in z.files:
+        assert r.dz.shape == z["dz"].shape and rel(r.dz, z["dz"]) < tol
+    if kw.get("motion_only"):
+        np.testing.assert_array_equal(r.disps, g.disps)
+    if kw.get("depth_only"):
+        np.testing.assert_array_equal(r.poses, g.poses)
 
-    from helpers import ROOT
 
-    so = os.path.join(ROOT, "oracle", "_ref", "ref_droid_backends.so")
-    if not os.path.exists(so):
-        pytest.skip("oracle/_ref/ref_droid_backends.so not built")
-    spec = importlib.util.spec_from_file_location("ref_droid_backends", so)
-    ref = importlib.util.module_from_spec(spec)
-    spec.loader.exec_module(ref)
-    for name in ("A", "R", "B", "C"):
-        g = small_graphs()[name] if name != "C" else synth.make_config("C")
-        d = to_dev(g)
-        ref.ba(d.poses, d.disps, d.intr, d.sens, d.targets, d.weights, d.eta, d.ii, d.jj, g.t0, g.t1, g.iters, g.lm,
-               g.ep, False, False)
-        torch.cuda.synchronize()
-        r = run_ba(g)
-        assert rel(sign_normalise(r.poses), sign_normalise(d.poses.cpu().numpy())) < STATE_RTOL, name
-        assert rel(r.disps, d.disps.cpu().numpy()) < STATE_RTOL, name
+def test_config_c_matches_fp64_oracle():
+    """config C (200 keyframes / 3000 edges / 48 x 64, BASELINE.json configs[2]) against the fp64 oracle"""
+    g = synth.make_config("C")
+    o = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj, g.t0, g.t1,
+                  g.iters, g.lm, g.ep, precision="f64")
+    r = run_ba(g)
+    assert rel(sign_normalise(r.poses), sign_normalise(o.poses)) < STATE_RTOL
+    assert rel(r.disps, o.disps) < STATE_RTOL
+
+
+def test_dspo_clamps_every_row_like_the_reference():
+    """golden = the reference's BA_with_scale_shift on negative disparities, some on a keyframe that has no
+    out-edge: ba.py:214 clamps the whole tensor"""
+    import geom_ba
+
+    g, z, _ = load_golden("dspo_neg")
+    d = to_dev(g)
+    tg = d.targets.permute(0, 2, 3, 1).contiguous()[None]
+    wg = d.weights.permute(0, 2, 3, 1).contiguous()[None]
+    disps, poses = d.disps[None], d.poses[None]
+    intr = d.intr[None, None].repeat(1, g.n_frames, 1)
+    mono = torch.from_numpy(g.mono_disps).cuda()[None]
+    mask = torch.from_numpy(g.valid_depth_mask).cuda()[None]
+    scales, shifts = torch.from_numpy(g.scales).cuda()[None], torch.from_numpy(g.shifts).cuda()[None]
+    for _ in range(2):
+        poses, disps, wqs = geom_ba.BA_with_scale_shift(tg, wg, d.eta, poses, disps, intr, d.ii, d.jj, mono, scales,
+                                                        shifts, mask, 0, g.lm, g.ep, alpha=g.alpha)
+        scales, shifts = wqs[..., 0], wqs[..., 1]
+    out = disps[0].cpu().numpy()
+    assert out.min() == 0.0 and (out[4] == 0).any()
+    assert rel(out, z["dspo_disps_f64"]) < STATE_RTOL
+    assert rel(wqs[0].cpu().numpy(), z["dspo_wqs_f64"]) < STATE_RTOL
+
+
+def test_geom_mode_clamps_every_row():
+    """src/geom/ba.py:119: disps.clamp(min=0) acts on every keyframe, also one outside unique(ii)"""
+    g = synth.make_graph(7, 16, 2, iters=1, seed=41, ht=16, wd=24)
+    keep = g.ii != 4
+    g.ii, g.jj, g.targets, g.weights = g.ii[keep], g.jj[keep], g.targets[keep], g.weights[keep]
+    g.eta = g.eta[: len(np.unique(g.ii))]
+    g.disps[4, :3] = -0.2
+    o = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj, g.t0, g.t1,
+                  1, g.lm, g.ep, mode=oracle.MODE_GEOM_PY, precision="f64")
+    r = run_ba(g, mode="geom_py", iters=1)
+    assert (o.disps[4, :3] == 0).all() and (r.disps[4, :3] == 0).all()
+    assert rel(r.disps, o.disps) < STATE_RTOL
+
+
+# ------------------------------------------------------------------------------------------
+# boundary hardening
+# ------------------------------------------------------------------------------------------
+def test_misaligned_pointers_are_refused():
+    """every per-pixel array is read with 16-byte vector loads: a view that starts 4 bytes into an allocation
+    must come back as GBA_EINVAL, not as a misaligned-address fault"""
+    import droid_backends
+
+    g = small_graphs()["tiny"]
+    d = to_dev(g)
+    args = [d.poses, d.disps, d.intr, d.sens, d.targets, d.weights, d.eta, d.ii, d.jj, g.t0, g.t1, 1, 1e-4, 0.1, False]
+    for idx in (1, 4, 5, 6):
+        t = args[idx]
+        shifted = torch.zeros(t.numel() + 1, dtype=t.dtype, device=t.device)[1:].view(t.shape)
+        shifted.copy_(t)
+        assert shifted.is_contiguous() and shifted.data_ptr() % 16 == 4
+        bad = list(args)
+        bad[idx] = shifted
+        with pytest.raises(RuntimeError, match="aligned"):
+            droid_backends.ba(*bad)
+    droid_backends.ba(*args)  # and the context still works
+    torch.cuda.synchronize()
+    L = _gba.lib()
+    out = torch.zeros(g.n_edges, 32, device="cuda")
+    off = torch.zeros(d.targets.numel() + 1, device="cuda")[1:].view(d.targets.shape)
+    rc = L.gba_edge_blocks_static(d.poses.data_ptr(), d.disps.data_ptr(), d.intr.data_ptr(), off.data_ptr(),
+                                  d.weights.data_ptr(), d.ii.data_ptr(), d.jj.data_ptr(), g.n_frames, g.n_edges,
+                                  g.disps.shape[1], g.disps.shape[2], 0, out.data_ptr(), None)
+    assert rc == -1 and b"aligned" in L.gba_last_error(None)
+
+
+def test_sharded_begin_rejects_a_local_edge_missing_from_the_whole_graph():
+    """gba_ba_begin derives the tile structure from ii_all / jj_all; a local edge that is not part of it would
+    add into a tile that does not exist.  It must be refused (GBA_EINVAL), not written somewhere."""
+    g = synth.make_config("C")  # large enough that a far edge needs a tile of its own
+    L = _gba.lib()
+    N, ht, wd = g.disps.shape
+    kx = np.unique(np.concatenate([np.arange(g.t0, g.t1), g.ii]))
+    far = (np.abs(g.ii - g.jj) > 60)
+    assert far.any()
+    keep = ~far  # the "whole graph" the caller declares lacks the long-range edges ...
+    d = to_dev(g)  # ... but the local edge list still has them
+    h = ctypes.c_void_p()
+    assert L.gba_create(ctypes.byref(h), 0, N, g.n_edges, ht, wd) == 0
+    ii_all, jj_all = torch.from_numpy(g.ii[keep]).cuda(), torch.from_numpy(g.jj[keep]).cuda()
+    pad = g.n_edges - int(keep.sum())
+    ii_all = torch.cat([ii_all, ii_all[:pad]]).contiguous()  # n_all >= n_edges, yet not a superset
+    jj_all = torch.cat([jj_all, jj_all[:pad]]).contiguous()
+    kx_t, own = torch.from_numpy(kx).cuda(), torch.ones(len(kx), dtype=torch.uint8, device="cuda")
+    rc = L.gba_ba_begin(h, d.poses.data_ptr(), d.disps.data_ptr(), d.intr.data_ptr(), d.sens.data_ptr(),
+                        d.targets.data_ptr(), d.weights.data_ptr(), d.eta.data_ptr(), d.ii.data_ptr(), d.jj.data_ptr(),
+                        N, g.n_edges, g.eta.shape[0], g.t0, g.t1, g.lm, g.ep, 0, 0, 0, kx_t.data_ptr(), len(kx),
+                        own.data_ptr(), ii_all.data_ptr(), jj_all.data_ptr(), int(ii_all.shape[0]), None)
+    assert rc == -1 and b"ii_all" in L.gba_last_error(h)
+    # an out-of-range index in the whole-graph list is still reported although the CSR is rebuilt afterwards
+    bad = torch.from_numpy(g.ii).cuda().clone()
+    bad[7] = N + 5
+    rc = L.gba_ba_begin(h, d.poses.data_ptr(), d.disps.data_ptr(), d.intr.data_ptr(), d.sens.data_ptr(),
+                        d.targets.data_ptr(), d.weights.data_ptr(), d.eta.data_ptr(), d.ii.data_ptr(), d.jj.data_ptr(),
+                        N, g.n_edges, g.eta.shape[0], g.t0, g.t1, g.lm, g.ep, 0, 0, 0, kx_t.data_ptr(), len(kx),
+                        own.data_ptr(), bad.data_ptr(), d.jj.data_ptr(), g.n_edges, None)
+    assert rc == -1 and b"outside" in L.gba_last_error(h)
+    L.gba_destroy(h)
+
+
+# ------------------------------------------------------------------------------------------
+# the call site: DepthVideo.ba / .dspo (src/depth_video.py:198-298) driving the drop-ins
+# ------------------------------------------------------------------------------------------
+def test_dispatcher_pose_depth_branch():
+    """depth_video.py:214-220: view/permute/contiguous, the 16 positional arguments, clamp(min=1e-5)"""
+    from stub_depth_video import StubDepthVideo
+
+    g, poses, disps, mono = helpers.dispatcher_case(0)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    v = StubDepthVideo(t(poses), t(disps), t(g.intrinsics), t(mono), g.n_frames, ba_type="DBA")
+    target = t(g.targets).permute(0, 2, 3, 1).contiguous()[None]  # [1,E,ht,wd,2] as the update operator emits it
+    weight = t(g.weights).permute(0, 2, 3, 1).contiguous()[None]
+    v.ba(target, weight, t(g.eta), t(g.ii), t(g.jj), t0=g.t0, t1=None, iters=2, lm=g.lm, ep=g.ep)
+    assert v.calls == ["pose_depth"]
+    o = oracle.ba(poses, disps, g.intrinsics, np.zeros_like(disps), g.targets, g.weights, g.eta, g.ii, g.jj, g.t0,
+                  g.n_frames, 2, g.lm, g.ep, precision="f64")
+    assert rel(sign_normalise(v.poses.cpu().numpy()), sign_normalise(o.poses)) < STATE_RTOL
+    assert rel(v.disps.cpu().numpy(), np.maximum(o.disps, 1e-5)) < STATE_RTOL
+    assert v.disps.min().item() >= 1e-5  # rows beyond the keyframes in use were 0 and are clamped too
+
+
+def test_dispatcher_depth_scale_branch():
+    """depth_video.py:221-288: depth_filter -> valid mask -> align_scale_and_shift -> mono_thres edge filter ->
+    itrs x BA_with_scale_shift -> rebind, against the same pipeline on the CPU oracle"""
+    from stub_depth_video import StubDepthVideo
+
+    g, poses, disps, mono = helpers.dispatcher_case(1)
+    n = g.n_frames
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    v = StubDepthVideo(t(poses), t(disps), t(g.intrinsics), t(mono), n, mono_thres=0.5)
+    target = t(g.targets).permute(0, 2, 3, 1).contiguous()[None]
+    weight = t(g.weights).permute(0, 2, 3, 1).contiguous()[None]
+    kx_all = np.unique(g.ii)
+    eta = g.eta[: len(kx_all)]
+    v.ba(target, weight, t(eta), t(g.ii), t(g.jj), t0=g.t0, t1=None, iters=2, lm=g.lm, ep=g.ep, opt_type="depth_scale")
+    assert v.calls == ["depth_scale"]
+    # ---- the same steps on the CPU oracle ----
+    depths = 1.0 / disps[:n].astype(np.float64)
+    thresh = (v.mv_thresh * depths.mean(axis=(1, 2))).astype(np.float32)
+    cnt = oracle.depth_filter(poses, disps, g.intrinsics, np.arange(n), thresh)
+    dd = np.where(cnt >= v.visible_num, (1.0 / disps[:n]).astype(np.float32), np.nan)
+    med = np.array([np.sort(r[~np.isnan(r)])[(np.sum(~np.isnan(r)) - 1) // 2] if (~np.isnan(r)).any() else np.nan
+                    for r in dd.reshape(n, -1)], dtype=np.float32)  # torch.nanmedian takes the lower middle
+    mask = dd < 3 * med[:, None, None]
+    got_mask = v.valid_depth_mask_small[:n].cpu().numpy()
+    assert (got_mask != mask).mean() < 2e-3  # depth_filter votes may flip on threshold-borderline pixels
+    s, q, e = oracle.align_scale_and_shift(mono[:n], disps[:n], got_mask.astype(np.float32), precision="f64")
+    avg = disps[:n].mean(axis=(1, 2))
+    with np.errstate(invalid="ignore", divide="ignore"):
+        invalid = (e / avg > v.mono_thres) | np.isnan(e) | (s < 0) | (got_mask.sum(axis=(1, 2)) < 0.5 * got_mask[0].size)
+    assert invalid[5] and not invalid.all()
+    drop = np.isin(g.ii, np.where(invalid)[0]) | np.isin(g.jj, np.where(invalid)[0])
+    ii_t, jj_t = g.ii[~drop], g.jj[~drop]
+    np.testing.assert_array_equal(v.last_filter[0].cpu().numpy(), ii_t)
+    np.testing.assert_array_equal(v.last_filter[1].cpu().numpy(), jj_t)
+    eta_t = eta[np.isin(kx_all, np.unique(ii_t))]
+    assert v.last_filter[2] == eta_t.shape[0]
+    tg = np.ascontiguousarray(g.targets.transpose(0, 2, 3, 1))[~drop]
+    wg = np.ascontiguousarray(g.weights.transpose(0, 2, 3, 1))[~drop]
+    buf = poses.shape[0]
+    sc, sh = np.ones(buf), np.zeros(buf)
+    sc[:n], sh[:n] = s, q
+    maskbuf = np.zeros(disps.shape, dtype=bool)
+    maskbuf[:n] = got_mask
+    dz = disps
+    for _ in range(2):
+        o = oracle.dspo(poses, dz, g.intrinsics, tg, wg, eta_t, ii_t, jj_t, mono, sc, sh, maskbuf, 0, g.lm, g.ep, 0.01,
+                        interleaved=True, precision="f64")
+        dz, sc, sh = o.disps, o.scales, o.shifts
+    assert rel(v.disps.cpu().numpy(), np.maximum(dz, 1e-5)) < STATE_RTOL
+    ok = ~invalid
+    assert rel(v.depth_scale.cpu().numpy()[:n][ok], sc[:n][ok]) < STATE_RTOL
+    assert rel(v.depth_shift.cpu().numpy()[:n][ok], sh[:n][ok]) < 1e-3  # shifts are ~0.05: absolute scale of the scales
+    np.testing.assert_array_equal(v.poses.cpu().numpy(), poses)  # stage 2 leaves the poses alone

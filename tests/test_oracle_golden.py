@@ -4,11 +4,78 @@ import numpy as np
 import pytest
 
 import synth
+import helpers
 from helpers import STATE_RTOL, load_golden, rel, sign_normalise
 from oracle import oracle
 
 
-@pytest.mark.parametrize("name", ["A", "R"])
+# ------------------------------------------------------------------------------------------
+# droid_cuda mode: fixtures written ON A B200 by the reference's own CUDA droid_backends.ba,
+# frame_distance, depth_filter, iproj, projmap (tests/golden/make_golden_cuda.py).  Config E is
+# left to the GPU suite: the dense fp64 oracle needs minutes for 5994 unknowns.
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", [n for n in helpers.DROID_CASES if n != "E"])
+def test_ba_droid_mode_matches_reference_cuda(name):
+    g, kw, stride, z = helpers.load_droid_golden(name)
+    for prec in ("f64", "f32"):
+        o = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj,
+                      g.t0, g.t1, g.iters, g.lm, g.ep, precision=prec, **kw)
+        assert o.fail == 0
+        # the reference is fp32 with fp32 block reductions: 2.6e-6 is the worst seen (config C)
+        assert rel(sign_normalise(o.poses), sign_normalise(z["poses"])) < 1e-5, prec
+        assert rel(o.disps[::stride], z["disps"]) < 1e-5, prec
+        # updates of the last iteration: small numbers, hence the looser bound (step4: dx ~ 1e-6)
+        assert rel(o.dx, z["dx"]) < (5e-3 if name == "step4" else 5e-4), prec
+        if "dz" in z.files:
+            assert rel(o.dz, z["dz"]) < (5e-3 if name == "step4" else 5e-4), prec
+    if kw.get("motion_only"):
+        np.testing.assert_array_equal(z["disps"], g.disps)  # the reference leaves disparities alone
+    if kw.get("depth_only"):
+        np.testing.assert_array_equal(z["poses"], g.poses)
+
+
+@pytest.fixture(scope="module")
+def geomfn():
+    return np.load(helpers.os.path.join(helpers.GOLDEN, "geomfn.npz"))
+
+
+@pytest.mark.parametrize("name", ["A", "R", "C"])
+def test_frame_distance_matches_reference_cuda(name, geomfn):
+    g, poses, ii, jj = helpers.frame_distance_case(name)
+    np.testing.assert_allclose([poses.astype(np.float64).sum(), g.disps.astype(np.float64).sum()],
+                               geomfn["fd_%s_checksum" % name], rtol=1e-9)
+    for key, a, b in (("ij", ii, jj), ("ji", jj, ii)):
+        ref = geomfn["fd_%s_%s" % (name, key)]
+        got = oracle.frame_distance(poses, g.disps, g.intrinsics, a, b, 0.3, precision="f64")
+        np.testing.assert_array_equal(got == 1000.0, ref == 1000.0)
+        ok = ref != 1000.0
+        np.testing.assert_allclose(got[ok], ref[ok], rtol=1e-4, atol=1e-4)
+
+
+@pytest.mark.parametrize("case", helpers.DEPTH_FILTER_CASES)
+def test_depth_filter_matches_reference_cuda(case, geomfn):
+    poses, disps, intr, inds, th = helpers.depth_filter_case(*case)
+    ref = geomfn["df_%d" % case[0]].astype(np.float32)
+    got = oracle.depth_filter(poses, disps, intr, inds, th)
+    diff = np.abs(got - ref)
+    # thresholded decisions on fp32 geometry: a pixel exactly on a threshold may flip with the rounding
+    assert diff.max() <= 1 and (diff > 0).mean() <= 2e-3
+
+
+@pytest.mark.parametrize("name", ["A", "C"])
+def test_iproj_projmap_match_reference_cuda(name, geomfn):
+    g, poses, ks, es = helpers.reproj_case(name)
+    got = oracle.iproj(poses, g.disps, g.intrinsics, precision="f64")[::ks]
+    np.testing.assert_allclose(got, geomfn["iproj_%s" % name], rtol=2e-5, atol=2e-5)
+    c, v = oracle.projmap(poses, g.disps, g.intrinsics, g.ii[::es], g.jj[::es], precision="f64")
+    rc, rv = geomfn["projmap_%s_coords" % name], geomfn["projmap_%s_valid" % name].astype(np.float64)
+    same = v == rv
+    assert same.mean() > 0.9999 and 0 < (rv == 0).sum() < rv.size
+    ok = np.broadcast_to(same & (np.abs(rc[..., :1]) < 1e4), rc.shape)
+    np.testing.assert_allclose(c[ok], rc[ok], rtol=1e-4, atol=2e-3)
+
+
+@pytest.mark.parametrize("name", ["A", "R", "near", "step6"])
 def test_ba_geom_mode_matches_reference_fp64(name):
     g, z, kw = load_golden(name)
     o = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj,
@@ -19,7 +86,24 @@ def test_ba_geom_mode_matches_reference_fp64(name):
     assert rel(o.disps, z["disps_f64"].reshape(o.disps.shape)) < 1e-7
 
 
-@pytest.mark.parametrize("name", ["A", "R"])
+def test_edge_case_graphs_reach_the_branches():
+    """near: pixels on every side of Z = 0.1 / 0.2 / 0.25 and behind the camera (projective_ops.py:44,112,
+    droid_kernels.cu:302-306); step4 / step6: rotation updates on both sides of 1e-4 (droid_kernels.cu:119,162)
+    and of lietorch's EPS 1e-6 (so3.h:153-170); stereo: self edges present"""
+    Z = synth.reprojected_depth(synth.make_edge_case("near"))
+    for lo, hi in ((-1e9, 0.0), (0.0, 0.1), (0.1, 0.2), (0.2, 0.25), (0.25, 1e9)):
+        assert ((Z >= lo) & (Z < hi)).sum() >= 20, (lo, hi)
+    for name, thr, mode in (("step4", 1e-4, oracle.MODE_DROID_CUDA), ("step6", 1e-6, oracle.MODE_GEOM_PY)):
+        g = synth.make_edge_case(name)
+        o = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj,
+                      g.t0, g.t1, 1, g.lm, g.ep, mode=mode, precision="f64")
+        th = np.linalg.norm(o.dx[:, 3:], axis=1)
+        assert th.min() < thr < th.max(), (name, th.min(), th.max())
+    g = synth.make_edge_case("stereo")
+    assert (g.ii == g.jj).sum() == 3
+
+
+@pytest.mark.parametrize("name", ["A", "R", "near", "step6"])
 def test_ba_geom_mode_fp32_within_bar(name):
     g, z, kw = load_golden(name)
     o = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj,
@@ -45,6 +129,22 @@ def test_dspo_matches_reference(name):
         wq = np.stack([sc, sh], -1)
         assert rel(disps, z["dspo_disps_f64"]) < tol
         assert rel(wq, z["dspo_wqs_f64"]) < tol
+
+
+def test_dspo_clamps_the_whole_tensor_like_the_reference():
+    """negative disparities, also on a keyframe outside unique(ii): ba.py:214 clamps everything"""
+    g, z, _ = load_golden("dspo_neg")
+    assert (g.disps[4] < 0).any() and 4 not in set(g.ii.tolist())
+    tg = np.ascontiguousarray(g.targets.transpose(0, 2, 3, 1))
+    wg = np.ascontiguousarray(g.weights.transpose(0, 2, 3, 1))
+    disps, sc, sh = g.disps, g.scales, g.shifts
+    for _ in range(2):
+        o = oracle.dspo(g.poses, disps, g.intrinsics, tg, wg, g.eta, g.ii, g.jj, g.mono_disps, sc, sh,
+                        g.valid_depth_mask, 0, g.lm, g.ep, g.alpha, interleaved=True, precision="f64")
+        disps, sc, sh = o.disps, o.scales, o.shifts
+    assert z["dspo_disps_f64"].min() == 0.0 and (z["dspo_disps_f64"][4] == 0).any()
+    assert rel(disps, z["dspo_disps_f64"]) < 1e-6
+    assert rel(np.stack([sc, sh], -1), z["dspo_wqs_f64"]) < 1e-6
 
 
 def test_planar_and_interleaved_layouts_agree():
