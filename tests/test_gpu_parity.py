@@ -782,7 +782,7 @@ def test_dispatcher_pose_depth_branch():
                   g.n_frames, 2, g.lm, g.ep, precision="f64")
     assert rel(sign_normalise(v.poses.cpu().numpy()), sign_normalise(o.poses)) < STATE_RTOL
     assert rel(v.disps.cpu().numpy(), np.maximum(o.disps, 1e-5)) < STATE_RTOL
-    assert v.disps.min().item() >= 1e-5  # rows beyond the keyframes in use were 0 and are clamped too
+    assert v.disps.min().item() >= float(np.float32(1e-5))  # rows beyond the keyframes in use were 0 and are clamped too
 
 
 def test_dispatcher_depth_scale_branch():
