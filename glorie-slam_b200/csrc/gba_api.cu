@@ -99,7 +99,7 @@ static cudaError_t dalloc(T **p, size_t n) {
   return cudaMalloc((void **)p, std::max<size_t>(n, 1) * sizeof(T));
 }
 
-static const int kSolverSmem = (2 * GBA_NB + 16) * (GBA_NB + 1) * (int)sizeof(double);
+static const int kSolverSmem = DM_SMEM_BYTES;
 static const int kGramSmemMax = 200 * 1024;
 
 extern "C" const char *gba_last_error(const gba_ctx *c) { return c ? c->err : g_create_err; }
@@ -203,7 +203,7 @@ extern "C" int gba_create(gba_ctx **out, int device, int max_frames, int max_edg
   CKC(dalloc(&c->wdog, 256));
   CKC(cudaMemset(c->wdog, 0, 256 * sizeof(int)));
   CKC(dalloc(&c->sb.tbits, nT * TS_WORDS));
-  CKC(dalloc(&c->flags, 5 * nT));
+  CKC(dalloc(&c->flags, 7 * nT));
   c->slot_cap = std::min<size_t>(nT * (nT + 1) / 2, (size_t)131072);
   CKC(dalloc(&c->upd, c->slot_cap));
   c->sb.upd = c->upd;
@@ -212,6 +212,8 @@ extern "C" int gba_create(gba_ctx **out, int device, int max_frames, int max_edg
   c->sb.cntB = c->flags + nT;
   c->sb.cntD = c->flags + 2 * nT;
   c->sb.flagX = c->flags + 3 * nT;
+  c->sb.cntY = c->flags + 5 * nT;
+  c->sb.ticket2 = c->flags + 6 * nT;
   CKC(cudaMemset(c->sb.fail, 0, sizeof(int)));
   CKC(cudaMemset(c->st_d, 0, sizeof(Status)));
   CKC(cudaFuncSetAttribute(k_gram, cudaFuncAttributeMaxDynamicSharedMemorySize, kGramSmemMax));
@@ -507,7 +509,7 @@ extern "C" int gba_ba_solve(gba_ctx *c) {
     k_damp<<<(6 * p.P + 255) / 256, 256, 0, s>>>(p, p.lm, p.ep);
     LAUNCH_CHECK("k_damp");
   }
-  CK(cudaMemsetAsync(c->flags, 0, (size_t)5 * c->nT_max * sizeof(unsigned int), s));
+  CK(cudaMemsetAsync(c->flags, 0, (size_t)7 * c->nT_max * sizeof(unsigned int), s));
   {
     // Tile columns of the n_seg band segments are independent: step t of every segment is one
     // launch (grid.y = segment); the closure block follows column by column.  16-row slabs
@@ -542,17 +544,23 @@ extern "C" int gba_ba_solve(gba_ctx *c) {
     };
     // One launch: the whole factorisation as a dependency graph of tile tasks on a persistent grid.
     // GBA_NO_CHAIN=1 keeps the older sequence, one launch per band step and per closure column.
-    long long total = nseg > 1 ? nseg : 1;
+    // spine queue: the first potrf of every segment, then per column its critical tasks; bulk queue: the rest
+    long long total_spine = nseg > 1 ? nseg : 1, total_bulk = 0;
+    int spine_width = 0;
     for (int kk = 0; kk < nT; kk++) {
       const int cnt = colcnt[kk];
       const bool in_band = kk < band;
       const bool has_next = in_band ? ((kk % segT) + 1 < segT || (kk == band - 1 && band < nT)) : (kk + 1 < nT);
-      total += 4LL * cnt + (cnt > 0 ? 4 + (long long)cnt * (cnt + 1) / 2 - 1 : 0) + (has_next ? 1 : 0);
+      total_spine += (cnt > 0 ? 8 : 0) + (has_next ? 1 : 0);
+      total_bulk += cnt > 0 ? 4LL * (cnt - 1) + (long long)cnt * (cnt + 1) / 2 - 1 : 0;
     }
-    if (!getenv("GBA_NO_CHAIN") && total < (1LL << 30)) {
+    if (!getenv("GBA_NO_CHAIN") && total_bulk < (1LL << 30)) {
       CK(cudaMemsetAsync(c->upd, 0, (size_t)st.n_slots * sizeof(unsigned int), s));
-      const int grid = (int)std::min<long long>(total, (long long)c->chain_capacity);
-      k_chain<16><<<grid, 256, kSolverSmem, s>>>(p, c->sb, nseg, segT, (int)total);
+      // spine CTAs: 4 slabs in flight per independent chain (band segments run side by side), at least 8
+      spine_width = std::min(c->chain_capacity / 2, std::max(8, 4 * std::max(nseg, 1)));
+      const int n_bulk = (int)std::max<long long>(1, std::min<long long>(total_bulk, (long long)c->chain_capacity - spine_width));
+      k_chain<16><<<spine_width + n_bulk, 256, kSolverSmem, s>>>(p, c->sb, nseg, segT, (int)total_spine, (int)total_bulk,
+                                                               spine_width);
       LAUNCH_CHECK("k_chain");
     } else {
       for (int t = 0; t < (nseg > 1 ? segT : 0); t++) {
@@ -566,15 +574,12 @@ extern "C" int gba_ba_solve(gba_ctx *c) {
     }
     stage_end(c);
     stage_begin(c, GBA_STAGE_SOLVE);
-    for (int i = nT - 1; i >= band; i--) {
-      k_back_step<<<1 + rowcnt[i], 256, 0, s>>>(p, c->sb, i, 0);
-      LAUNCH_CHECK("k_back_step");
-    }
-    for (int t = (nseg > 1 ? segT : 0) - 1; t >= 0; t--) {
-      int mr = 0;
-      for (int y = 0; y < nseg; y++) mr = std::max(mr, rowcnt[t + y * segT]);
-      k_back_step<<<dim3(1 + mr, nseg), 256, 0, s>>>(p, c->sb, t, segT);
-      LAUNCH_CHECK("k_back_step");
+    {  // one launch: a task per active tile below the diagonal, plus the rows that receive no update
+      int tasks = 0;
+      for (int i = 0; i < nT; i++) tasks += rowcnt[i] + (colcnt[i] == 0 ? 1 : 0);
+      const int grid = std::max(1, std::min(tasks, 4 * c->sm_count));
+      k_back<<<grid, 256, 0, s>>>(p, c->sb, tasks);
+      LAUNCH_CHECK("k_back");
     }
   }
   k_dx_out<<<(6 * p.P + 255) / 256, 256, 0, s>>>(p, c->sb);

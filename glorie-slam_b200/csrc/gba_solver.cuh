@@ -14,6 +14,7 @@
 // The numbers are those of a dense fp64 Cholesky of the permuted matrix.
 #pragma once
 #include "gba_common.cuh"
+#include "gba_dmma.cuh"
 
 #define TS_MAXT 512  // max tile rows (6 * P <= 32768)
 #define TS_WORDS (TS_MAXT / 32)
@@ -25,6 +26,7 @@ struct SolverBufs {
   double *invL;           // [nT][NB*NB]
   int *fail;              // factorisation hit a non-positive pivot
   unsigned int *flagA, *cntB, *cntD, *flagX, *ticket;  // per-panel in-kernel synchronisation
+  unsigned int *cntY, *ticket2;  // backward substitution: updates received per rhs block, its ticket dispenser
   unsigned int *upd;      // [n_slots] slab updates a tile has received inside k_chain
 };
 
@@ -313,321 +315,57 @@ __global__ void k_pad_diag(BaParams p) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// Tile-column roles (256 threads; dynamic shared memory: 2 tiles of 64 x 65 doubles + 16 rows).
-// fp64 runs at 64 FMA/clk/SM on B200, so a 64^3 tile product pins one SM for ~9 us; the
-// trsm / syrk roles therefore work on SLAB-row slabs of a tile (SPLIT = 64 / SLAB CTAs per tile)
-// to spread a tile column over more SMs, and the potrf role keeps divisions and square roots off
-// its critical path (Newton rsqrt from an fp32 seed, blocked inverse without divisions).
+// Tile-column roles (256 threads; dynamic shared memory DM_SMEM_BYTES).  The 64 x 64 fp64 tile
+// operations run on the tensor pipe (mma.sync.m8n8k4.f64, gba_dmma.cuh); the trsm / update roles
+// work on SLAB-row slabs of a tile (SPLIT = 64 / SLAB CTAs per tile) to spread a tile column over
+// more SMs while the structure is sparse.
 // ---------------------------------------------------------------------------------------------
-typedef double (*TilePtr)[GBA_NB + 1];
-#define TILE_STRIDE (GBA_NB * (GBA_NB + 1))
-
 __device__ __forceinline__ double *rhs_ptr(const BaParams &p) { return p.sys + (size_t)p.st->n_slots * GBA_NB2; }
 
-__device__ __forceinline__ double fast_rsqrt(double d) {
-  double y = (double)rsqrtf((float)d);
-  y = y * (1.5 - 0.5 * d * y * y);
-  y = y * (1.5 - 0.5 * d * y * y);
-  return y;
-}
-
-// Copy ROWS x 64 doubles from global (L2, row stride 64) into a padded shared tile; all the
-// 128-bit loads are issued before the first store so that their latencies overlap.
-template <int ROWS>
-__device__ __forceinline__ void load_rows(TilePtr dst, const double *src) {
-  constexpr int NV = ROWS * GBA_NB / 2 / 256;  // double2 per thread
-  static_assert(NV >= 1, "tile too small");
-  double2 v[NV];
-  const int tid = threadIdx.x;
-#pragma unroll
-  for (int k = 0; k < NV; k++) v[k] = __ldcg(reinterpret_cast<const double2 *>(src) + tid + 256 * k);
-#pragma unroll
-  for (int k = 0; k < NV; k++) {
-    const int e = 2 * (tid + 256 * k);
-    dst[e >> 6][e & 63] = v[k].x;
-    dst[e >> 6][(e & 63) + 1] = v[k].y;
-  }
-}
-
-// Reciprocal for the pivot loop.  Dependent fp64 operations cost ~40 cycles each on B200 (measured
-// with clock64), so the chain is kept to seed + ONE Newton step: rcp.approx.ftz.f64 gives ~20 bits,
-// one step ~40 bits (1e-12 relative).  The trailing update therefore eliminates with a pivot that is
-// off by 1e-12 relative -- a backward error far below fp64 assembly noise; the columns of L are
-// scaled afterwards with an exact sqrt of the pivots actually used.
-__device__ __forceinline__ double fast_rcp(double d) {
-  double r;
-  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
-  const double e = fma(-d, r, 1.0);
-  return fma(r, e, r);
-}
-
-// Cholesky of the diagonal tile, its inverse, and the forward substitution y_kk = inv(L_kk) b_kk.
-// The tile lives in REGISTERS (thread (ty,tx) owns elements (ty+16u, tx+16v)); per pivot only
-// column j goes through shared memory (double buffered, one barrier per pivot).  The pivot loop is
-// latency bound, so its dependent chain is kept short: the update uses the UNSCALED column and
-// 1/d (Newton from an fp32 seed), is applied to all 16 owned elements without predicates (elements
-// of finished rows/columns are dead, updating them is harmless), the owner of the next column is
-// known at compile time, and the sqrt scaling of the columns happens after the loop.
+// Cholesky of the diagonal tile: inverse of its factor into invL[kk] (the factor itself is never needed
+// again: the solves and substitutions use the inverse), forward substitution y_kk = inv(L_kk) b_kk.
+// A pivot that is not positive and finite raises the failure flag (SimplicialLLT: NumericalIssue).
 __device__ void role_potrf(const BaParams &p, const SolverBufs &sb, int kk, double *s_buf) {
-  TilePtr Lo = reinterpret_cast<TilePtr>(s_buf);
-  TilePtr X = reinterpret_cast<TilePtr>(s_buf + TILE_STRIDE);
-  TilePtr Tm = reinterpret_cast<TilePtr>(s_buf + 2 * TILE_STRIDE);
-  __shared__ int s_bad;
-  __shared__ double s_v[GBA_NB], s_rd[GBA_NB], s_dinv[GBA_NB], s_col[2][2][GBA_NB];
-  const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
-  double *T = p.sys + (size_t)p.tslot[kk * p.nT + kk] * GBA_NB2;
-  if (tid == 0) s_bad = 0;
-  double *b = rhs_ptr(p) + kk * GBA_NB;
-  const double b_pre = (tid < GBA_NB) ? __ldcg(b + tid) : 0.0;  // rhs block, needed only at the end
-  double a[4][4];
-#pragma unroll
-  for (int u = 0; u < 4; u++)
-#pragma unroll
-    for (int v = 0; v < 4; v++) {
-      const int r = ty + 16 * u, c = tx + 16 * v;
-      a[u][v] = (c <= r) ? __ldcg(T + r * GBA_NB + c) : 0.0;
-    }
-  for (int i = tid; i < GBA_NB * (GBA_NB + 1); i += 256) {
-    (&Lo[0][0])[i] = 0.0;
-    (&X[0][0])[i] = 0.0;
-  }
-  // Two pivots per barrier.  The owners publish columns j and j+1 as they stand after pivots < j;
-  // every thread derives the pivot-j update of column j+1 itself (B' = B - A * A[j+1] / d0) and
-  // applies both rank-1 updates.  1/d1 = d0 / (d0 * B[j+1] - A[j+1]^2) does not wait for 1/d0.
-  if (tx < 2) {  // columns 0, 1 -> buffer 0
-#pragma unroll
-    for (int u = 0; u < 4; u++) s_col[0][tx][ty + 16 * u] = a[u][0];
-  }
-  __syncthreads();
-  bool bad = false;
-#pragma unroll
-  for (int v0 = 0; v0 < 4; v0++) {  // columns 16 v0 .. 16 v0 + 15
-    for (int jj = 0; jj < 16; jj += 2) {
-      const int j = 16 * v0 + jj;
-      const double *cA = s_col[(j >> 1) & 1][0], *cB = s_col[(j >> 1) & 1][1];
-      const double d0 = cA[j], e = cA[j + 1], f = cB[j + 1];
-      // rows / columns below 16 v0 are finished: only the sub-blocks u, v >= v0 are still live
-      double arA[4], acA[4], arB[4], acB[4];
-#pragma unroll
-      for (int u = v0; u < 4; u++) {
-        arA[u] = cA[ty + 16 * u];
-        acA[u] = cA[tx + 16 * u];
-        arB[u] = cB[ty + 16 * u];
-        acB[u] = cB[tx + 16 * u];
-      }
-      const double lA = (tid < GBA_NB) ? cA[tid] : 0.0, lB = (tid < GBA_NB) ? cB[tid] : 0.0;
-      const double t = fma(d0, f, -e * e);  // d0 * d1
-      const double dinv0 = fast_rcp(d0), rt = fast_rcp(t);
-      const double m = e * dinv0;           // L[j+1][j] / L[j][j], unscaled form
-      const double d1 = fma(-e, m, f);
-      const double dinv1 = d0 * rt;
-      if (!(d0 > 0.0) || isinf(d0) || !(d1 > 0.0) || isinf(d1)) bad = true;  // SimplicialLLT: NumericalIssue
-#pragma unroll
-      for (int u = v0; u < 4; u++) {
-        arB[u] = fma(-arA[u], m, arB[u]);
-        acB[u] = fma(-acA[u], m, acB[u]);
-      }
-      if (tid < GBA_NB) {  // unscaled columns of L, scaled after the loop
-        Lo[tid][j] = (tid >= j) ? lA : 0.0;
-        Lo[tid][j + 1] = (tid >= j + 1) ? fma(-lA, m, lB) : 0.0;
-      }
-      if (tid == 0) {  // the pivots themselves; exact scaling after the loop
-        s_dinv[j] = d0;
-        s_dinv[j + 1] = d1;
-      }
-#pragma unroll
-      for (int u = v0; u < 4; u++) {
-        const double ra = arA[u] * dinv0, rb = arB[u] * dinv1;
-#pragma unroll
-        for (int v = v0; v < 4; v++) a[u][v] = fma(-rb, acB[v], fma(-ra, acA[v], a[u][v]));
-      }
-      // owners of columns j+2, j+3 publish them into the other buffer
-      if (jj < 14) {
-        if (tx == jj + 2 || tx == jj + 3) {
-#pragma unroll
-          for (int u = 0; u < 4; u++) s_col[((j >> 1) + 1) & 1][tx - jj - 2][ty + 16 * u] = a[u][v0];
-        }
-      } else if (v0 < 3) {
-        if (tx < 2) {
-#pragma unroll
-          for (int u = 0; u < 4; u++) s_col[((j >> 1) + 1) & 1][tx][ty + 16 * u] = a[u][(v0 + 1) & 3];
-        }
-      }
-      __syncthreads();
-    }
-  }
-  if (bad && tid == 0) s_bad = 1;
-  __syncthreads();
-  if (s_bad) {
-    if (tid == 0) *sb.fail = 1;
-    return;
-  }
-  // scale the columns: L[:,j] = col_j / sqrt(d_j);  s_rd[j] = 1 / L[j][j] = sqrt(dinv_j)
-  if (tid < GBA_NB) s_rd[tid] = rsqrt(s_dinv[tid]);
-  __syncthreads();
-  for (int i = tid; i < GBA_NB2; i += 256) {
-    const int r = i >> 6, c = i & 63;
-    Lo[r][c] *= s_rd[c];
-  }
-  __syncthreads();
-  // ---- X = inv(L), blocked by 16 -----------------------------------------------------------
-  // level 0: the four 16x16 diagonal blocks.  One thread per column, right-looking with the
-  // column's 16 partial results in registers: per step one multiply and 15 INDEPENDENT fmas,
-  // instead of a dot product whose dependent chain grows with the row.
-  if (tid < GBA_NB) {
-    const int c = tid, base = (c >> 4) * 16, cc = c - base;
-    double acc[16];
-#pragma unroll
-    for (int i = 0; i < 16; i++) acc[i] = (i == cc) ? 1.0 : 0.0;
-#pragma unroll
-    for (int j = 0; j < 16; j++) {
-      const double xj = acc[j] * s_rd[base + j];
-      X[base + j][c] = xj;
-#pragma unroll
-      for (int i = j + 1; i < 16; i++) acc[i] = fma(-Lo[base + i][base + j], xj, acc[i]);
-    }
-  }
-  __syncthreads();
-  // block rows I = 1..3: T[I][J] = sum_{K=J}^{I-1} L[I][K] X[K][J];  X[I][J] = -X[I][I] T[I][J].
-  // Each thread owns up to 3 outputs (same row-in-block rr, columns cl, cl+16, cl+32) and advances
-  // them together with 2 partial sums each, so that 6 independent fma chains are in flight.
-#pragma unroll
-  for (int I = 1; I < 4; I++) {
-    const int rr = tid >> 4, cl = tid & 15, r = 16 * I + rr;
-    double s0[3] = {0.0, 0.0, 0.0}, s1[3] = {0.0, 0.0, 0.0}, s2[3] = {0.0, 0.0, 0.0}, s3[3] = {0.0, 0.0, 0.0};
-#pragma unroll 2
-    for (int m = 0; m < 16 * I; m += 4) {
-      const double l0 = Lo[r][m], l1 = Lo[r][m + 1], l2 = Lo[r][m + 2], l3 = Lo[r][m + 3];
-#pragma unroll
-      for (int q = 0; q < 3; q++)
-        if (q < I) {  // X[m][c] is zero above its block's diagonal, so starting at m = 0 is harmless
-          s0[q] = fma(l0, X[m][cl + 16 * q], s0[q]);
-          s1[q] = fma(l1, X[m + 1][cl + 16 * q], s1[q]);
-          s2[q] = fma(l2, X[m + 2][cl + 16 * q], s2[q]);
-          s3[q] = fma(l3, X[m + 3][cl + 16 * q], s3[q]);
-        }
-    }
-#pragma unroll
-    for (int q = 0; q < 3; q++)
-      if (q < I) Tm[rr][cl + 16 * q] = (s0[q] + s1[q]) + (s2[q] + s3[q]);
-    __syncthreads();
-    double t0[3] = {0.0, 0.0, 0.0}, t1[3] = {0.0, 0.0, 0.0}, t2[3] = {0.0, 0.0, 0.0}, t3[3] = {0.0, 0.0, 0.0};
-#pragma unroll
-    for (int m = 0; m < 16; m += 4) {  // X[I][I] is lower triangular: entries right of the diagonal are 0
-      const double x0 = X[r][16 * I + m], x1 = X[r][16 * I + m + 1], x2 = X[r][16 * I + m + 2],
-                   x3 = X[r][16 * I + m + 3];
-#pragma unroll
-      for (int q = 0; q < 3; q++)
-        if (q < I) {
-          t0[q] = fma(x0, Tm[m][cl + 16 * q], t0[q]);
-          t1[q] = fma(x1, Tm[m + 1][cl + 16 * q], t1[q]);
-          t2[q] = fma(x2, Tm[m + 2][cl + 16 * q], t2[q]);
-          t3[q] = fma(x3, Tm[m + 3][cl + 16 * q], t3[q]);
-        }
-    }
-    __syncthreads();
-#pragma unroll
-    for (int q = 0; q < 3; q++)
-      if (q < I) X[r][cl + 16 * q] = -((t0[q] + t1[q]) + (t2[q] + t3[q]));
-    __syncthreads();
-  }
-  double *XI = sb.invL + (size_t)kk * GBA_NB2;
-  for (int i = tid; i < GBA_NB2; i += 256) {
-    const int r = i >> 6, c = i & 63;
-    T[i] = Lo[r][c];
-    XI[i] = X[r][c];
-  }
-  // forward substitution of the rhs block
-  if (tid < GBA_NB) s_v[tid] = b_pre;
-  __syncthreads();
-  {
-    const int row = tid >> 2, part = tid & 3;
-    double sa = 0.0, sb_ = 0.0, sc = 0.0, sd = 0.0;
-#pragma unroll
-    for (int m = part * 16; m < part * 16 + 16; m += 4) {
-      sa = fma(X[row][m], s_v[m], sa);
-      sb_ = fma(X[row][m + 1], s_v[m + 1], sb_);
-      sc = fma(X[row][m + 2], s_v[m + 2], sc);
-      sd = fma(X[row][m + 3], s_v[m + 3], sd);
-    }
-    double s = (sa + sb_) + (sc + sd);
-    s += __shfl_xor_sync(0xffffffffu, s, 1);
-    s += __shfl_xor_sync(0xffffffffu, s, 2);
-    if (part == 0) b[row] = s;
-  }
+  DmPotrfSmem &s = *reinterpret_cast<DmPotrfSmem *>(s_buf);
+  const double *T = p.sys + (size_t)p.tslot[kk * p.nT + kk] * GBA_NB2;
+  const bool ok = dm_potrf64(T, sb.invL + (size_t)kk * GBA_NB2, rhs_ptr(p) + kk * GBA_NB, s);
+  if (!ok && threadIdx.x == 0) *sb.fail = 1;
 }
 
 // Rows [q*SLAB, (q+1)*SLAB) of L[i,kk] = A[i,kk] * inv(L_kk)^T, then b_i -= L[i,kk] y_kk there.
-// Thread (ty, tx) computes outputs (ty + 16u, tx + 16v): a warp then reads 16 consecutive rows of
-// the 65-double-pitch tile per operand, which is bank-conflict free for 8-byte words.
 template <int SLAB>
 __device__ void role_trsm(const BaParams &p, const SolverBufs &sb, int kk, int a, int q, int atomic_from,
                           double *s_buf) {
-  TilePtr X = reinterpret_cast<TilePtr>(s_buf);
-  TilePtr A = reinterpret_cast<TilePtr>(s_buf + TILE_STRIDE);
-  __shared__ double s_y[GBA_NB];
-  constexpr int RPT = SLAB / 16;  // rows per thread
-  const int i = sb.colrows[kk * p.nT + a], tid = threadIdx.x, rb = q * SLAB, ty = tid >> 4, tx = tid & 15;
-  double *T = p.sys + (size_t)p.tslot[i * p.nT + kk] * GBA_NB2 + rb * GBA_NB;
-  load_rows<GBA_NB>(X, sb.invL + (size_t)kk * GBA_NB2);
-  load_rows<SLAB>(A, T);
-  if (tid < GBA_NB) s_y[tid] = __ldcg(rhs_ptr(p) + kk * GBA_NB + tid);
+  DmSlabSmem &s = *reinterpret_cast<DmSlabSmem *>(s_buf);
+  constexpr int RB = SLAB / 8;
+  const int i = sb.colrows[kk * p.nT + a], tid = threadIdx.x, lane = tid & 31, w = tid >> 5, rb0 = q * SLAB;
+  const int g = lane >> 2, t = lane & 3;
+  double *T = p.sys + (size_t)p.tslot[i * p.nT + kk] * GBA_NB2 + rb0 * GBA_NB;
+  dm_load_rows<GBA_NB>(s.B, sb.invL + (size_t)kk * GBA_NB2);
+  dm_load_rows<SLAB>(s.A, T);
+  if (tid < GBA_NB) s.y[tid] = __ldcg(rhs_ptr(p) + kk * GBA_NB + tid);
   __syncthreads();
-  // KS interleaved partial sums per output keep >= 16 independent fp64 fma chains per thread
-  constexpr int KS = (RPT >= 4) ? 1 : 4 / RPT;
-  double part_[KS][RPT][4] = {};
-#pragma unroll 4
-  for (int m = 0; m < GBA_NB; m += KS) {
+  double acc[RB][2];
 #pragma unroll
-    for (int ks = 0; ks < KS; ks++) {
-      double av[RPT], xv[4];
+  for (int rb = 0; rb < RB; rb++) acc[rb][0] = acc[rb][1] = 0.0;
+  dm_slab_nt<RB>(acc, s, w, 8 * (w + 1), lane);  // inv(L) is lower triangular: row c ends at column c
+  const double y0 = s.y[8 * w + 2 * t], y1 = s.y[8 * w + 2 * t + 1];
 #pragma unroll
-      for (int u = 0; u < RPT; u++) av[u] = A[ty + 16 * u][m + ks];
-#pragma unroll
-      for (int v = 0; v < 4; v++) xv[v] = X[tx + 16 * v][m + ks];
-#pragma unroll
-      for (int u = 0; u < RPT; u++)
-#pragma unroll
-        for (int v = 0; v < 4; v++) part_[ks][u][v] = fma(av[u], xv[v], part_[ks][u][v]);
-    }
+  for (int rb = 0; rb < RB; rb++) {
+    *reinterpret_cast<double2 *>(T + (8 * rb + g) * GBA_NB + 8 * w + 2 * t) = make_double2(acc[rb][0], acc[rb][1]);
+    double v = fma(acc[rb][0], y0, acc[rb][1] * y1);  // this warp's 8 columns of (L y)[row]
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    if (t == 0) s.part[w][8 * rb + g] = v;
   }
-  double acc[RPT][4];
-#pragma unroll
-  for (int u = 0; u < RPT; u++)
-#pragma unroll
-    for (int v = 0; v < 4; v++) {
-      double t_ = part_[0][u][v];
-#pragma unroll
-      for (int ks = 1; ks < KS; ks++) t_ += part_[ks][u][v];
-      acc[u][v] = t_;
-    }
   __syncthreads();
+  if (tid < SLAB) {
+    double v = 0.0;
 #pragma unroll
-  for (int u = 0; u < RPT; u++)
-#pragma unroll
-    for (int v = 0; v < 4; v++) {
-      T[(ty + 16 * u) * GBA_NB + tx + 16 * v] = acc[u][v];
-      A[ty + 16 * u][tx + 16 * v] = acc[u][v];
-    }
-  __syncthreads();
-  if (tid < SLAB * 4) {
-    const int row = tid >> 2, part = tid & 3;
-    double sa = 0.0, sb_ = 0.0, sc = 0.0, sd = 0.0;
-#pragma unroll
-    for (int m = part * 16; m < part * 16 + 16; m += 4) {
-      sa = fma(A[row][m], s_y[m], sa);
-      sb_ = fma(A[row][m + 1], s_y[m + 1], sb_);
-      sc = fma(A[row][m + 2], s_y[m + 2], sc);
-      sd = fma(A[row][m + 3], s_y[m + 3], sd);
-    }
-    double s = (sa + sb_) + (sc + sd);
-    s += __shfl_xor_sync(0xffffffffu, s, 1);
-    s += __shfl_xor_sync(0xffffffffu, s, 2);
-    if (part == 0) {
-      // closure rows are updated by several band segments at once
-      if (i >= atomic_from) atomicAdd(&rhs_ptr(p)[i * GBA_NB + rb + row], -s);
-      else rhs_ptr(p)[i * GBA_NB + rb + row] -= s;
-    }
+    for (int ww = 0; ww < 8; ww++) v += s.part[ww][tid];
+    // closure rows are updated by several band segments at once
+    if (i >= atomic_from) atomicAdd(&rhs_ptr(p)[i * GBA_NB + rb0 + tid], -v);
+    else rhs_ptr(p)[i * GBA_NB + rb0 + tid] -= v;
   }
 }
 
@@ -635,59 +373,38 @@ __device__ void role_trsm(const BaParams &p, const SolverBufs &sb, int kk, int a
 template <int SLAB>
 __device__ void role_syrk(const BaParams &p, const SolverBufs &sb, int kk, int a, int b, int q, int atomic_from,
                           double *s_buf) {
-  TilePtr B = reinterpret_cast<TilePtr>(s_buf);
-  TilePtr A = reinterpret_cast<TilePtr>(s_buf + TILE_STRIDE);
-  constexpr int RPT = SLAB / 16;
-  const int i = sb.colrows[kk * p.nT + a], j = sb.colrows[kk * p.nT + b], tid = threadIdx.x, rb = q * SLAB;
-  const int ty = tid >> 4, tx = tid & 15;
-  const double *Li = p.sys + (size_t)p.tslot[i * p.nT + kk] * GBA_NB2 + rb * GBA_NB;
+  DmSlabSmem &s = *reinterpret_cast<DmSlabSmem *>(s_buf);
+  constexpr int RB = SLAB / 8;
+  const int i = sb.colrows[kk * p.nT + a], j = sb.colrows[kk * p.nT + b], tid = threadIdx.x, rb0 = q * SLAB;
+  const int lane = tid & 31, w = tid >> 5, g = lane >> 2, t = lane & 3;
+  const double *Li = p.sys + (size_t)p.tslot[i * p.nT + kk] * GBA_NB2 + rb0 * GBA_NB;
   const double *Lj = p.sys + (size_t)p.tslot[j * p.nT + kk] * GBA_NB2;
-  double *T = p.sys + (size_t)p.tslot[i * p.nT + j] * GBA_NB2 + rb * GBA_NB;
-  load_rows<GBA_NB>(B, Lj);
-  load_rows<SLAB>(A, Li);
+  double *T = p.sys + (size_t)p.tslot[i * p.nT + j] * GBA_NB2 + rb0 * GBA_NB;
+  dm_load_rows<GBA_NB>(s.B, Lj);
+  dm_load_rows<SLAB>(s.A, Li);
   // the target values are fetched now so that their latency hides behind the product; tiles of
   // the closure block are shared by concurrently factorised band segments -> atomic adds instead
   const bool shared_tile = j >= atomic_from;
-  double t[RPT][4];
+  double2 tv[RB];
 #pragma unroll
-  for (int u = 0; u < RPT; u++)
-#pragma unroll
-    for (int v = 0; v < 4; v++) t[u][v] = shared_tile ? 0.0 : __ldcg(T + (ty + 16 * u) * GBA_NB + tx + 16 * v);
+  for (int rb = 0; rb < RB; rb++)
+    tv[rb] = shared_tile ? make_double2(0.0, 0.0)
+                         : __ldcg(reinterpret_cast<const double2 *>(T + (8 * rb + g) * GBA_NB + 8 * w + 2 * t));
   __syncthreads();
-  constexpr int KS = (RPT >= 4) ? 1 : 4 / RPT;
-  double part_[KS][RPT][4] = {};
-#pragma unroll 4
-  for (int m = 0; m < GBA_NB; m += KS) {
+  double acc[RB][2];
 #pragma unroll
-    for (int ks = 0; ks < KS; ks++) {
-      double x[RPT], y[4];
+  for (int rb = 0; rb < RB; rb++) acc[rb][0] = acc[rb][1] = 0.0;
+  dm_slab_nt<RB>(acc, s, w, GBA_NB, lane);
 #pragma unroll
-      for (int u = 0; u < RPT; u++) x[u] = A[ty + 16 * u][m + ks];
-#pragma unroll
-      for (int v = 0; v < 4; v++) y[v] = B[tx + 16 * v][m + ks];
-#pragma unroll
-      for (int u = 0; u < RPT; u++)
-#pragma unroll
-        for (int v = 0; v < 4; v++) part_[ks][u][v] = fma(x[u], y[v], part_[ks][u][v]);
+  for (int rb = 0; rb < RB; rb++) {
+    double *dst = T + (8 * rb + g) * GBA_NB + 8 * w + 2 * t;
+    if (shared_tile) {
+      atomicAdd(dst, -acc[rb][0]);
+      atomicAdd(dst + 1, -acc[rb][1]);
+    } else {
+      *reinterpret_cast<double2 *>(dst) = make_double2(tv[rb].x - acc[rb][0], tv[rb].y - acc[rb][1]);
     }
   }
-  double acc[RPT][4];
-#pragma unroll
-  for (int u = 0; u < RPT; u++)
-#pragma unroll
-    for (int v = 0; v < 4; v++) {
-      double t_ = part_[0][u][v];
-#pragma unroll
-      for (int ks = 1; ks < KS; ks++) t_ += part_[ks][u][v];
-      acc[u][v] = t_;
-    }
-#pragma unroll
-  for (int u = 0; u < RPT; u++)
-#pragma unroll
-    for (int v = 0; v < 4; v++) {
-      if (shared_tile) atomicAdd(&T[(ty + 16 * u) * GBA_NB + tx + 16 * v], -acc[u][v]);
-      else T[(ty + 16 * u) * GBA_NB + tx + 16 * v] = t[u][v] - acc[u][v];
-    }
 }
 
 __device__ __forceinline__ unsigned ld_acquire(const unsigned *p) {
@@ -815,7 +532,8 @@ __device__ __forceinline__ void chain_wait(const unsigned *ptr, unsigned target,
 }
 
 template <int SLAB>
-__global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int nseg, int segT, int total) {
+__global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int nseg, int segT, int total_spine,
+                                               int total_bulk, int n_spine) {
   extern __shared__ double s_buf[];
   constexpr int SPLIT = GBA_NB / SLAB;
   __shared__ int s_task[5];  // role, kk, a, b, q
@@ -823,6 +541,15 @@ __global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int ns
   const int tid = threadIdx.x, nT = p.st->n_tiles;
   const int band = nseg > 1 ? nseg * segT : 0, ninit = nseg > 1 ? nseg : 1;
   const int atomic_from = nseg > 1 ? band : (1 << 30);
+  // Two ticket queues.  SPINE: the tasks every following column waits for -- P(k), the solve of the tile below
+  // the diagonal and the update of the next diagonal tile -- served by the first n_spine CTAs only, so that
+  // they never queue behind a wave of bulk updates.  BULK: everything else.  Inside each queue tickets are
+  // handed out in sequence order; a waiting task only waits for tasks that precede it in the combined order,
+  // and the earliest unfinished task of the combined order is always the head of its own queue, hence taken
+  // and runnable: no deadlock for any grid size >= n_spine + 1.
+  const bool spine = (int)blockIdx.x < n_spine;
+  unsigned *ticket = spine ? &sb.ticket[0] : &sb.ticket[1];
+  const int total = spine ? total_spine : total_bulk;
   auto seq = [&](int s_) { return s_ < band ? (s_ % nseg) * segT + s_ / nseg : s_; };
   auto next_of = [&](int s_, int kk_) {  // column whose potrf is issued inside block(kk_), or -1
     if (s_ < band) {
@@ -831,41 +558,41 @@ __global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int ns
     }
     return kk_ + 1 < nT ? kk_ + 1 : -1;
   };
-  int spos = 0, base = ninit;  // sequence position and first ticket of its block (thread 0 only)
+  int spos = 0, base = spine ? ninit : 0;  // sequence position and first ticket of its block (thread 0 only)
   for (;;) {
     __syncthreads();  // the previous task's shared memory is dead
     if (tid == 0) {
-      const int t = (int)atomicAdd(&sb.ticket[0], 1u);
+      const int t = (int)atomicAdd(ticket, 1u);
       int role = -1, kk = 0, a = 0, b = 0, q = 0;
-      if (t < ninit) {
+      if (spine && t < ninit) {
         role = 0;
         kk = nseg > 1 ? t * segT : 0;
       } else if (t < total) {
         for (;;) {  // tickets only grow: the walk over the sequence is amortised
           const int col = seq(spos), nx = next_of(spos, col);
           const int cnt = sb.colcnt[col], pairs = cnt * (cnt + 1) / 2, nxt = nx >= 0 ? 1 : 0;
-          const int n = SPLIT * cnt + (cnt > 0 ? SPLIT + pairs - 1 : 0) + nxt;
+          // spine block(k): T(k, 0, *)  S(k, pair 0, *)  P(next(k));  bulk block(k): T(k, a >= 1, *)  S(k, other pairs)
+          const int n = spine ? (cnt > 0 ? 2 * SPLIT : 0) + nxt : (cnt > 0 ? SPLIT * (cnt - 1) + pairs - 1 : 0);
           if (t < base + n) {
             int o = t - base;
             kk = col;
-            if (o < SPLIT * cnt) {
-              role = 1; a = o / SPLIT; q = o % SPLIT;
-            } else {
-              o -= SPLIT * cnt;
+            if (spine) {
               if (cnt > 0 && o < SPLIT) {
-                role = 2; a = 0; b = 0; q = o;
+                role = 1; a = 0; q = o;
+              } else if (cnt > 0 && o < 2 * SPLIT) {
+                role = 2; a = 0; b = 0; q = o - SPLIT;
               } else {
-                if (cnt > 0) o -= SPLIT;
-                if (nxt && o == 0) {
-                  role = 0; kk = nx;
-                } else {
-                  o -= nxt;
-                  int pr = 1 + o;  // whole-tile update
-                  a = 0;
-                  while (pr > a) { pr -= a + 1; a++; }
-                  b = pr;
-                  role = 3;
-                }
+                role = 0; kk = nx;
+              }
+            } else {
+              if (o < SPLIT * (cnt - 1)) {
+                role = 1; a = 1 + o / SPLIT; q = o % SPLIT;
+              } else {
+                int pr = 1 + (o - SPLIT * (cnt - 1));  // whole-tile update, pairs 1 .. pairs-1
+                a = 0;
+                while (pr > a) { pr -= a + 1; a++; }
+                b = pr;
+                role = 3;
               }
             }
             break;
@@ -959,22 +686,95 @@ __global__ void __launch_bounds__(256) k_syrk(BaParams p, SolverBufs sb, int kk)
 }
 
 // ---------------------------------------------------------------------------------------------
-// Backward substitution, one launch per tile row i (from the last to the first): CTA 0 computes
-// x_i = inv(L_i)^T y_i, the others push y_k -= L[i,k]^T x_i to the active tiles of row i.
+// Backward substitution L^T x = y in ONE launch: a task per active tile (i, k), k < i, handed out by
+// ticket in order of descending tile row i.  Task (i, k) waits for x_i (flagX[i]), subtracts
+// L[i,k]^T x_i from y_k (fp64 atomics: rows that do not touch each other update the same block
+// concurrently) and counts itself into cntY[k]; whoever delivers the LAST update of y_k computes
+// x_k = inv(L_k)^T y_k on the spot and raises flagX[k] -- one hop per tile row on the critical path.
+// Rows that receive no update (no active tile below their diagonal tile: the last row) are seeded
+// by the first tickets.  Every wait is for a task with a smaller ticket (rows > i come first), so
+// the kernel cannot deadlock whatever the grid size; the watchdog of k_chain applies.
+// Replaces solver.solve(b)'s backward half (droid_kernels.cu:1203) and 37 launches per iteration.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_back_step(BaParams p, SolverBufs sb, int i0, int i_stride) {
-  __shared__ double s_x[GBA_NB], s_part[4][GBA_NB];
-  // thread = (column of the tile, quarter of its rows): lanes run over columns -> coalesced
-  const int b = blockIdx.x, tid = threadIdx.x, col = tid & 63, part = tid >> 6;
-  const int i = i0 + blockIdx.y * i_stride;  // blockIdx.y = band segment
+__device__ __forceinline__ void back_solve_x(const BaParams &p, const SolverBufs &sb, int i, const double (&xi)[16],
+                                             double *s_x, double (*s_part)[GBA_NB]) {
+  // x_i = inv(L_i)^T y_i; thread = (column col of inv(L), quarter `part` of its rows), xi = its slice of inv(L_i)
+  const int tid = threadIdx.x, col = tid & 63, part = tid >> 6;
   double *rhs = rhs_ptr(p);
-  if (__ldcg(sb.fail)) return;
-  if (b == 0) {
-    const double *XI = sb.invL + (size_t)i * GBA_NB2;
-    double l[16];
+  if (tid < GBA_NB) s_x[tid] = __ldcg(rhs + i * GBA_NB + tid);
+  __syncthreads();
+  double sa = 0.0, sb_ = 0.0, sc = 0.0, sd = 0.0;
 #pragma unroll
-    for (int m = 0; m < 16; m++) l[m] = __ldcg(XI + (part * 16 + m) * GBA_NB + col);
-    if (tid < GBA_NB) s_x[tid] = __ldcg(rhs + i * GBA_NB + tid);
+  for (int m = 0; m < 16; m += 4) {
+    sa = fma(xi[m], s_x[part * 16 + m], sa);
+    sb_ = fma(xi[m + 1], s_x[part * 16 + m + 1], sb_);
+    sc = fma(xi[m + 2], s_x[part * 16 + m + 2], sc);
+    sd = fma(xi[m + 3], s_x[part * 16 + m + 3], sd);
+  }
+  s_part[part][col] = (sa + sb_) + (sc + sd);
+  __syncthreads();
+  if (tid < GBA_NB) rhs[i * GBA_NB + tid] = s_part[0][tid] + s_part[1][tid] + s_part[2][tid] + s_part[3][tid];
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) atomicExch(&sb.flagX[i], 1u);
+}
+
+__global__ void __launch_bounds__(256) k_back(BaParams p, SolverBufs sb, int total) {
+  __shared__ double s_x[GBA_NB], s_part[4][GBA_NB];
+  __shared__ int s_task[3];  // role (0 seed, 1 tile, -1 done), i, k
+  const int tid = threadIdx.x, col = tid & 63, part = tid >> 6, nT = p.st->n_tiles;
+  if (__ldcg(sb.fail)) return;
+  int row = nT - 1, base = 0, nseed = -1;  // thread 0: walk over the rows, amortised (tickets only grow)
+  for (;;) {
+    __syncthreads();
+    if (tid == 0) {
+      const int tk = (int)atomicAdd(sb.ticket2, 1u);
+      int role = -1, i = 0, k = 0;
+      if (nseed < 0) {
+        nseed = 0;
+        for (int r = 0; r < nT; r++) nseed += (sb.colcnt[r] == 0);
+        base = nseed;
+      }
+      if (tk < nseed) {  // the tk-th row (from the end) without updates
+        int seen = 0;
+        for (int r = nT - 1; r >= 0; r--)
+          if (sb.colcnt[r] == 0 && seen++ == tk) {
+            role = 0;
+            i = r;
+            break;
+          }
+      } else if (tk < total) {
+        while (row >= 0 && tk >= base + sb.rowcnt[row]) base += sb.rowcnt[row--];
+        if (row >= 0) {
+          role = 1;
+          i = row;
+          k = sb.rowcols[row * p.nT + (tk - base)];
+        }
+      }
+      s_task[0] = role; s_task[1] = i; s_task[2] = k;
+    }
+    __syncthreads();
+    const int role = s_task[0], i = s_task[1], k = s_task[2];
+    if (role < 0) return;
+    double l[16];
+    if (role == 0) {
+      const double *XI = sb.invL + (size_t)i * GBA_NB2;
+#pragma unroll
+      for (int m = 0; m < 16; m++) l[m] = __ldcg(XI + (part * 16 + m) * GBA_NB + col);
+      back_solve_x(p, sb, i, l, s_x, s_part);
+      continue;
+    }
+    // this thread's slices of L[i,k] and of inv(L_k), requested before the wait
+    const double *L = p.sys + (size_t)p.tslot[i * p.nT + k] * GBA_NB2, *XK = sb.invL + (size_t)k * GBA_NB2;
+    double xk[16];
+#pragma unroll
+    for (int m = 0; m < 16; m++) l[m] = __ldcg(L + (part * 16 + m) * GBA_NB + col);
+#pragma unroll
+    for (int m = 0; m < 16; m++) xk[m] = __ldcg(XK + (part * 16 + m) * GBA_NB + col);
+    if (tid == 0) chain_wait(&sb.flagX[i], 1u, sb.fail);
+    __syncthreads();
+    if (__ldcg(sb.fail)) return;
+    if (tid < GBA_NB) s_x[tid] = __ldcg(rhs_ptr(p) + i * GBA_NB + tid);
     __syncthreads();
     double sa = 0.0, sb_ = 0.0, sc = 0.0, sd = 0.0;
 #pragma unroll
@@ -986,35 +786,17 @@ __global__ void __launch_bounds__(256) k_back_step(BaParams p, SolverBufs sb, in
     }
     s_part[part][col] = (sa + sb_) + (sc + sd);
     __syncthreads();
-    if (tid < GBA_NB) rhs[i * GBA_NB + tid] = s_part[0][tid] + s_part[1][tid] + s_part[2][tid] + s_part[3][tid];
+    if (tid < GBA_NB)
+      atomicAdd(rhs_ptr(p) + k * GBA_NB + tid, -(s_part[0][tid] + s_part[1][tid] + s_part[2][tid] + s_part[3][tid]));
     __threadfence();
     __syncthreads();
-    if (tid == 0) atomicExch(&sb.flagX[i], 1u);
-    return;
+    if (tid == 0) s_task[0] = (atomicAdd(&sb.cntY[k], 1u) == (unsigned)(sb.colcnt[k] - 1));
+    __syncthreads();
+    if (s_task[0]) {  // y_k is complete
+      __threadfence();
+      back_solve_x(p, sb, k, xk, s_x, s_part);
+    }
   }
-  if (b - 1 >= sb.rowcnt[i]) return;
-  const int k = sb.rowcols[i * p.nT + b - 1];
-  const double *L = p.sys + (size_t)p.tslot[i * p.nT + k] * GBA_NB2;
-  // prefetch this thread's slice of the tile while waiting for x_i
-  double l[16];
-#pragma unroll
-  for (int m = 0; m < 16; m++) l[m] = __ldcg(L + (part * 16 + m) * GBA_NB + col);
-  if (tid == 0)
-    while (ld_acquire(&sb.flagX[i]) == 0u) __nanosleep(20);
-  __syncthreads();
-  if (tid < GBA_NB) s_x[tid] = __ldcg(rhs + i * GBA_NB + tid);
-  __syncthreads();
-  double sa = 0.0, sb_ = 0.0, sc = 0.0, sd = 0.0;
-#pragma unroll
-  for (int m = 0; m < 16; m += 4) {
-    sa = fma(l[m], s_x[part * 16 + m], sa);
-    sb_ = fma(l[m + 1], s_x[part * 16 + m + 1], sb_);
-    sc = fma(l[m + 2], s_x[part * 16 + m + 2], sc);
-    sd = fma(l[m + 3], s_x[part * 16 + m + 3], sd);
-  }
-  s_part[part][col] = (sa + sb_) + (sc + sd);
-  __syncthreads();
-  if (tid < GBA_NB) rhs[k * GBA_NB + tid] -= s_part[0][tid] + s_part[1][tid] + s_part[2][tid] + s_part[3][tid];
 }
 
 // dx = (float) x in the caller's pose order, or zero when the factorisation failed

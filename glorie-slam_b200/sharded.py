@@ -21,6 +21,21 @@ import torch.distributed as dist
 import _gba
 
 
+# optional device timing of the two exchanges (bench.py): {"allreduce": [(ev0, ev1), ...], "merge": [...]}
+TIMERS = None
+
+
+def _timed(name, fn):
+    if TIMERS is None:
+        return fn()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    out = fn()
+    b.record()
+    TIMERS.setdefault(name, []).append((a, b))
+    return out
+
+
 def frame_list(ii, t0, t1):
     """Sorted depth keyframes kx = unique([t0,t1) U ii) (reference droid_kernels.cu:1337-1345)."""
     ii = np.asarray(ii, dtype=np.int64)
@@ -97,9 +112,13 @@ def ba_sharded(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, 
         view = _gba.system_view(ctx, dev)
         for _ in range(int(iterations)):
             _gba.check(ctx, L.gba_ba_build(ctx))
-            allreduce_system(view, group)
+            _timed("allreduce", lambda: allreduce_system(view, group))
             _gba.check(ctx, L.gba_ba_solve(ctx))
         _gba.check(ctx, L.gba_ba_end(ctx, None, None))
         if merge:
-            merge_owned_rows(disps, kx_t, owned_t, group)
+            _timed("merge", lambda: merge_owned_rows(disps, kx_t, owned_t, group))
+        # every rank factorises the same summed system, but fp64 atomics inside the factorisation are unordered
+        # and a failed factorisation (zero update) is rank-local: rank 0's poses are the run's poses
+        if dist.is_initialized() and dist.get_world_size(group) > 1:
+            _timed("merge", lambda: dist.broadcast(poses[int(t0):int(t1)], src=dist.get_global_rank(group, 0) if group is not None else 0, group=group))
     return ctx

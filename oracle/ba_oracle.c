@@ -63,6 +63,16 @@ static int oracle_chol_solve(double *A, const double *b, double *x, int n) {
 #undef REAL
 #undef SUFFIX
 
+/* torchrun exports OMP_NUM_THREADS=1; the CPU baseline must use the cores it reports (bench.py) */
+void oracle_set_threads(int n) {
+#ifdef _OPENMP
+  extern void omp_set_num_threads(int);
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}
+
 int oracle_num_threads(void) {
 #ifdef _OPENMP
   extern int omp_get_max_threads(void);

@@ -20,7 +20,7 @@ Both need one compatibility overload that torch>=2 removed
 thirdparty/lietorch/lietorch/include/dispatch.h:39); it is force-included
 from a generated header, the reference files themselves stay untouched.
 
-Usage:  python oracle/build_ref.py [lietorch] [droid]
+Usage:  python oracle/build_ref.py [lietorch] [droid] [pyref]
 """
 import os
 import sys
@@ -99,6 +99,23 @@ def build_droid():
     )
 
 
+def stage_python():
+    """Copies the handful of pure-Python reference files that `src/geom/ba.py` needs to run -- src/geom/
+    and the lietorch package front-end -- next to lietorch_backends.so in the git-ignored oracle/_ref/pyref/,
+    so that the GPU box (which has no /root/reference) can time the reference's own PyTorch BA on its host
+    cores (bench.py cpu_baseline / --impl reference).  Nothing under oracle/_ref/ is tracked or shipped."""
+    import shutil
+
+    dst = os.path.join(OUT, "pyref")
+    for sub, names in (("src/geom", ("__init__.py", "ba.py", "chol.py", "projective_ops.py")),
+                       ("thirdparty/lietorch/lietorch", ("__init__.py", "groups.py", "group_ops.py", "broadcasting.py"))):
+        d = os.path.join(dst, "lietorch" if "lietorch" in sub else sub)
+        os.makedirs(d, exist_ok=True)
+        for n in names:
+            shutil.copy2(os.path.join(REF, sub, n), os.path.join(d, n))
+    return dst
+
+
 def available():
     return os.path.isdir(REF)
 
@@ -107,8 +124,10 @@ if __name__ == "__main__":
     if not available():
         print("reference tree not present at", REF, "- nothing to build")
         sys.exit(0)
-    what = sys.argv[1:] or ["lietorch", "droid"]
+    what = sys.argv[1:] or ["lietorch", "droid", "pyref"]
     if "lietorch" in what:
         print("lietorch_backends ->", build_lietorch())
     if "droid" in what:
         print("ref_droid_backends ->", build_droid())
+    if "pyref" in what:
+        print("python reference ->", stage_python())

@@ -47,6 +47,12 @@ def num_threads():
     return int(lib().oracle_num_threads())
 
 
+def set_threads(n):
+    """OpenMP threads of the oracle (torchrun exports OMP_NUM_THREADS=1 to its workers)"""
+    lib().oracle_set_threads(ctypes.c_int(int(n)))
+    return num_threads()
+
+
 def _p(a):
     return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
 

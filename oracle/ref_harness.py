@@ -21,12 +21,22 @@ import types
 
 REF = os.environ.get("GLORIE_REFERENCE", "/root/reference")
 HERE = os.path.dirname(os.path.abspath(__file__))
+PYREF = os.path.join(HERE, "_ref", "pyref")  # staged copy for the GPU box (oracle/build_ref.py stage_python)
 _loaded = None
 
 
+def _roots():
+    """(directory holding src/geom, directory holding the lietorch package): the reference tree where it
+    is mounted, else the staged copy under the git-ignored oracle/_ref/pyref/"""
+    if os.path.isdir(os.path.join(REF, "src", "geom")):
+        return REF, os.path.join(REF, "thirdparty", "lietorch")
+    if os.path.isdir(os.path.join(PYREF, "src", "geom")):
+        return PYREF, PYREF
+    return None, None
+
+
 def available():
-    return os.path.isdir(os.path.join(REF, "src", "geom")) and os.path.exists(
-        os.path.join(HERE, "_ref", "lietorch_backends.so"))
+    return _roots()[0] is not None and os.path.exists(os.path.join(HERE, "_ref", "lietorch_backends.so"))
 
 
 def _scatter_sum(src, index, dim=-1, out=None, dim_size=None):
@@ -49,22 +59,23 @@ def load():
         raise RuntimeError("reference tree or oracle/_ref/lietorch_backends.so missing; run oracle/build_ref.py")
     import torch  # noqa: F401
 
+    root, lt_root = _roots()
     sys.path.insert(0, os.path.join(HERE, "_ref"))
-    sys.path.insert(0, os.path.join(REF, "thirdparty", "lietorch"))
+    sys.path.insert(0, lt_root)
     ts = types.ModuleType("torch_scatter")
     ts.scatter_sum = _scatter_sum
     sys.modules.setdefault("torch_scatter", ts)
     lietorch = importlib.import_module("lietorch")
 
     pkg = types.ModuleType("src")
-    pkg.__path__ = [os.path.join(REF, "src")]
+    pkg.__path__ = [os.path.join(root, "src")]
     geom = types.ModuleType("src.geom")
-    geom.__path__ = [os.path.join(REF, "src", "geom")]
+    geom.__path__ = [os.path.join(root, "src", "geom")]
     sys.modules["src"] = pkg
     sys.modules["src.geom"] = geom
     pkg.geom = geom
 
-    path = os.path.join(REF, "src", "geom", "projective_ops.py")
+    path = os.path.join(root, "src", "geom", "projective_ops.py")
     code = open(path).read()
     old = 'torch.as_tensor([-0.1, 0.0, 0.0, 0.0, 0.0, 0.0, 1.0], device="cuda")'
     new = "torch.as_tensor([-0.1, 0.0, 0.0, 0.0, 0.0, 0.0, 1.0], device=Gij.data.device, dtype=Gij.data.dtype)"
