@@ -110,7 +110,7 @@ extern "C" void gba_destroy(gba_ctx *c) {
   void *ptrs[] = {c->kx, c->fmap, c->deg, c->eptr, c->eidx, c->ek, c->goff, c->st_d, c->geo, c->hpart, c->edge_hv,
                   c->Q, c->W, c->gram, c->dx, c->dzbuf, c->dspo_part, c->dwq, c->sys, c->tslot, c->perm, c->iperm, c->dspo_bad, c->wdog,
                   c->sb.tbits, c->sb.colrows, c->sb.colcnt, c->sb.rowcols, c->sb.rowcnt, c->sb.invL, c->sb.fail,
-                  c->flags, c->upd};
+                  c->flags, c->upd, c->sb.trace};
   for (void *q : ptrs)
     if (q) cudaFree(q);
   if (c->st_h) cudaFreeHost(c->st_h);
@@ -207,6 +207,11 @@ extern "C" int gba_create(gba_ctx **out, int device, int max_frames, int max_edg
   c->slot_cap = std::min<size_t>(nT * (nT + 1) / 2, (size_t)131072);
   CKC(dalloc(&c->upd, c->slot_cap));
   c->sb.upd = c->upd;
+  c->sb.trace = nullptr;
+  if (getenv("GBA_CHAIN_TRACE")) {  // development aid: task timeline of k_chain (GBA_GET_CHAIN_TRACE)
+    CKC(cudaMalloc((void **)&c->sb.trace, (1 + 4 * (size_t)CHAIN_TRACE_CAP) * sizeof(unsigned long long)));
+    CKC(cudaMemset(c->sb.trace, 0, sizeof(unsigned long long)));
+  }
   c->sb.ticket = c->flags + 4 * nT;
   c->sb.flagA = c->flags;
   c->sb.cntB = c->flags + nT;
@@ -556,6 +561,7 @@ extern "C" int gba_ba_solve(gba_ctx *c) {
     }
     if (!getenv("GBA_NO_CHAIN") && total_bulk < (1LL << 30)) {
       CK(cudaMemsetAsync(c->upd, 0, (size_t)st.n_slots * sizeof(unsigned int), s));
+      if (c->sb.trace) CK(cudaMemsetAsync(c->sb.trace, 0, sizeof(unsigned long long), s));  // keeps the last launch
       // spine CTAs: 4 slabs in flight per independent chain (band segments run side by side), at least 8
       spine_width = std::min(c->chain_capacity / 2, std::max(8, 4 * std::max(nseg, 1)));
       const int n_bulk = (int)std::max<long long>(1, std::min<long long>(total_bulk, (long long)c->chain_capacity - spine_width));
@@ -777,6 +783,9 @@ extern "C" int gba_get(gba_ctx *c, int what, void *dst, size_t bytes) {
     case GBA_GET_W: src = c->W; need = (size_t)st.K * p.HW * 4; break;
     case GBA_GET_GRAM: src = c->gram; need = (size_t)st.gram_floats * 4; break;
     case GBA_GET_WATCHDOG: src = c->wdog; need = 256 * 4; break;
+    case GBA_GET_CHAIN_TRACE:
+      if (!c->sb.trace) return fail_msg(c, GBA_EINVAL, "gba_get: no trace buffer (create the context with GBA_CHAIN_TRACE=1 set)");
+      src = c->sb.trace; need = std::min(bytes, (1 + 4 * (size_t)CHAIN_TRACE_CAP) * sizeof(unsigned long long)); break;
     case GBA_GET_TILEMASK: {
       const int nTa = st.n_tiles;
       need = (size_t)nTa * nTa;

@@ -28,6 +28,7 @@ struct SolverBufs {
   unsigned int *flagA, *cntB, *cntD, *flagX, *ticket;  // per-panel in-kernel synchronisation
   unsigned int *cntY, *ticket2;  // backward substitution: updates received per rhs block, its ticket dispenser
   unsigned int *upd;      // [n_slots] slab updates a tile has received inside k_chain
+  unsigned long long *trace;  // optional (GBA_CHAIN_TRACE=1): [0] = record count, then 4 words per task of k_chain
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -520,6 +521,12 @@ __global__ void __launch_bounds__(256) k_panel(BaParams p, SolverBufs sb, int kk
 // ---------------------------------------------------------------------------------------------
 #define CHAIN_WATCHDOG (1 << 21)  // polls of >= 32 ns: > 60 ms
 #define CHAIN_TDONE (1u << 20)      // upd[tile]: low 20 bits count update slabs, the rest solved slabs
+__device__ __forceinline__ unsigned long long chain_now() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#define CHAIN_TRACE_CAP 65536
 __device__ __forceinline__ void chain_wait(const unsigned *ptr, unsigned target, int *fail) {
   int spins = 0;
   while (ld_acquire(ptr) < target) {
@@ -606,6 +613,8 @@ __global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int ns
     __syncthreads();
     const int role = s_task[0], kk = s_task[1], a = s_task[2], b = s_task[3], q = s_task[4];
     if (role < 0) return;
+    unsigned long long tr_take = 0, tr_run = 0;
+    if (sb.trace && tid == 0) tr_take = chain_now();
     // tiles whose update counts gate this task: (i, j) and the number of earlier columns touching both
     int ti, tj;
     if (role == 0) ti = tj = kk;
@@ -636,6 +645,7 @@ __global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int ns
         chain_wait(sb.upd + p.tslot[tj * p.nT + kk], (unsigned)SPLIT * CHAIN_TDONE, sb.fail);
       }
       chain_wait(updp, need, sb.fail);
+      if (sb.trace) tr_run = chain_now();
     }
     __syncthreads();
     const bool failed = __ldcg(sb.fail) != 0;
@@ -659,6 +669,16 @@ __global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int ns
       __threadfence();
       __syncthreads();
       if (tid == 0) atomicAdd(const_cast<unsigned *>(updp), (unsigned)SPLIT);
+    }
+    if (sb.trace && tid == 0) {
+      const unsigned long long n = atomicAdd(sb.trace, 1ull);
+      if (n < CHAIN_TRACE_CAP) {
+        unsigned long long *r = sb.trace + 1 + 4 * n;
+        unsigned smid;
+        asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+        r[0] = ((unsigned long long)role << 56) | ((unsigned long long)kk << 40) | ((unsigned long long)a << 28) | ((unsigned long long)b << 16) | ((unsigned long long)q << 12) | (smid & 0xfff);
+        r[1] = tr_take; r[2] = tr_run; r[3] = chain_now();
+      }
     }
   }
 }

@@ -153,6 +153,10 @@ int gba_last_depth_frames(const gba_ctx *ctx);
 #define GBA_GET_WATCHDOG 10 /* int32 [256]: [0] = number of pipeline waits in the tensor-core Gram kernel that exceeded
                                the watchdog limit since gba_create (0 in a healthy run), then up to 42 records
                                {keyframe, split, warp, wait site, index, group}                                  */
+#define GBA_GET_CHAIN_TRACE 11 /* uint64: development aid, only when the context was created with the environment
+                                  variable GBA_CHAIN_TRACE set: [0] = tasks of the last factorisation kernel, then per task
+                                  {role<<56 | column<<40 | a<<28 | b<<16 | slab<<12 | SM, t_taken, t_inputs_ready, t_done}
+                                  in %globaltimer nanoseconds                                                           */
 int gba_get(gba_ctx *ctx, int what, void *dst, size_t bytes);
 
 /* ---- optional per-stage device timing ---------------------------------------------------
