@@ -25,7 +25,8 @@
 //   LBO = 16 * 128 + 16 = 2064: the 16 B pad makes the 32 pixel lanes of a producer warp, which all
 //   store the same row r at k = lane, fall into 32 different banks.
 // Pipeline (16 warps, one CTA per SM):
-//   warp 14, loader: 16-byte cp.async of the raw inputs -- per edge the target and weight rows, per
+//   warp 14, loader: 16-byte cp.async of the raw inputs -- per edge the two weight rows (the E rows carry no
+//     residual, so the targets are not read here), per
 //     keyframe disparity, Q, w -- 64 pixels (one "slot") at a time into a GT_IS-deep ring; each lane's
 //     cp.async.mbarrier.arrive fires on in_full[] when its copies have landed.  ~45 KB in flight per
 //     SM without a single register.
@@ -61,7 +62,7 @@
 #define GT_TPI 2                    // tiles per input stage
 #define GT_IPX (GT_TPI * GT_K)      // pixels per input stage
 #define GT_IS 3                     // input ring
-#define GT_IN_ROWS (4 * GT_MAXDEG + 3)
+#define GT_IN_ROWS (2 * GT_MAXDEG + 3)  // per edge the two weight rows (the E rows need no residual, hence no targets)
 #define GT_IN_BYTES (GT_IN_ROWS * GT_IPX * 4)
 #define GT_GROUP 4                  // tiles per accumulator group (16 truncating accumulations of hi hi^T)
 #define GT_SBO 128
@@ -216,7 +217,7 @@ __global__ void __launch_bounds__(GT_NT, 1) k_gram_tc(BaParams p) {
   uint64_t *s_bar = reinterpret_cast<uint64_t *>(s_raw + (size_t)GT_STAGES * GT_STAGE_BYTES + (size_t)GT_IS * GT_IN_BYTES);
   uint32_t *s_tmem = reinterpret_cast<uint32_t *>(s_bar + 2 * GT_STAGES + 4 + 2 * GT_IS);
   EdgeGeo *s_geo = reinterpret_cast<EdgeGeo *>(reinterpret_cast<unsigned char *>(s_bar) + 256);
-  const float **s_row = reinterpret_cast<const float **>(s_geo + deg);  // [4 deg + 3] input row bases
+  const float **s_row = reinterpret_cast<const float **>(s_geo + deg);  // [2 deg + 3] input row bases
   const uint32_t bar0 = tc::smem_u32(s_bar);
   auto full_bar = [&](int s) { return bar0 + 8u * s; };
   auto empty_bar = [&](int s) { return bar0 + 8u * (GT_STAGES + s); };
@@ -250,16 +251,15 @@ __global__ void __launch_bounds__(GT_NT, 1) k_gram_tc(BaParams p) {
     *reinterpret_cast<float *>(s_ops + (size_t)b * GT_BUF + (r & 7) * 16 + (r >> 3) * GT_SBO + (kk & 3) * 4 + (kk >> 2) * GT_LBO) = 0.f;
   }
   tc::fence_async_smem();
-  for (int c = tid; c < 4 * deg + 3; c += GT_NT) {
+  for (int c = tid; c < 2 * deg + 3; c += GT_NT) {
     const float *src;
-    if (c < 4 * deg) {
-      const int n = p.eidx[e0 + (c >> 2)], a = c & 3;
-      // interleaved layout: rows 4q, 4q+1 of a slot are the two 64-float halves of ONE run of 128 floats
-      // (u0 v0 u1 v1 ...) of the edge's targets, rows 4q+2, 4q+3 of its weights
-      src = IL ? ((a < 2) ? p.targets : p.weights) + (size_t)n * 2 * HW + (a & 1) * GT_IPX
-                 : ((a < 2) ? p.targets : p.weights) + ((size_t)n * 2 + (a & 1)) * HW;
+    if (c < 2 * deg) {
+      const int n = p.eidx[e0 + (c >> 1)], a = c & 1;
+      // interleaved layout: rows 2q, 2q+1 of a slot are the two 64-float halves of ONE run of 128 floats
+      // (u0 v0 u1 v1 ...) of the edge's weights
+      src = IL ? p.weights + (size_t)n * 2 * HW + a * GT_IPX : p.weights + ((size_t)n * 2 + a) * HW;
     } else {
-      const int a = c - 4 * deg;
+      const int a = c - 2 * deg;
       src = (a == 0 ? p.disps + (size_t)frame * HW : a == 1 ? p.Q + (size_t)k * HW : p.W + (size_t)k * HW);
     }
     s_row[c] = src;
@@ -315,26 +315,23 @@ __global__ void __launch_bounds__(GT_NT, 1) k_gram_tc(BaParams p) {
     auto fast_slot = [&](auto ne_c, int is, int it0, int b0) {
       constexpr int NE = decltype(ne_c)::value;
       const float *in = s_in + (size_t)is * (GT_IN_BYTES / 4) + lane;
-      float ctu[NE][GT_TPI], ctv[NE][GT_TPI], cwu[NE][GT_TPI], cwv[NE][GT_TPI], czq[GT_TPI], cqv[GT_TPI], cwk[GT_TPI];
+      float cwu[NE][GT_TPI], cwv[NE][GT_TPI], czq[GT_TPI], cqv[GT_TPI], cwk[GT_TPI];
 #pragma unroll
       for (int u = 0; u < GT_TPI; u++) {
 #pragma unroll
         for (int h = 0; h < NE; h++) {
           const int q = b0 + h * GT_NPW;
           if (IL) {  // (u, v) pairs: pixel u * 32 + lane of the slot sits at float 2 * (u * 32 + lane) of the run
-            const float2 tt = *reinterpret_cast<const float2 *>(in + lane + (4 * q + 0) * GT_IPX + 2 * u * GT_K);
-            const float2 ww = *reinterpret_cast<const float2 *>(in + lane + (4 * q + 2) * GT_IPX + 2 * u * GT_K);
-            ctu[h][u] = tt.x; ctv[h][u] = tt.y; cwu[h][u] = ww.x; cwv[h][u] = ww.y;
+            const float2 ww = *reinterpret_cast<const float2 *>(in + lane + (2 * q) * GT_IPX + 2 * u * GT_K);
+            cwu[h][u] = ww.x; cwv[h][u] = ww.y;
           } else {
-            ctu[h][u] = in[(4 * q + 0) * GT_IPX + u * GT_K];
-            ctv[h][u] = in[(4 * q + 1) * GT_IPX + u * GT_K];
-            cwu[h][u] = in[(4 * q + 2) * GT_IPX + u * GT_K];
-            cwv[h][u] = in[(4 * q + 3) * GT_IPX + u * GT_K];
+            cwu[h][u] = in[(2 * q + 0) * GT_IPX + u * GT_K];
+            cwv[h][u] = in[(2 * q + 1) * GT_IPX + u * GT_K];
           }
         }
-        czq[u] = in[(4 * deg + 0) * GT_IPX + u * GT_K];
-        cqv[u] = in[(4 * deg + 1) * GT_IPX + u * GT_K];
-        cwk[u] = (b0 == 0) ? in[(4 * deg + 2) * GT_IPX + u * GT_K] : 0.f;
+        czq[u] = in[(2 * deg + 0) * GT_IPX + u * GT_K];
+        cqv[u] = in[(2 * deg + 1) * GT_IPX + u * GT_K];
+        cwk[u] = (b0 == 0) ? in[(2 * deg + 2) * GT_IPX + u * GT_K] : 0.f;
       }
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(inempty_bar(is));
@@ -363,7 +360,7 @@ __global__ void __launch_bounds__(GT_NT, 1) k_gram_tc(BaParams p) {
         for (int h = 0; h < NE; h++) {
           const EdgeGeo &ge = s_geo[b0 + h * GT_NPW];
           PixHat L;
-          pix_hat<MODE>(ge.R, ge.t, pk, x0, y0, czq[u], ctu[h][u], ctv[h][u], cwu[h][u], cwv[h][u], L);
+          pix_hat<MODE>(ge.R, ge.t, pk, x0, y0, czq[u], 0.f, 0.f, cwu[h][u], cwv[h][u], L);  // residuals unused
           const float g = csq * gate[h];
           const float su = g * L.wu * L.jzu, sv = g * L.wv * L.jzv;
           float e[6];
@@ -428,26 +425,23 @@ __global__ void __launch_bounds__(GT_NT, 1) k_gram_tc(BaParams p) {
       } else {
         const int ne = (b0 + GT_NPW < deg) ? 2 : 1;
         const float *in = s_in + (size_t)is * (GT_IN_BYTES / 4) + lane;
-        float ctu[2][GT_TPI], ctv[2][GT_TPI], cwu[2][GT_TPI], cwv[2][GT_TPI], czq[GT_TPI], cqv[GT_TPI], cwk[GT_TPI];
+        float cwu[2][GT_TPI], cwv[2][GT_TPI], czq[GT_TPI], cqv[GT_TPI], cwk[GT_TPI];
   #pragma unroll
         for (int u = 0; u < GT_TPI; u++) {
   #pragma unroll
           for (int h = 0; h < 2; h++) {
             const int q = (h < ne) ? b0 + h * GT_NPW : b0;
             if (IL) {
-              const float2 tt = *reinterpret_cast<const float2 *>(in + lane + (4 * q + 0) * GT_IPX + 2 * u * GT_K);
-              const float2 ww = *reinterpret_cast<const float2 *>(in + lane + (4 * q + 2) * GT_IPX + 2 * u * GT_K);
-              ctu[h][u] = tt.x; ctv[h][u] = tt.y; cwu[h][u] = ww.x; cwv[h][u] = ww.y;
+              const float2 ww = *reinterpret_cast<const float2 *>(in + lane + (2 * q) * GT_IPX + 2 * u * GT_K);
+              cwu[h][u] = ww.x; cwv[h][u] = ww.y;
             } else {
-              ctu[h][u] = in[(4 * q + 0) * GT_IPX + u * GT_K];
-              ctv[h][u] = in[(4 * q + 1) * GT_IPX + u * GT_K];
-              cwu[h][u] = in[(4 * q + 2) * GT_IPX + u * GT_K];
-              cwv[h][u] = in[(4 * q + 3) * GT_IPX + u * GT_K];
+              cwu[h][u] = in[(2 * q + 0) * GT_IPX + u * GT_K];
+              cwv[h][u] = in[(2 * q + 1) * GT_IPX + u * GT_K];
             }
           }
-          czq[u] = in[(4 * deg + 0) * GT_IPX + u * GT_K];
-          cqv[u] = in[(4 * deg + 1) * GT_IPX + u * GT_K];
-          cwk[u] = (b0 == 0) ? in[(4 * deg + 2) * GT_IPX + u * GT_K] : 0.f;
+          czq[u] = in[(2 * deg + 0) * GT_IPX + u * GT_K];
+          cqv[u] = in[(2 * deg + 1) * GT_IPX + u * GT_K];
+          cwk[u] = (b0 == 0) ? in[(2 * deg + 2) * GT_IPX + u * GT_K] : 0.f;
         }
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(inempty_bar(is));
@@ -470,7 +464,7 @@ __global__ void __launch_bounds__(GT_NT, 1) k_gram_tc(BaParams p) {
                 float e[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
                 if (pv && !(ge.flags & 1)) {
                   PixHat L;
-                  pix_hat<MODE>(ge.R, ge.t, pk, x0, y0, czq[u], ctu[h][u], ctv[h][u], cwu[h][u], cwv[h][u], L);
+                  pix_hat<MODE>(ge.R, ge.t, pk, x0, y0, czq[u], 0.f, 0.f, cwu[h][u], cwv[h][u], L);  // residuals unused
                   const float su = csq * L.wu * L.jzu, sv = csq * L.wv * L.jzv;
                   e[0] = su * L.e;
                   e[1] = sv * L.e;
@@ -535,7 +529,7 @@ __global__ void __launch_bounds__(GT_NT, 1) k_gram_tc(BaParams p) {
     // ---------------- loader: bulk copies of the raw inputs, GT_IPX pixels per slot -----------------
     // Lane l moves 16 bytes: two 64-pixel rows per warp instruction.  (A TMA bulk copy per row was
     // tried first: at 256 B per copy the loader spent ~90 cycles per copy and set the kernel's pace.)
-    const int nin = (nloc + GT_TPI - 1) / GT_TPI, nrow = 4 * deg + 3;
+    const int nin = (nloc + GT_TPI - 1) / GT_TPI, nrow = 2 * deg + 3;
     const int sub = lane >> 4, c4 = (lane & 15) * 4;  // which row of the pair, first pixel of the 16 B piece
     for (int j = 0; j < nin; j++) {
       const int is = j % GT_IS, use = j / GT_IS;
@@ -545,14 +539,14 @@ __global__ void __launch_bounds__(GT_NT, 1) k_gram_tc(BaParams p) {
       const int start = (tile0 + j * GT_TPI) * GT_K;
       const int npx = min(min(GT_IPX, HW - start), (nloc - j * GT_TPI) * GT_K);  // HW % 4 == 0: whole 16 B pieces
       const uint32_t dst0 = tc::smem_u32(s_in) + (uint32_t)is * GT_IN_BYTES + (uint32_t)c4 * 4u;
-      // edge rows (targets / weights), then the three keyframe rows.  Both loops are straight-line
+      // edge rows (weights), then the three keyframe rows.  Both loops are straight-line
       // (no test inside) so that the row-pointer loads of the unrolled iterations overlap: this warp is
       // a latency chain, a branch or a predicate in the body costs the whole kernel 15-60 %.
-      const int nedge = 4 * deg;
+      const int nedge = 2 * deg;
       const int estart = IL ? 2 * start : start;  // interleaved: an edge row advances 2 floats per pixel
       const int elim = IL ? 2 * npx : npx;
       // c = sub, sub + 2, ...: the parity of c is this lane's `sub`, so the bound test leaves the loop
-      const int eoff = IL ? sub * GT_IPX + c4 : c4;  // interleaved: rows 4q, 4q+1 are halves of one run
+      const int eoff = IL ? sub * GT_IPX + c4 : c4;  // interleaved: rows 2q, 2q+1 are halves of one run
       if (eoff < elim) {
 #pragma unroll 8
         for (int c = sub; c < nedge; c += 2) tc::cp_async16(dst0 + (uint32_t)c * (GT_IPX * 4), s_row[c] + estart + c4);

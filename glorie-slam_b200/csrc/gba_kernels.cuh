@@ -597,12 +597,10 @@ __global__ void __launch_bounds__(GRAM_NT, 2) k_gram(BaParams p) {
       if (nq <= GRAM_PB) {
         // common case: all edges of this warp fit one batch.  The producer is latency bound, so the
         // inputs of tile it+1 are requested before tile it is computed (register double buffer).
-        const float *tgp[GRAM_PB];
         const float *wgp[GRAM_PB];
 #pragma unroll
         for (int u = 0; u < GRAM_PB; u++) {
           const int n = (u < nq) ? s_eid[pw + u * npw] : 0;
-          tgp[u] = p.targets + (size_t)n * 2 * HW;
           wgp[u] = p.weights + (size_t)n * 2 * HW;
         }
         float tu_[GRAM_PB], tv_[GRAM_PB], wu_[GRAM_PB], wv_[GRAM_PB], zq = 1.f, qv = 0.f, wk = 0.f;
@@ -616,8 +614,7 @@ __global__ void __launch_bounds__(GRAM_NT, 2) k_gram(BaParams p) {
           for (int u = 0; u < GRAM_PB; u++) {
             const bool ok = pv && u < nq;
             const int ou = p.il ? 2 * pix : pix, ov = p.il ? 2 * pix + 1 : HW + pix;
-            tu_[u] = ok ? ldg_stream(tgp[u] + ou) : 0.f;
-            tv_[u] = ok ? ldg_stream(tgp[u] + ov) : 0.f;
+            tu_[u] = tv_[u] = 0.f;  // the E rows carry no residual: the targets are not read in this pass
             wu_[u] = ok ? ldg_stream(wgp[u] + ou) : 0.f;
             wv_[u] = ok ? ldg_stream(wgp[u] + ov) : 0.f;
           }
@@ -663,10 +660,8 @@ __global__ void __launch_bounds__(GRAM_NT, 2) k_gram(BaParams p) {
               tu_[u] = tv_[u] = wu_[u] = wv_[u] = 0.f;
               if (j0 + u < nq && pv) {
                 const int n = s_eid[pw + (j0 + u) * npw];
-                const float *tg = p.targets + (size_t)n * 2 * HW, *wg = p.weights + (size_t)n * 2 * HW;
+                const float *wg = p.weights + (size_t)n * 2 * HW;
                 const int ou = p.il ? 2 * pix : pix, ov = p.il ? 2 * pix + 1 : HW + pix;
-                tu_[u] = ldg_stream(tg + ou);
-                tv_[u] = ldg_stream(tg + ov);
                 wu_[u] = ldg_stream(wg + ou);
                 wv_[u] = ldg_stream(wg + ov);
               }
