@@ -17,6 +17,7 @@ MODES = {"droid_cuda": MODE_DROID_CUDA, "geom_py": MODE_GEOM_PY}
 LAYOUT_INTERLEAVED = 0x100
 
 GET_KX, GET_EPTR, GET_EIDX, GET_EDGE_HV, GET_Q, GET_W, GET_SYSTEM, GET_TILEMASK, GET_GRAM, GET_WATCHDOG = range(1, 11)
+GET_CHAIN_TRACE, GET_PERM = 11, 12
 
 _lib = None
 _ctx = {}
@@ -25,7 +26,7 @@ _ctx = {}
 class Info(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int) for n in (
         "n_depth_frames", "n_poses", "max_out_degree", "chol_failures", "n_tiles", "n_active_tiles",
-        "kernel_launches", "chain_columns", "last_fail_code", "watchdog_trips")]
+        "kernel_launches", "chain_columns", "last_fail_code", "watchdog_trips", "n_segments", "segment_tiles")]
 
 
 def lib():
@@ -51,6 +52,13 @@ def lib():
         L.gba_ba_end.argtypes = [vp, vp, vp]
         L.gba_query.argtypes = [vp, ctypes.POINTER(Info)]
         L.gba_get.argtypes = [vp, ci, vp, ctypes.c_size_t]
+        L.gba_ba_set_shard.argtypes = [vp, ci, ci, ci]
+        L.gba_ba_eliminate.argtypes = [vp]
+        L.gba_ba_finish.argtypes = [vp]
+        L.gba_ba_system_part.argtypes = [vp, ci, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]
+        L.gba_plan.argtypes = [vp, vp, vp, ci, ci, ci, ci, vp]
+        for f in ("gba_ba_set_shard", "gba_ba_eliminate", "gba_ba_finish", "gba_ba_system_part", "gba_plan"):
+            getattr(L, f).restype = ci
         L.gba_last_depth_frames.argtypes = [vp]
         L.gba_last_depth_frames.restype = ci
         L.gba_edge_blocks_static.argtypes = [vp] * 7 + [ci] * 5 + [vp, vp]
@@ -148,11 +156,11 @@ class _DevBuf:
                                          "version": 2}
 
 
-def system_view(ctx, device):
-    """torch.float64 view of the packed reduced camera system of the last gba_ba_build
-    (what an edge-sharded run all-reduces)."""
+def system_view(ctx, device, part=0):
+    """torch.float64 view of the packed reduced camera system of the last gba_ba_build: part 0 = all of
+    it, part 1 = the closure x closure tiles + rhs (the one range the ranks of a sharded solve exchange)."""
     import torch
 
     ptr, cnt = ctypes.c_void_p(), ctypes.c_size_t()
-    check(ctx, lib().gba_ba_system(ctx, ctypes.byref(ptr), ctypes.byref(cnt)))
+    check(ctx, lib().gba_ba_system_part(ctx, int(part), ctypes.byref(ptr), ctypes.byref(cnt)))
     return torch.as_tensor(_DevBuf(ptr.value, cnt.value, "<f8"), device=device)

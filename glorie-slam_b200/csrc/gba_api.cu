@@ -41,6 +41,7 @@ struct gba_ctx {
   BaParams p;
   cudaStream_t stream;
   int begun, launches, variant, gsplit, total_fail, last_P;
+  int seg_lo, seg_n, first_rank;  // edge-sharded solve: this rank's band segments (seg_n = 0: not sharded)
   size_t sys_count;
   char err[512];
   // optional stage timing
@@ -226,16 +227,9 @@ extern "C" int gba_create(gba_ctx **out, int device, int max_frames, int max_edg
   CKC(cudaFuncSetAttribute(k_gram_tc<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gram_tc_smem(GT_MAXDEG)));
   CKC(cudaFuncSetAttribute(k_gram_tc<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gram_tc_smem(GT_MAXDEG)));
   CKC(cudaFuncSetAttribute(k_gram_tc<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gram_tc_smem(GT_MAXDEG)));
-  CKC(cudaFuncSetAttribute(k_potrf_diag, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolverSmem));
-  CKC(cudaFuncSetAttribute(k_trsm, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolverSmem));
-  CKC(cudaFuncSetAttribute(k_syrk, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolverSmem));
-  CKC(cudaFuncSetAttribute(k_panel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolverSmem));
-  CKC(cudaFuncSetAttribute(k_panel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolverSmem));
   CKC(cudaFuncSetAttribute(k_chain<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolverSmem));
   {
     int per_sm = 0;
-    CKC(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_panel<16>, 256, kSolverSmem));
-    c->panel_capacity = per_sm * c->sm_count;  // the fused tile-column kernel needs a co-resident grid
     CKC(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_chain<16>, 256, kSolverSmem));
     c->chain_capacity = std::max(1, per_sm) * c->sm_count;
   }
@@ -342,6 +336,9 @@ extern "C" int gba_ba_begin(gba_ctx *c, float *poses, float *disps, const float 
   c->stream = (cudaStream_t)stream;
   c->launches = 0;
   c->total_fail = 0;
+  c->seg_lo = 0;
+  c->seg_n = 0;
+  c->first_rank = 1;
   BaParams &p = c->p;
   memset(&p, 0, sizeof(p));
   p.poses = poses; p.disps = disps; p.intr = intrinsics; p.sens = disps_sens; p.targets = targets;
@@ -448,7 +445,7 @@ extern "C" int gba_ba_build(gba_ctx *c) {
     LAUNCH_CHECK("k_edge_finish");
   }
   if (p.mode == GBA_MODE_GEOM_PY) {  // damping on H before the Schur complement (chol.py:66-68)
-    k_damp<<<(6 * p.P + 255) / 256, 256, 0, s>>>(p, p.lm, p.ep);
+    k_damp<<<(6 * p.P + 255) / 256, 256, 0, s>>>(p, p.lm, p.ep, 0, -1, 1, 0, 0);
     LAUNCH_CHECK("k_damp");
   }
   stage_end(c);
@@ -503,92 +500,71 @@ extern "C" int gba_ba_system(gba_ctx *c, double **buf, size_t *count) {
   return GBA_OK;
 }
 
-extern "C" int gba_ba_solve(gba_ctx *c) {
-  if (!c || !c->begun) return c ? fail_msg(c, GBA_EINVAL, "gba_ba_solve without gba_ba_begin") : GBA_EINVAL;
+// The factorisation kernel.  phase 0: everything (one rank).  Edge-sharded runs: phase 1 = the tile columns of this
+// rank's band segments, phase 2 = the closure block after the ranks have summed it.
+static int launch_chain(gba_ctx *c, int phase) {
   BaParams &p = c->p;
   cudaStream_t s = c->stream;
   const Status &st = *c->st_h;
-  CK(cudaSetDevice(c->device));
-  stage_begin(c, GBA_STAGE_FACTOR);
-  if (p.mode == GBA_MODE_DROID_CUDA) {  // damping after the Schur complement (droid_kernels.cu:1197,1407)
-    k_damp<<<(6 * p.P + 255) / 256, 256, 0, s>>>(p, p.lm, p.ep);
-    LAUNCH_CHECK("k_damp");
+  const int nT = st.n_tiles, nseg = st.n_seg, segT = st.seg_tiles, band = nseg > 1 ? nseg * segT : 0;
+  const int *colcnt = c->h_cnt;
+  const int seg_lo = phase == 1 ? c->seg_lo : 0, seg_n = phase == 1 ? c->seg_n : (nseg > 1 ? nseg : 0);
+  // spine queue: the first potrf of every chain, then per column its critical tasks; bulk queue: the rest
+  long long total_spine = 0, total_bulk = 0;
+  auto add_col = [&](int kk, bool has_next) {
+    const int cnt = colcnt[kk];
+    total_spine += (cnt > 0 ? 8 : 0) + (has_next ? 1 : 0);
+    total_bulk += cnt > 0 ? 4LL * (cnt - 1) + (long long)cnt * (cnt + 1) / 2 - 1 : 0;
+  };
+  int chains = 0;
+  if (phase != 2 && nseg > 1) {
+    for (int sg = seg_lo; sg < seg_lo + seg_n; sg++)
+      for (int t = 0; t < segT; t++) {
+        const int kk = sg * segT + t;
+        add_col(kk, t + 1 < segT || (phase == 0 && kk == band - 1 && band < nT));
+      }
+    chains = seg_n;
+    total_spine += seg_n;
   }
-  CK(cudaMemsetAsync(c->flags, 0, (size_t)7 * c->nT_max * sizeof(unsigned int), s));
-  {
-    // Tile columns of the n_seg band segments are independent: step t of every segment is one
-    // launch (grid.y = segment); the closure block follows column by column.  16-row slabs
-    // (4 CTAs per tile) spread the fp64 work over more SMs while the structure is sparse.
-    const int nT = st.n_tiles, nseg = st.n_seg, segT = st.seg_tiles, band = nseg > 1 ? nseg * segT : 0;
-    const int *colcnt = c->h_cnt, *rowcnt = c->h_cnt + c->nT_max;
-    const int atomic_from = nseg > 1 ? band : (1 << 30);
-    auto panel = [&](int kk0, int stride, int ny, bool last) -> int {
-      int mc = 0;  // the launch is sized by the fullest of its tile columns (counts known on the host)
-      for (int y = 0; y < ny; y++) mc = std::max(mc, colcnt[kk0 + y * stride]);
-      const int pairs = mc * (mc + 1) / 2;
-      const bool split = (1 + mc + pairs) * ny <= 4 * c->sm_count;
-      if (getenv("GBA_UNFUSED") && ny == 1) {  // diagnostic: the three phases as separate launches
-        k_potrf_diag<<<1, 256, kSolverSmem, s>>>(p, c->sb, kk0);
-        LAUNCH_CHECK("k_potrf_diag");
-        if (mc > 0 && !last) {
-          k_trsm<<<mc, 256, kSolverSmem, s>>>(p, c->sb, kk0);
-          LAUNCH_CHECK("k_trsm");
-          k_syrk<<<pairs, 256, kSolverSmem, s>>>(p, c->sb, kk0);
-          LAUNCH_CHECK("k_syrk");
-        }
-      } else if (split) {
-        k_panel<16><<<dim3(last ? 1 : 1 + 4 * mc + 4 * pairs, ny), 256, kSolverSmem, s>>>(p, c->sb, kk0, stride, mc,
-                                                                                      atomic_from);
-        LAUNCH_CHECK("k_panel");
-      } else {
-        k_panel<64><<<dim3(last ? 1 : 1 + mc + pairs, ny), 256, kSolverSmem, s>>>(p, c->sb, kk0, stride, mc,
-                                                                              atomic_from);
-        LAUNCH_CHECK("k_panel");
-      }
-      return GBA_OK;
-    };
-    // One launch: the whole factorisation as a dependency graph of tile tasks on a persistent grid.
-    // GBA_NO_CHAIN=1 keeps the older sequence, one launch per band step and per closure column.
-    // spine queue: the first potrf of every segment, then per column its critical tasks; bulk queue: the rest
-    long long total_spine = nseg > 1 ? nseg : 1, total_bulk = 0;
-    int spine_width = 0;
-    for (int kk = 0; kk < nT; kk++) {
-      const int cnt = colcnt[kk];
-      const bool in_band = kk < band;
-      const bool has_next = in_band ? ((kk % segT) + 1 < segT || (kk == band - 1 && band < nT)) : (kk + 1 < nT);
-      total_spine += (cnt > 0 ? 8 : 0) + (has_next ? 1 : 0);
-      total_bulk += cnt > 0 ? 4LL * (cnt - 1) + (long long)cnt * (cnt + 1) / 2 - 1 : 0;
-    }
-    if (!getenv("GBA_NO_CHAIN") && total_bulk < (1LL << 30)) {
-      CK(cudaMemsetAsync(c->upd, 0, (size_t)st.n_slots * sizeof(unsigned int), s));
-      if (c->sb.trace) CK(cudaMemsetAsync(c->sb.trace, 0, sizeof(unsigned long long), s));  // keeps the last launch
-      // spine CTAs: 4 slabs in flight per independent chain (band segments run side by side), at least 8
-      spine_width = std::min(c->chain_capacity / 2, std::max(8, 4 * std::max(nseg, 1)));
-      const int n_bulk = (int)std::max<long long>(1, std::min<long long>(total_bulk, (long long)c->chain_capacity - spine_width));
-      k_chain<16><<<spine_width + n_bulk, 256, kSolverSmem, s>>>(p, c->sb, nseg, segT, (int)total_spine, (int)total_bulk,
-                                                               spine_width);
-      LAUNCH_CHECK("k_chain");
-    } else {
-      for (int t = 0; t < (nseg > 1 ? segT : 0); t++) {
-        const int rc = panel(t, segT, nseg, false);
-        if (rc) return rc;
-      }
-      for (int kk = band; kk < nT; kk++) {
-        const int rc = panel(kk, 0, 1, kk + 1 >= nT);
-        if (rc) return rc;
-      }
-    }
-    stage_end(c);
-    stage_begin(c, GBA_STAGE_SOLVE);
-    {  // one launch: a task per active tile below the diagonal, plus the rows that receive no update
-      int tasks = 0;
-      for (int i = 0; i < nT; i++) tasks += rowcnt[i] + (colcnt[i] == 0 ? 1 : 0);
-      const int grid = std::max(1, std::min(tasks, 4 * c->sm_count));
-      k_back<<<grid, 256, 0, s>>>(p, c->sb, tasks);
-      LAUNCH_CHECK("k_back");
+  if (phase != 1) {
+    for (int kk = band; kk < nT; kk++) add_col(kk, kk + 1 < nT);
+    if (chains == 0) {
+      chains = 1;
+      total_spine += 1;
     }
   }
-  k_dx_out<<<(6 * p.P + 255) / 256, 256, 0, s>>>(p, c->sb);
+  if (total_bulk >= (1LL << 30)) return fail_msg(c, GBA_ECAPACITY, "reduced system too large for the tile task graph");
+  CK(cudaMemsetAsync(c->flags, 0, (size_t)5 * c->nT_max * sizeof(unsigned int), s));  // flagA .. ticket (not cntY / ticket2)
+  CK(cudaMemsetAsync(c->upd, 0, (size_t)st.n_slots * sizeof(unsigned int), s));
+  if (c->sb.trace) CK(cudaMemsetAsync(c->sb.trace, 0, sizeof(unsigned long long), s));  // keeps the last launch
+  // spine CTAs: 4 slabs in flight per independent chain (band segments run side by side), at least 8
+  const int spine_width = std::min(c->chain_capacity / 2, std::max(8, 4 * chains));
+  const int n_bulk = (int)std::max<long long>(1, std::min<long long>(total_bulk, (long long)c->chain_capacity - spine_width));
+  k_chain<16><<<spine_width + n_bulk, 256, kSolverSmem, s>>>(p, c->sb, nseg, segT, (int)total_spine, (int)total_bulk,
+                                                           spine_width, phase, seg_lo, phase == 1 ? c->seg_n : 0);
+  LAUNCH_CHECK("k_chain");
+  return GBA_OK;
+}
+
+// backward substitution (one launch), dx, failure accounting, then back-substitution of the disparities and the
+// pose retraction
+static int solve_tail(gba_ctx *c, bool sharded) {
+  BaParams &p = c->p;
+  cudaStream_t s = c->stream;
+  const Status &st = *c->st_h;
+  const int nT = st.n_tiles;
+  const int *colcnt = c->h_cnt, *rowcnt = c->h_cnt + c->nT_max;
+  stage_begin(c, GBA_STAGE_SOLVE);
+  CK(cudaMemsetAsync(c->sb.cntY, 0, (size_t)2 * c->nT_max * sizeof(unsigned int), s));  // cntY, ticket2
+  CK(cudaMemsetAsync(c->sb.flagX, 0, (size_t)c->nT_max * sizeof(unsigned int), s));
+  {  // one launch: a task per active tile below the diagonal, plus the rows that receive no update
+    int tasks = 0;
+    for (int i = 0; i < nT; i++) tasks += rowcnt[i] + (colcnt[i] == 0 ? 1 : 0);
+    const int grid = std::max(1, std::min(tasks, 4 * c->sm_count));
+    k_back<<<grid, 256, 0, s>>>(p, c->sb, tasks, sharded ? c->seg_lo : 0, sharded ? c->seg_n : -1, st.n_seg, st.seg_tiles);
+    LAUNCH_CHECK("k_back");
+  }
+  k_dx_out<<<(6 * p.P + 255) / 256, 256, 0, s>>>(p, c->sb, sharded ? c->seg_lo : 0, sharded ? c->seg_n : -1, st.n_seg, st.seg_tiles);
   LAUNCH_CHECK("k_dx_out");
   k_fail_account<<<1, 1, 0, s>>>(p, c->sb);
   LAUNCH_CHECK("k_fail_account");
@@ -622,6 +598,98 @@ extern "C" int gba_ba_solve(gba_ctx *c) {
     stage_end(c);
   }
   return GBA_OK;
+}
+
+extern "C" int gba_ba_solve(gba_ctx *c) {
+  if (!c || !c->begun) return c ? fail_msg(c, GBA_EINVAL, "gba_ba_solve without gba_ba_begin") : GBA_EINVAL;
+  BaParams &p = c->p;
+  cudaStream_t s = c->stream;
+  CK(cudaSetDevice(c->device));
+  stage_begin(c, GBA_STAGE_FACTOR);
+  if (p.mode == GBA_MODE_DROID_CUDA) {  // damping after the Schur complement (droid_kernels.cu:1197,1407)
+    k_damp<<<(6 * p.P + 255) / 256, 256, 0, s>>>(p, p.lm, p.ep, 0, -1, 1, 0, 0);
+    LAUNCH_CHECK("k_damp");
+  }
+  int rc = launch_chain(c, 0);
+  if (rc) return rc;
+  stage_end(c);
+  return solve_tail(c, false);
+}
+
+// ---- the solve of an edge-sharded run, split at the one exchange it needs ------------------------------------
+extern "C" int gba_ba_set_shard(gba_ctx *c, int seg_lo, int seg_n, int first_rank) {
+  if (!c || !c->begun) return c ? fail_msg(c, GBA_EINVAL, "gba_ba_set_shard without gba_ba_begin") : GBA_EINVAL;
+  const Status &st = *c->st_h;
+  if (st.n_seg < 2) return fail_msg(c, GBA_EINVAL, "the reduced system of this graph has no independent band segments");
+  if (seg_lo < 0 || seg_n < 1 || seg_lo + seg_n > st.n_seg)
+    return fail_msg(c, GBA_EINVAL, "segments [%d,%d) outside [0,%d)", seg_lo, seg_lo + seg_n, st.n_seg);
+  if (c->p.mode != GBA_MODE_DROID_CUDA) return fail_msg(c, GBA_EINVAL, "sharded solve: droid_cuda semantics only");
+  c->seg_lo = seg_lo;
+  c->seg_n = seg_n;
+  c->first_rank = first_rank ? 1 : 0;
+  return GBA_OK;
+}
+
+extern "C" int gba_ba_eliminate(gba_ctx *c) {
+  if (!c || !c->begun || c->seg_n < 1) return c ? fail_msg(c, GBA_EINVAL, "gba_ba_eliminate without gba_ba_set_shard") : GBA_EINVAL;
+  BaParams &p = c->p;
+  cudaStream_t s = c->stream;
+  const Status &st = *c->st_h;
+  CK(cudaSetDevice(c->device));
+  stage_begin(c, GBA_STAGE_FACTOR);
+  // damping d += ep + lm d on the SUMMED diagonal, by linearity: own band rows in full (only this rank holds them),
+  // closure rows lm d_local on every rank and ep once
+  k_damp<<<(6 * p.P + 255) / 256, 256, 0, s>>>(p, p.lm, p.ep, c->seg_lo, c->seg_n, c->first_rank, st.n_seg, st.seg_tiles);
+  LAUNCH_CHECK("k_damp");
+  int rc = launch_chain(c, 1);
+  if (rc) return rc;
+  stage_end(c);
+  return GBA_OK;
+}
+
+extern "C" int gba_ba_system_part(gba_ctx *c, int which, double **buf, size_t *count) {
+  if (!c || !c->begun || !buf || !count) return GBA_EINVAL;
+  const Status &st = *c->st_h;
+  if (which == 0) {
+    *buf = c->sys;
+    *count = c->sys_count;
+  } else {  // closure x closure tiles + the whole rhs: one contiguous range (k_tile_fill numbers those tiles last)
+    *buf = c->sys + (size_t)st.cc_slot0 * GBA_NB2;
+    *count = c->sys_count - (size_t)st.cc_slot0 * GBA_NB2;
+  }
+  return GBA_OK;
+}
+
+extern "C" int gba_ba_finish(gba_ctx *c) {
+  if (!c || !c->begun || c->seg_n < 1) return c ? fail_msg(c, GBA_EINVAL, "gba_ba_finish without gba_ba_set_shard") : GBA_EINVAL;
+  CK(cudaSetDevice(c->device));
+  stage_begin(c, GBA_STAGE_FACTOR);
+  int rc = launch_chain(c, 2);
+  if (rc) return rc;
+  stage_end(c);
+  return solve_tail(c, true);
+}
+
+// index build + ordering + tile structure of a graph given by its edge indices alone (no per-pixel data): what a
+// caller needs (GBA_GET_PERM, gba_query) to decide which rank owns which source keyframe
+extern "C" int gba_plan(gba_ctx *c, const int64_t *ii, const int64_t *jj, int n_edges, int n_frames, int t0, int t1,
+                        void *stream) {
+  if (!c) return GBA_EINVAL;
+  c->begun = 0;
+  if (!ii || !jj || n_edges < 1 || n_edges > c->E_max) return fail_msg(c, GBA_EINVAL, "gba_plan: bad edge list");
+  if (n_frames < 1 || n_frames > c->N_max || t0 < 0 || t1 <= t0 || t1 > n_frames)
+    return fail_msg(c, GBA_EINVAL, "gba_plan: bad frame window");
+  CK(cudaSetDevice(c->device));
+  c->stream = (cudaStream_t)stream;
+  c->launches = 0;
+  BaParams &p = c->p;
+  memset(&p, 0, sizeof(p));
+  p.ii = ii; p.jj = jj; p.N = n_frames; p.E = n_edges; p.HW = c->HW; p.wd = c->wd; p.t0 = t0; p.t1 = t1; p.P = t1 - t0;
+  p.mode = GBA_MODE_DROID_CUDA;
+  p.kx = c->kx; p.fmap = c->fmap; p.deg = c->deg; p.eptr = c->eptr; p.eidx = c->eidx; p.ek = c->ek;
+  p.goff = c->goff; p.st = c->st_d; p.tslot = c->tslot; p.perm = c->perm; p.iperm = c->iperm; p.nT = c->nT_max;
+  c->last_P = p.P;
+  return build_index(c, nullptr, 0, true);
 }
 
 extern "C" int gba_ba_end(gba_ctx *c, float *dx_out, float *dz_out) {
@@ -760,6 +828,8 @@ extern "C" int gba_query(gba_ctx *c, gba_info *info) {
   // sequential tile columns of the factorisation: one band segment's worth plus the closure block
   info->chain_columns = (st.n_seg > 1 ? st.seg_tiles : 0) + (st.n_tiles - (st.n_seg > 1 ? st.n_seg * st.seg_tiles : 0));
   info->last_fail_code = st.last_fail;
+  info->n_segments = st.n_seg;
+  info->segment_tiles = st.seg_tiles;
   int wd0 = 0;
   CK(cudaMemcpy(&wd0, c->wdog, sizeof(int), cudaMemcpyDeviceToHost));
   info->watchdog_trips = wd0;
@@ -783,6 +853,7 @@ extern "C" int gba_get(gba_ctx *c, int what, void *dst, size_t bytes) {
     case GBA_GET_W: src = c->W; need = (size_t)st.K * p.HW * 4; break;
     case GBA_GET_GRAM: src = c->gram; need = (size_t)st.gram_floats * 4; break;
     case GBA_GET_WATCHDOG: src = c->wdog; need = 256 * 4; break;
+    case GBA_GET_PERM: src = c->perm; need = (size_t)c->last_P * 4; break;
     case GBA_GET_CHAIN_TRACE:
       if (!c->sb.trace) return fail_msg(c, GBA_EINVAL, "gba_get: no trace buffer (create the context with GBA_CHAIN_TRACE=1 set)");
       src = c->sb.trace; need = std::min(bytes, (1 + 4 * (size_t)CHAIN_TRACE_CAP) * sizeof(unsigned long long)); break;

@@ -38,7 +38,9 @@ struct Status {          // device -> host after the index build
   int n_seg;             // independent band segments (nested dissection); 1 = plain band
   int seg_tiles;         // tile columns per segment
   int n_pos;             // pose positions of the reduced system incl. padding
+  int cc_slot0;          // first slot of the closure x closure tiles (they are numbered last)
   int last_fail;         // code of the most recent failed factorisation: 1 pivot <= 0, 3 / 4 a pipeline watchdog
+  int pad3;
   unsigned long long gram_floats;  // total size of the per-frame Gram buffers
 };
 

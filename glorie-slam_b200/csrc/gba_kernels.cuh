@@ -851,12 +851,21 @@ __global__ void __launch_bounds__(SCHUR_NT) k_schur(BaParams p) {
 
 // Levenberg-Marquardt damping of the diagonal: d += ep + lm * d
 // (droid_kernels.cu:1197 after the Schur complement; chol.py:66-68 before it).
-__global__ void k_damp(BaParams p, float lm, float ep) {
+// seg_n < 0: the whole system.  Edge-sharded (seg_n >= 1): the damping acts on the SUM over ranks, so by linearity
+// this rank damps its own band segments [seg_lo, seg_lo + seg_n) in full (nobody else contributes to them), adds
+// lm * d_local to the closure rows and -- on the first rank only -- their ep; foreign band rows are left alone.
+__global__ void k_damp(BaParams p, float lm, float ep, int seg_lo, int seg_n, int first_rank, int nseg, int segT) {
   const int q = blockIdx.x * blockDim.x + threadIdx.x;
   if (q >= 6 * p.P) return;
   const int i = 6 * p.perm[q / 6] + q % 6;
   double *d = sys_at(p, i, i);
-  *d += (double)ep + (double)lm * (*d);
+  if (seg_n < 0) {
+    *d += (double)ep + (double)lm * (*d);
+    return;
+  }
+  const int tile = i / GBA_NB, band = nseg * segT;
+  if (tile >= band) *d += (first_rank ? (double)ep : 0.0) + (double)lm * (*d);
+  else if (tile / segT >= seg_lo && tile / segT < seg_lo + seg_n) *d += (double)ep + (double)lm * (*d);
 }
 
 // --------------------------------------------------------------------------------------------

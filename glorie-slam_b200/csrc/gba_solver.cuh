@@ -263,27 +263,40 @@ __global__ void __launch_bounds__(512) k_tile_fill(BaParams p, SolverBufs sb) {
     }
     __syncthreads();
   }
-  // slots: row-major over the lower triangle
-  for (int i = tid; i < nT; i += blockDim.x) {
+  // slots: row-major over the lower triangle, but the closure x closure tiles (both tile indices >= bandT) are
+  // numbered after all the others: together with the rhs that follows the tiles they form ONE contiguous
+  // range -- what the ranks of an edge-sharded run exchange (every other tile is produced by one rank alone).
+  const int bandT = p.st->n_seg > 1 ? p.st->n_seg * p.st->seg_tiles : 0;
+  auto popc_below = [&](int i, int j) {  // structure bits of row i in columns [0, j)
     int c = 0;
-    for (int w = 0; w < nW; w++) c += __popc(bits[i * TS_WORDS + w]);
-    s_start[i + 1] = c;
+    for (int w = 0; w < (j >> 5); w++) c += __popc(bits[i * TS_WORDS + w]);
+    if (j & 31) c += __popc(bits[i * TS_WORDS + (j >> 5)] & ((1u << (j & 31)) - 1u));
+    return c;
+  };
+  __shared__ int s_start_cc[TS_MAXT + 1];
+  for (int i = tid; i < nT; i += blockDim.x) {
+    const int all = popc_below(i, i + 1), nc = popc_below(i, min(bandT, i + 1));
+    s_start[i + 1] = nc;            // tiles of row i left of the closure block
+    s_start_cc[i + 1] = all - nc;   // its closure x closure tiles
   }
   __syncthreads();
   if (tid == 0) {
     s_start[0] = 0;
-    for (int i = 0; i < nT; i++) s_start[i + 1] += s_start[i];
-    p.st->n_slots = s_start[nT];
+    s_start_cc[0] = 0;
+    for (int i = 0; i < nT; i++) {
+      s_start[i + 1] += s_start[i];
+      s_start_cc[i + 1] += s_start_cc[i];
+    }
+    p.st->cc_slot0 = s_start[nT];
+    p.st->n_slots = s_start[nT] + s_start_cc[nT];
   }
   __syncthreads();
   for (int idx = tid; idx < nT * nT; idx += blockDim.x) {
     const int i = idx / nT, j = idx % nT;
     int slot = -1;
     if (j <= i && ((bits[i * TS_WORDS + (j >> 5)] >> (j & 31)) & 1)) {
-      int c = 0;
-      for (int w = 0; w < (j >> 5); w++) c += __popc(bits[i * TS_WORDS + w]);
-      c += __popc(bits[i * TS_WORDS + (j >> 5)] & ((1u << (j & 31)) - 1u));
-      slot = s_start[i] + c;
+      if (j < bandT) slot = s_start[i] + popc_below(i, j);
+      else slot = s_start[nT] + s_start_cc[i] + popc_below(i, j) - popc_below(i, bandT);
     }
     p.tslot[i * nS + j] = slot;
   }
@@ -414,79 +427,6 @@ __device__ __forceinline__ unsigned ld_acquire(const unsigned *p) {
   return v;
 }
 
-// Fused tile column kk.  Grid = 1 + SPLIT*max_col + SPLIT*max_col(max_col+1)/2 CTAs:
-//   CTA 0             potrf of the diagonal tile (skipped when the previous column's look-ahead
-//                     already did it), then raises flagA[kk];
-//   trsm CTAs         wait for flagA[kk], solve one slab of one tile below the diagonal, count
-//                     themselves into cntB[kk];
-//   syrk CTAs         wait until cntB[kk] == SPLIT*cnt, update one slab of one trailing tile.
-//   look-ahead        the syrk CTAs of tile (kk+1, kk+1) take a ticket; the last one factorises
-//                     that tile at once (potrf of column kk+1 overlaps the rest of this update).
-// Roles are handed out by an atomic ticket taken when a CTA starts running, not by blockIdx: a
-// CTA that waits therefore only ever waits for CTAs that started before it, so the kernel cannot
-// deadlock however the grid is dispatched and however much larger than the GPU it is.
-// blockIdx.y selects the band segment: tile column kk = kk0 + y * kk_stride (independent columns).
-template <int SLAB>
-__global__ void __launch_bounds__(256) k_panel(BaParams p, SolverBufs sb, int kk0, int kk_stride, int max_col,
-                                               int atomic_from) {
-  extern __shared__ double s_buf[];
-  constexpr int SPLIT = GBA_NB / SLAB;
-  __shared__ int s_flag, s_bid;
-  const int tid = threadIdx.x, kk = kk0 + blockIdx.y * kk_stride;
-  if (tid == 0) s_bid = (int)atomicAdd(&sb.ticket[kk], 1u);
-  __syncthreads();
-  const int b = s_bid;
-  const int cnt = sb.colcnt[kk];
-  if (b == 0) {
-    if (ld_acquire(&sb.flagA[kk]) == 0u) {
-      if (!__ldcg(sb.fail)) role_potrf(p, sb, kk, s_buf);
-      __threadfence();
-      __syncthreads();
-      if (tid == 0) atomicExch(&sb.flagA[kk], 1u);
-    }
-    return;
-  }
-  if (b <= SPLIT * max_col) {
-    const int a = (b - 1) / SPLIT, q = (b - 1) % SPLIT;
-    if (a >= cnt) return;
-    if (tid == 0)
-      while (ld_acquire(&sb.flagA[kk]) == 0u) __nanosleep(20);
-    __syncthreads();
-    if (!__ldcg(sb.fail)) role_trsm<SLAB>(p, sb, kk, a, q, atomic_from, s_buf);
-    __threadfence();
-    __syncthreads();
-    if (tid == 0) atomicAdd(&sb.cntB[kk], 1u);
-    return;
-  }
-  const int w = b - 1 - SPLIT * max_col, pair = w / SPLIT, q = w % SPLIT;
-  int a = 0, rem = pair;
-  while (rem > a) {
-    rem -= a + 1;
-    a++;
-  }
-  if (a >= cnt) return;
-  if (tid == 0)
-    while (ld_acquire(&sb.cntB[kk]) < (unsigned)(SPLIT * cnt)) __nanosleep(20);
-  __syncthreads();
-  const bool failed = __ldcg(sb.fail);
-  if (!failed) role_syrk<SLAB>(p, sb, kk, a, rem, q, atomic_from, s_buf);
-  // look-ahead: tile (kk+1, kk+1) is complete once its SPLIT slabs are updated
-  // (not into the closure block: its tiles are still being updated by the other band segments)
-  if (pair == 0 && sb.colrows[kk * p.nT] == kk + 1 && kk + 1 < atomic_from) {
-    __threadfence();
-    __syncthreads();
-    if (tid == 0) s_flag = (atomicAdd(&sb.cntD[kk], 1u) == (unsigned)(SPLIT - 1));
-    __syncthreads();
-    if (s_flag) {
-      __threadfence();
-      if (!failed) role_potrf(p, sb, kk + 1, s_buf);
-      __threadfence();
-      __syncthreads();
-      if (tid == 0) atomicExch(&sb.flagA[kk + 1], 1u);
-    }
-  }
-}
-
 // ---------------------------------------------------------------------------------------------
 // k_chain: the WHOLE factorisation in ONE launch, as a dependency graph of tile tasks.
 //
@@ -540,14 +480,23 @@ __device__ __forceinline__ void chain_wait(const unsigned *ptr, unsigned target,
 
 template <int SLAB>
 __global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int nseg, int segT, int total_spine,
-                                               int total_bulk, int n_spine) {
+                                               int total_bulk, int n_spine, int phase, int seg_lo, int seg_n) {
   extern __shared__ double s_buf[];
   constexpr int SPLIT = GBA_NB / SLAB;
   __shared__ int s_task[5];  // role, kk, a, b, q
   __shared__ unsigned s_need[2];
   const int tid = threadIdx.x, nT = p.st->n_tiles;
-  const int band = nseg > 1 ? nseg * segT : 0, ninit = nseg > 1 ? nseg : 1;
-  const int atomic_from = nseg > 1 ? band : (1 << 30);
+  // phase 0: the whole factorisation.  An edge-sharded run splits it: phase 1 = the columns of this rank's band
+  // segments [seg_lo, seg_lo + seg_n) only (their updates of closure tiles are unordered atomics), phase 2 = the
+  // closure block alone, after the ranks have summed it (updates of band columns are then already in the tiles:
+  // only the columns >= band count as predecessors).
+  const int band = nseg > 1 ? nseg * segT : 0;
+  const int nsl = phase == 1 ? seg_n : (phase == 2 ? 0 : (nseg > 1 ? nseg : 0));  // band segments in play
+  const int seg0 = phase == 1 ? seg_lo : 0;
+  const int nband = nsl * segT, clo = phase == 1 ? 0 : nT - band;  // sequence positions: band part, closure part
+  const int ninit = nsl > 0 ? nsl : 1;
+  const int minbit = phase == 2 ? band : 0;
+  const int atomic_from = (nsl > 0) ? band : (1 << 30);
   // Two ticket queues.  SPINE: the tasks every following column waits for -- P(k), the solve of the tile below
   // the diagonal and the update of the next diagonal tile -- served by the first n_spine CTAs only, so that
   // they never queue behind a wave of bulk updates.  BULK: everything else.  Inside each queue tickets are
@@ -557,11 +506,11 @@ __global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int ns
   const bool spine = (int)blockIdx.x < n_spine;
   unsigned *ticket = spine ? &sb.ticket[0] : &sb.ticket[1];
   const int total = spine ? total_spine : total_bulk;
-  auto seq = [&](int s_) { return s_ < band ? (s_ % nseg) * segT + s_ / nseg : s_; };
+  auto seq = [&](int s_) { return s_ < nband ? (seg0 + s_ % nsl) * segT + s_ / nsl : band + (s_ - nband); };
   auto next_of = [&](int s_, int kk_) {  // column whose potrf is issued inside block(kk_), or -1
-    if (s_ < band) {
-      if (s_ / nseg + 1 < segT) return kk_ + 1;
-      return (s_ == band - 1 && band < nT) ? band : -1;
+    if (s_ < nband) {
+      if (s_ / nsl + 1 < segT) return kk_ + 1;
+      return (s_ == nband - 1 && clo > 0) ? band : -1;
     }
     return kk_ + 1 < nT ? kk_ + 1 : -1;
   };
@@ -573,7 +522,7 @@ __global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int ns
       int role = -1, kk = 0, a = 0, b = 0, q = 0;
       if (spine && t < ninit) {
         role = 0;
-        kk = nseg > 1 ? t * segT : 0;
+        kk = nsl > 0 ? (seg0 + t) * segT : band;
       } else if (t < total) {
         for (;;) {  // tickets only grow: the walk over the sequence is amortised
           const int col = seq(spos), nx = next_of(spos, col);
@@ -621,14 +570,16 @@ __global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int ns
     else if (role == 1) { ti = sb.colrows[kk * p.nT + a]; tj = kk; }
     else { ti = sb.colrows[kk * p.nT + a]; tj = sb.colrows[kk * p.nT + b]; }
     // closure tile updated from a band column: atomic, unordered
-    const bool unordered = role >= 2 && tj >= atomic_from && kk < band;
+    const bool unordered = role >= 2 && tj >= atomic_from && kk < band;  // (band columns only exist when nsl > 0)
     if (tid < 32) {
       unsigned n = 0;
       if (tid < TS_WORDS && !unordered) {
         unsigned m = sb.tbits[ti * TS_WORDS + tid] & sb.tbits[tj * TS_WORDS + tid];
-        const int hi = kk - 32 * tid;  // keep bits c < kk of this word
+        const int hi = kk - 32 * tid, lo = minbit - 32 * tid;  // keep bits minbit <= c < kk of this word
         if (hi <= 0) m = 0;
         else if (hi < 32) m &= (1u << hi) - 1u;
+        if (lo >= 32) m = 0;
+        else if (lo > 0) m &= ~((1u << lo) - 1u);
         n = __popc(m);
       }
 #pragma unroll
@@ -683,28 +634,6 @@ __global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int ns
   }
 }
 
-// the same three phases as separate launches (large, near-dense structures)
-__global__ void __launch_bounds__(256) k_potrf_diag(BaParams p, SolverBufs sb, int kk) {
-  extern __shared__ double s_buf[];
-  if (!*sb.fail) role_potrf(p, sb, kk, s_buf);
-}
-__global__ void __launch_bounds__(256) k_trsm(BaParams p, SolverBufs sb, int kk) {
-  extern __shared__ double s_buf[];
-  if (*sb.fail || (int)blockIdx.x >= sb.colcnt[kk]) return;
-  role_trsm<GBA_NB>(p, sb, kk, blockIdx.x, 0, 1 << 30, s_buf);
-}
-__global__ void __launch_bounds__(256) k_syrk(BaParams p, SolverBufs sb, int kk) {
-  extern __shared__ double s_buf[];
-  if (*sb.fail) return;
-  int a = 0, rem = blockIdx.x;
-  while (rem > a) {
-    rem -= a + 1;
-    a++;
-  }
-  if (a >= sb.colcnt[kk]) return;
-  role_syrk<GBA_NB>(p, sb, kk, a, rem, 0, 1 << 30, s_buf);
-}
-
 // ---------------------------------------------------------------------------------------------
 // Backward substitution L^T x = y in ONE launch: a task per active tile (i, k), k < i, handed out by
 // ticket in order of descending tile row i.  Task (i, k) waits for x_i (flagX[i]), subtracts
@@ -739,11 +668,15 @@ __device__ __forceinline__ void back_solve_x(const BaParams &p, const SolverBufs
   if (tid == 0) atomicExch(&sb.flagX[i], 1u);
 }
 
-__global__ void __launch_bounds__(256) k_back(BaParams p, SolverBufs sb, int total) {
+// seg_n >= 1 (edge-sharded run): only the closure rows and the rows of this rank's band segments are solved here.
+__global__ void __launch_bounds__(256) k_back(BaParams p, SolverBufs sb, int total, int seg_lo, int seg_n, int nseg,
+                                              int segT) {
   __shared__ double s_x[GBA_NB], s_part[4][GBA_NB];
   __shared__ int s_task[3];  // role (0 seed, 1 tile, -1 done), i, k
   const int tid = threadIdx.x, col = tid & 63, part = tid >> 6, nT = p.st->n_tiles;
   if (__ldcg(sb.fail)) return;
+  const int band = nseg * segT;
+  auto own = [&](int tile) { return seg_n < 0 || tile >= band || (tile / segT >= seg_lo && tile / segT < seg_lo + seg_n); };
   int row = nT - 1, base = 0, nseed = -1;  // thread 0: walk over the rows, amortised (tickets only grow)
   for (;;) {
     __syncthreads();
@@ -776,6 +709,7 @@ __global__ void __launch_bounds__(256) k_back(BaParams p, SolverBufs sb, int tot
     __syncthreads();
     const int role = s_task[0], i = s_task[1], k = s_task[2];
     if (role < 0) return;
+    if (!own(role == 0 ? i : k)) continue;  // another rank's band segment
     double l[16];
     if (role == 0) {
       const double *XI = sb.invL + (size_t)i * GBA_NB2;
@@ -821,12 +755,14 @@ __global__ void __launch_bounds__(256) k_back(BaParams p, SolverBufs sb, int tot
 
 // dx = (float) x in the caller's pose order, or zero when the factorisation failed
 // (droid_kernels.cu:1202-1210, chol.py:13-15; the reference hands dx back as fp32, :1204-1205)
-__global__ void k_dx_out(BaParams p, SolverBufs sb) {
+// (edge-sharded run: poses of another rank's band segments get a zero update here; their owner moves them)
+__global__ void k_dx_out(BaParams p, SolverBufs sb, int seg_lo, int seg_n, int nseg, int segT) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int failed = *sb.fail;
   if (i < 6 * p.P) {
-    const int pose = i / 6, r = i - 6 * pose;
-    p.dx[i] = failed ? 0.f : (float)rhs_ptr(p)[6 * p.perm[pose] + r];
+    const int pose = i / 6, r = i - 6 * pose, pos = p.perm[pose], tile = 6 * pos / GBA_NB;
+    const bool own = seg_n < 0 || tile >= nseg * segT || (tile / segT >= seg_lo && tile / segT < seg_lo + seg_n);
+    p.dx[i] = (failed || !own) ? 0.f : (float)rhs_ptr(p)[6 * pos + r];
   }
 }
 __global__ void k_fail_account(BaParams p, SolverBufs sb) {

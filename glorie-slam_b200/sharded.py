@@ -64,6 +64,87 @@ def partition(ii, kx, world):
     return owner
 
 
+class Plan:
+    """Ownership of the depth keyframes for a SEGMENTED sharded solve (see `plan`)."""
+
+    def __init__(self, owner, seg_of_rank, pose_owner, n_segments):
+        self.owner = owner              # [K] int32: rank that owns kx[k]
+        self.seg_of_rank = seg_of_rank  # [world] (seg_lo, seg_n)
+        self.pose_owner = pose_owner    # [t1 - t0] int32: rank whose solve moves that pose (closure poses: 0)
+        self.n_segments = n_segments
+
+
+def plan_from_perm(ii, jj, kx, t0, t1, perm, n_segments, segment_tiles, world):
+    """Host half of `plan`: given the pose -> position map of the ordered reduced system, assign every depth
+    keyframe to the rank that owns the ONE band segment its pose blocks fall into (its own pose and the
+    destinations of its out-edges; closure poses are shared and do not count).  Returns None when some keyframe
+    touches two segments or the segments do not divide among the ranks -- the caller then keeps the replicated solve."""
+    ii, jj, kx, perm = (np.asarray(a, dtype=np.int64) for a in (ii, jj, kx, perm))
+    if n_segments < 2 or n_segments % world != 0:
+        return None
+    P = t1 - t0
+    seg_pos = segment_tiles * 64 // 6            # pose positions per segment (tile aligned: 32 poses = 3 tiles)
+    band_end = n_segments * seg_pos
+    seg_of_pose = np.where(perm < band_end, perm // seg_pos, -1)  # -1: closure block
+    def pose_seg(frames):
+        pr = frames - t0
+        ok = (pr >= 0) & (pr < P)
+        out = np.full(frames.shape, -1, dtype=np.int64)
+        out[ok] = seg_of_pose[pr[ok]]
+        return out
+    lo = np.full(len(kx), n_segments, dtype=np.int64)
+    hi = np.full(len(kx), -1, dtype=np.int64)
+    k_of_edge = np.searchsorted(kx, ii)
+    for segs, ks in ((pose_seg(jj), k_of_edge), (pose_seg(kx), np.arange(len(kx)))):
+        m = segs >= 0
+        np.minimum.at(lo, ks[m], segs[m])
+        np.maximum.at(hi, ks[m], segs[m])
+    if np.any((hi >= 0) & (lo != hi)):
+        return None
+    seg = np.where(hi >= 0, hi, -1)
+    # keyframes that touch closure poses only: follow the nearest keyframe in time that has a segment
+    if np.any(seg < 0):
+        known = np.where(seg >= 0)[0]
+        if len(known) == 0:
+            return None
+        nearest = known[np.abs(kx[known][None, :] - kx[:, None]).argmin(axis=1)]
+        seg = np.where(seg >= 0, seg, seg[nearest])
+    per = n_segments // world
+    owner = (seg // per).astype(np.int32)
+    pose_owner = np.where(seg_of_pose >= 0, seg_of_pose // per, 0).astype(np.int32)
+    return Plan(owner, [(r * per, per) for r in range(world)], pose_owner, n_segments)
+
+
+def plan(ii, jj, t0, t1, n_frames, ht, wd, world, device):
+    """Decide which rank owns which source keyframe so that only the CLOSURE block of the reduced system is
+    shared between ranks: runs the library's ordering on the edge indices (gba_plan), then `plan_from_perm`.
+    Every rank computes the same plan from the same (replicated) edge list.  Returns (kx, Plan or None)."""
+    import ctypes
+
+    ii_t = torch.as_tensor(np.ascontiguousarray(ii), dtype=torch.int64, device=device)
+    jj_t = torch.as_tensor(np.ascontiguousarray(jj), dtype=torch.int64, device=device)
+    kx = frame_list(ii, t0, t1)
+    L = _gba.lib()
+    with torch.cuda.device(device):
+        ctx = _gba.context(torch.device(device).index, n_frames, int(ii_t.shape[0]), ht, wd)
+        _gba.check(ctx, L.gba_plan(ctx, ii_t.data_ptr(), jj_t.data_ptr(), int(ii_t.shape[0]), int(n_frames), int(t0),
+                                   int(t1), torch.cuda.current_stream(device).cuda_stream))
+        info = _gba.query(ctx)
+        perm = np.zeros(t1 - t0, dtype=np.int32)
+        _gba.check(ctx, L.gba_get(ctx, _gba.GET_PERM, perm.ctypes.data_as(ctypes.c_void_p), perm.nbytes))
+    return kx, plan_from_perm(ii, jj, kx, t0, t1, perm, info.n_segments, info.segment_tiles, world)
+
+
+def merge_poses(poses, t0, t1, pose_owner_t, rank, group=None):
+    """Segmented solve: every rank moved the closure poses and the poses of its own band segments; sum the
+    masked rows so that all ranks end with the full trajectory (closure poses are taken from rank 0)."""
+    rows = poses[t0:t1] * (pose_owner_t == rank).to(poses.dtype)[:, None]
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(rows, op=dist.ReduceOp.SUM, group=group)
+    poses[t0:t1] = rows
+    return poses
+
+
 def local_edges(ii, kx, owner, rank):
     """Boolean mask of the edges whose source keyframe `rank` owns."""
     pos = np.searchsorted(np.asarray(kx), np.asarray(ii))
@@ -87,7 +168,7 @@ def allreduce_system(view, group=None):
 
 
 def ba_sharded(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1, iterations, lm, ep,
-               kx_t, owned_t, ii_all, jj_all, group=None, merge=True):
+               kx_t, owned_t, ii_all, jj_all, group=None, merge=True, segments=None, pose_owner_t=None):
     """`droid_backends.ba` for one rank of an edge-sharded run.
 
     poses / disps / intrinsics / disps_sens / eta: the full (replicated) tensors on this rank's GPU;
@@ -95,7 +176,10 @@ def ba_sharded(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, 
     owned_t [K] uint8 = (owner == rank), ii_all / jj_all: the edge indices of the WHOLE graph
     (replicated; the pose ordering and the tile layout of the reduced system are derived from them
     so that all ranks pack the system identically).  poses and the owned rows of disps are updated in place;
-    with merge=True all rows of disps are consistent on return.  Returns the kernel-launch count."""
+    with merge=True all rows of disps are consistent on return.
+    segments = (seg_lo, seg_n) from `plan` switches to the SEGMENTED solve: this rank eliminates its own band
+    segments, only the closure block + rhs is all-reduced, the closure factorisation is replicated; pose_owner_t
+    [t1 - t0] (rank per pose) is then needed for the final merge of the poses.  Returns the context."""
     dev = poses.device
     N, ht, wd = disps.shape
     E = int(ii.shape[0])
@@ -109,14 +193,26 @@ def ba_sharded(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, 
                                        nul(jj), N, E, int(eta.shape[0]), int(t0), int(t1), float(lm), float(ep), 0, 0,
                                        _gba.MODE_DROID_CUDA, kx_t.data_ptr(), int(kx_t.shape[0]), owned_t.data_ptr(),
                                        ii_all.data_ptr(), jj_all.data_ptr(), int(ii_all.shape[0]), stream))
-        view = _gba.system_view(ctx, dev)
+        rank = dist.get_rank(group) if dist.is_initialized() else 0
+        if segments is not None:
+            _gba.check(ctx, L.gba_ba_set_shard(ctx, int(segments[0]), int(segments[1]), int(rank == 0)))
+        view = _gba.system_view(ctx, dev, 0 if segments is None else 1)
         for _ in range(int(iterations)):
             _gba.check(ctx, L.gba_ba_build(ctx))
-            _timed("allreduce", lambda: allreduce_system(view, group))
-            _gba.check(ctx, L.gba_ba_solve(ctx))
+            if segments is None:
+                _timed("allreduce", lambda: allreduce_system(view, group))
+                _gba.check(ctx, L.gba_ba_solve(ctx))
+            else:
+                _gba.check(ctx, L.gba_ba_eliminate(ctx))
+                _timed("allreduce", lambda: allreduce_system(view, group))
+                _gba.check(ctx, L.gba_ba_finish(ctx))
         _gba.check(ctx, L.gba_ba_end(ctx, None, None))
         if merge:
             _timed("merge", lambda: merge_owned_rows(disps, kx_t, owned_t, group))
+        if segments is not None:
+            if merge:
+                _timed("merge", lambda: merge_poses(poses, int(t0), int(t1), pose_owner_t, rank, group))
+            return ctx
         # every rank factorises the same summed system, but fp64 atomics inside the factorisation are unordered
         # and a failed factorisation (zero update) is rank-local: rank 0's poses are the run's poses
         if dist.is_initialized() and dist.get_world_size(group) > 1:

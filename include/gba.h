@@ -115,6 +115,30 @@ int gba_ba_system(gba_ctx *ctx, double **buf, size_t *count);
 int gba_ba_solve(gba_ctx *ctx);
 int gba_ba_end(gba_ctx *ctx, float *dx_out, float *dz_out);
 
+/* ---- sharded SOLVE (optional second stage of the split-phase form) ---------------------------------
+ * With gba_ba_solve every rank factorises the whole summed system.  When the ordering found independent band
+ * segments (gba_query: n_segments > 1) and every source keyframe lives on the rank that owns the band segment its
+ * pose blocks fall into, only the closure block of the reduced system is shared between ranks:
+ *   gba_plan            index build + ordering + tile structure from the edge indices alone; read the pose ->
+ *                       position map with gba_get(GBA_GET_PERM) and n_segments / segment_tiles with gba_query to
+ *                       decide the ownership (glorie-slam_b200/sharded.py::plan does it)
+ *   gba_ba_begin        as above (owned = the keyframes of this rank's segments)
+ *   gba_ba_set_shard    this rank eliminates band segments [seg_lo, seg_lo + seg_n); first_rank != 0 on exactly one rank
+ *   per iteration:
+ *     gba_ba_build      local contributions
+ *     gba_ba_eliminate  damping + factorisation of this rank's band segments (their Schur complement lands in
+ *                       the closure tiles)
+ *     (caller sums gba_ba_system_part(ctx, 1, ..) over ranks: closure x closure tiles + rhs, one contiguous range)
+ *     gba_ba_finish     closure factorisation (replicated), backward substitution of the closure and of this rank's
+ *                       segments, disparity update of the owned keyframes, retraction of the closure poses and of
+ *                       this rank's poses (the other poses get a zero update here: merge them after the last iteration)
+ * No counterpart in the reference (it has no multi-GPU path). */
+int gba_plan(gba_ctx *ctx, const int64_t *ii, const int64_t *jj, int n_edges, int n_frames, int t0, int t1, void *stream);
+int gba_ba_set_shard(gba_ctx *ctx, int seg_lo, int seg_n, int first_rank);
+int gba_ba_eliminate(gba_ctx *ctx);
+int gba_ba_system_part(gba_ctx *ctx, int which /* 0 whole system, 1 closure block + rhs */, double **buf, size_t *count);
+int gba_ba_finish(gba_ctx *ctx);
+
 /* ---- introspection (used by the parity tests; synchronises the stream) ----------------- */
 typedef struct gba_info {
   int n_depth_frames;   /* K                                                  */
@@ -129,6 +153,8 @@ typedef struct gba_info {
                            NumericalIssue, droid_kernels.cu:1202-1210), 3 / 4 = an in-kernel wait of the tile
                            Cholesky / the tensor-core Gram pipeline exceeded its watchdog; 0 = none since begin */
   int watchdog_trips;   /* GBA_GET_WATCHDOG[0]: watchdog records since gba_create (0 in a healthy process)       */
+  int n_segments;       /* independent band segments of the ordered reduced system (1: none)                     */
+  int segment_tiles;    /* tile columns per segment                                                              */
 } gba_info;
 int gba_query(gba_ctx *ctx, gba_info *info);
 /* K = number of depth keyframes of the last gba_ba / gba_ba_begin / gba_dspo call on this context, from the host copy
@@ -153,6 +179,9 @@ int gba_last_depth_frames(const gba_ctx *ctx);
 #define GBA_GET_WATCHDOG 10 /* int32 [256]: [0] = number of pipeline waits in the tensor-core Gram kernel that exceeded
                                the watchdog limit since gba_create (0 in a healthy run), then up to 42 records
                                {keyframe, split, warp, wait site, index, group}                                  */
+#define GBA_GET_PERM 12     /* int32 [P]: pose (frame - t0) -> position in the ordered reduced system; positions below
+                               n_segments * segment_tiles * 64 / 6 belong to band segment position / (segment_tiles * 64 / 6),
+                               the others to the closure block (gba_query gives n_segments, segment_tiles)          */
 #define GBA_GET_CHAIN_TRACE 11 /* uint64: development aid, only when the context was created with the environment
                                   variable GBA_CHAIN_TRACE set: [0] = tasks of the last factorisation kernel, then per task
                                   {role<<56 | column<<40 | a<<28 | b<<16 | slab<<12 | SM, t_taken, t_inputs_ready, t_done}

@@ -102,3 +102,58 @@ def split_phase(g, mode=0, owned_masks=None, iters=1):
     for d in ranks:
         L.gba_destroy(d.h)
     return SimpleNamespace(poses=poses, disps=disps, M=systems[0], rhs=systems[1], infos=infos, kx=kx)
+
+
+def segmented(g, world, iters=2):
+    """The SEGMENTED sharded solve, `world` ranks emulated on ONE GPU through the C ABI: every rank builds and
+    eliminates its own band segments, the closure block + rhs ranges are summed (the all-reduce), every rank
+    finishes.  Returns None when the graph's ordering offers no plan for `world` ranks, else the merged state."""
+    import sharded
+
+    L = _gba.lib()
+    N, ht, wd = g.disps.shape
+    kx, plan = sharded.plan(g.ii, g.jj, g.t0, g.t1, N, ht, wd, world, "cuda:0")
+    if plan is None:
+        return None
+    ranks = []
+    for r in range(world):
+        m = (plan.owner == r)
+        sel = sharded.local_edges(g.ii, kx, plan.owner, r)
+        h = ctypes.c_void_p()
+        assert L.gba_create(ctypes.byref(h), 0, N, g.n_edges, ht, wd) == 0, L.gba_last_error(None)
+        t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+        d = SimpleNamespace(h=h, own=m, poses=t(g.poses), disps=t(g.disps), intr=t(g.intrinsics), sens=t(g.disps_sens),
+                            targets=t(g.targets[sel]), weights=t(g.weights[sel]), eta=t(g.eta), ii=t(g.ii[sel]),
+                            jj=t(g.jj[sel]), kx=t(kx), mask=t(m.astype(np.uint8)), ii_all=t(g.ii), jj_all=t(g.jj))
+        _gba.check(h, L.gba_ba_begin(h, d.poses.data_ptr(), d.disps.data_ptr(), d.intr.data_ptr(), d.sens.data_ptr(),
+                                     d.targets.data_ptr(), d.weights.data_ptr(), d.eta.data_ptr(), d.ii.data_ptr(),
+                                     d.jj.data_ptr(), N, int(sel.sum()), g.eta.shape[0], g.t0, g.t1, g.lm, g.ep, 0, 0,
+                                     0, d.kx.data_ptr(), len(kx), d.mask.data_ptr(), d.ii_all.data_ptr(),
+                                     d.jj_all.data_ptr(), g.n_edges, None))
+        lo, n = plan.seg_of_rank[r]
+        _gba.check(h, L.gba_ba_set_shard(h, lo, n, int(r == 0)))
+        ranks.append(d)
+    shared_bytes = None
+    for _ in range(iters):
+        views = []
+        for d in ranks:
+            _gba.check(d.h, L.gba_ba_build(d.h))
+            _gba.check(d.h, L.gba_ba_eliminate(d.h))
+            views.append(_gba.system_view(d.h, "cuda:0", 1))
+        assert len(set(v.numel() for v in views)) == 1
+        total = torch.stack(views).sum(dim=0)
+        for v in views:
+            v.copy_(total)
+        shared_bytes = (views[0].numel() * 8, _gba.system_view(ranks[0].h, "cuda:0", 0).numel() * 8)
+        for d in ranks:
+            _gba.check(d.h, L.gba_ba_finish(d.h))
+    torch.cuda.synchronize()
+    poses, disps = ranks[0].poses.cpu().numpy(), ranks[0].disps.cpu().numpy()
+    for r, d in enumerate(ranks[1:], start=1):
+        disps[kx[d.own]] = d.disps.cpu().numpy()[kx[d.own]]
+        mine = np.where(plan.pose_owner == r)[0] + g.t0
+        poses[mine] = d.poses.cpu().numpy()[mine]
+    infos = [_gba.query(d.h) for d in ranks]
+    for d in ranks:
+        L.gba_destroy(d.h)
+    return SimpleNamespace(poses=poses, disps=disps, infos=infos, plan=plan, shared_bytes=shared_bytes)

@@ -16,7 +16,7 @@ from oracle import oracle
 pytestmark = pytest.mark.gpu
 
 import _gba  # noqa: E402
-from gba_run import get_array, run_ba, split_phase, to_dev  # noqa: E402
+from gba_run import get_array, run_ba, segmented, split_phase, to_dev  # noqa: E402
 
 
 # ------------------------------------------------------------------------------------------
@@ -270,23 +270,17 @@ def test_tensor_core_gram_matches_cuda_core_gram(n, ht, wd, monkeypatch):
 
 
 @pytest.mark.parametrize("n,e,r", [(60, 700, 3), (260, 4200, 8)])
-def test_task_graph_factorisation_matches_per_column_launches(n, e, r, monkeypatch):
-    """k_chain (whole factorisation as one dependency graph of tile tasks) against the launch-per-column
-    sequence it replaced: same tiles, same arithmetic, only the order of the atomic closure updates
-    may differ.  The larger graph has several band segments and a closure block."""
+def test_task_graph_factorisation_matches_oracle(n, e, r):
+    """k_chain (the whole factorisation as one dependency graph of tile tasks, several band segments and a
+    closure block in the larger graph) and k_back against the dense fp64 Cholesky of the oracle"""
     g = synth.make_graph(n, e, r, iters=2, seed=n + e, ht=24, wd=32, lm=1e-5, ep=0.01)
-    monkeypatch.setenv("GBA_NO_CHAIN", "1")
-    r0 = run_ba(g)
-    monkeypatch.delenv("GBA_NO_CHAIN")
     r1 = run_ba(g)
-    assert r0.info.chol_failures == 0 and r1.info.chol_failures == 0
+    assert r1.info.chol_failures == 0 and r1.info.watchdog_trips == 0
     assert r1.info.chain_columns <= r1.info.n_tiles
     if n > 200:
         assert r1.info.chain_columns < r1.info.n_tiles  # nested dissection shortened the chain
-    # (870 random graphs: worst 4.3e-6, from the order of the fp64 atomics on the closure tiles)
-    assert rel(sign_normalise(r1.poses), sign_normalise(r0.poses)) < 2e-5
-    assert rel(r1.disps, r0.disps) < 2e-5
-    assert r1.info.kernel_launches < r0.info.kernel_launches
+        assert r1.info.n_segments > 1
+    assert r1.info.kernel_launches < 60
     o = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj, g.t0, g.t1,
                   g.iters, g.lm, g.ep, precision="f64")
     assert rel(sign_normalise(r1.poses), sign_normalise(o.poses)) < STATE_RTOL
@@ -431,6 +425,24 @@ def test_sharded_build_sums_to_single_rank(name):
     assert rel(two.rhs, one.rhs) < 1e-6
     assert rel(sign_normalise(two.poses), sign_normalise(one.poses)) < 1e-5
     assert rel(two.disps, one.disps) < 1e-5
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_segmented_sharded_solve_matches_single_rank(world):
+    """every rank eliminates its own band segments, only the closure block + rhs is summed across ranks, the
+    closure factorisation is replicated: same state as the single-rank call"""
+    g = synth.make_graph(420, 6400, 8, iters=2, seed=77, ht=24, wd=32, lm=1e-5, ep=0.01)
+    one = run_ba(g)
+    seg = segmented(g, world)
+    assert seg is not None and seg.plan.n_segments >= world
+    assert all(i.chol_failures == 0 and i.watchdog_trips == 0 for i in seg.infos)
+    assert seg.shared_bytes[0] < 0.6 * seg.shared_bytes[1]  # the exchanged range is a fraction of the system
+    assert rel(sign_normalise(seg.poses), sign_normalise(one.poses)) < 1e-5
+    assert rel(seg.disps, one.disps) < 1e-5
+    o = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj, g.t0, g.t1,
+                  g.iters, g.lm, g.ep, precision="f64")
+    assert rel(sign_normalise(seg.poses), sign_normalise(o.poses)) < STATE_RTOL
+    assert rel(seg.disps, o.disps) < STATE_RTOL
 
 
 # ------------------------------------------------------------------------------------------
