@@ -9,8 +9,9 @@ A "step" is one `droid_backends.ba` call (`iters` Gauss-Newton iterations, BASEL
 backend setting 2) over one synthetic factor graph.  Default workload: config E (ScanNet-scale
 global BA, 1000 keyframes / 20000 edges / 48x64), the configuration BASELINE.json's metric and
 target are quoted on; it fits one GPU.  At N > 1 the SAME graph is edge-sharded by source keyframe
-over the ranks (strong scaling) with one NCCL all-reduce of the packed reduced camera system per
-iteration.
+over the ranks (strong scaling): every rank owns the keyframes of its band segments of the ordered
+reduced system, eliminates those segments itself, and one NCCL all-reduce per iteration sums the
+closure block + rhs (GBA_REPLICATED_SOLVE=1: the older scheme, whole system all-reduced, solve replicated).
 
 Printed JSON (one line, rank 0): the driver contract plus
   roofline            the dominant HBM kernel: algorithmic bytes of one launch / its CUDA-event time
@@ -401,8 +402,16 @@ def main():
     iters = g.iters
     N, ht, wd = g.disps.shape
     HW = ht * wd
-    kx = sharded.frame_list(g.ii, g.t0, g.t1)
-    owner = sharded.partition(g.ii, kx, world)
+    # ownership: by band segment of the ordered reduced system when the ordering offers enough segments (then only
+    # the closure block crosses ranks), else greedy by out-degree with the whole system all-reduced
+    plan = None
+    if world > 1 and not os.environ.get("GBA_REPLICATED_SOLVE"):
+        kx, plan = sharded.plan(g.ii, g.jj, g.t0, g.t1, N, ht, wd, world, dev)
+    else:
+        kx = sharded.frame_list(g.ii, g.t0, g.t1)
+    owner = plan.owner if plan is not None else sharded.partition(g.ii, kx, world)
+    segments = plan.seg_of_rank[rank] if plan is not None else None
+    pose_owner_t = torch.from_numpy(plan.pose_owner).to(dev) if plan is not None else None
     sel = sharded.local_edges(g.ii, kx, owner, rank)
     E_total, E_local = g.n_edges, int(sel.sum())
     pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
@@ -429,7 +438,8 @@ def main():
                               d["ii"], d["jj"], g.t0, g.t1, iters, g.lm, g.ep, False, False)
         else:
             sharded.ba_sharded(d["poses"], d["disps"], d["intr"], d["sens"], d["targets"], d["weights"], d["eta"],
-                               d["ii"], d["jj"], g.t0, g.t1, iters, g.lm, g.ep, kx_t, owned_t, ii_all, jj_all)
+                               d["ii"], d["jj"], g.t0, g.t1, iters, g.lm, g.ep, kx_t, owned_t, ii_all, jj_all,
+                               segments=segments, pose_owner_t=pose_owner_t)
 
     def barrier():
         if world > 1:
@@ -618,7 +628,7 @@ def main():
                 else:
                     sharded.ba_sharded(bset["poses"], bset["disps"], bset["intr"], bset["sens"], bset["targets"],
                                        bset["weights"], bset["eta"], bset["ii"], bset["jj"], g.t0, g.t1, iters, g.lm,
-                                       g.ep, kx_t, owned_t, ii_all, jj_all)
+                                       g.ep, kx_t, owned_t, ii_all, jj_all, segments=segments, pose_owner_t=pose_owner_t)
                 outs[s_ % 2][0].copy_(bset["poses"], non_blocking=True)
                 outs[s_ % 2][1].copy_(bset["disps"], non_blocking=True)
                 done[s_].record(main)
@@ -683,6 +693,9 @@ def main():
             "config": {"workload": "config %s: global BA, %d keyframes / %d edges / %dx%d, %d iterations per step"
                                    % (args.config, N, E_total, ht, wd, iters),
                        "lm": g.lm, "ep": g.ep, "sharding": "by source keyframe, %d rank(s)" % world,
+                       "solve": ("one rank" if world == 1 else
+                                 "segmented: own band segments per rank, closure block all-reduced (%d segments)" % plan.n_segments
+                                 if plan is not None else "replicated after an all-reduce of the whole system"),
                        "l2": "inputs (%.0f MB per rank) larger than L2" % (input_bytes / 1e6) if l2_flush is None
                              else "256 MB L2 flush between steps"},
             "roofline": roofline, "roofline_iteration": roofline_iteration, "roofline_gram": roofline_gram,
