@@ -61,12 +61,12 @@ def peaks():
         return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}, "fallback (B200_PROFILING.md)"
 
 
-def traffic_of(kernel, config, world):
+def traffic_of(kernel, config, world, what="dram_bytes"):
     """DRAM bytes per launch from an ncu --set full capture of THIS kernel, config and GPU count
     (profiles/traffic.json), else None -- never a number measured on another configuration."""
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            return json.load(f).get("%s_%s_%dgpu_dram_bytes" % (kernel, config, world))
+            return json.load(f).get("%s_%s_%dgpu_%s" % (kernel, config, world, what))
     except Exception:
         return None
 
@@ -522,7 +522,8 @@ def main():
         "frac_linearize_plus_backsub": (b_alg / ((st_ms("linearize") + st_ms("backsub")) * 1e-3) / 1e9 / pk["hbm_gbs"])
         if st_ms("linearize") + st_ms("backsub") > 0 else 0.0,
         "traffic": traffic_of("iteration", args.config, world),
-        "note": "the edge inputs are streamed by k_linearize, the Gram and k_backsub: three passes against B_alg counted once"}
+        "note": "the edge inputs are streamed by k_linearize (targets + weights), the Gram and k_backsub (weights "
+                "only): 32 B per edge pixel against the 16 B of B_alg"}
 
     # The Schur Gram (k_gram_tc) is the GEMM-shaped kernel of the path: G_k = A_k A_k^T per depth keyframe,
     # A_k = [6 deg_k + 1 rows] x [HW pixels].  Algorithmic flops = sum_k R_k (R_k + 1) HW (the symmetric
@@ -554,15 +555,16 @@ def main():
     nb3 = 64.0 ** 3
     chol_flops = 2.0 * nb3 * float((1.0 / 3.0 + col + col * (col + 1) / 2).sum())
     fp64_peak = 2.0 * 64 * 148 * (clocks["sm_mhz"] if clocks and clocks.get("sm_mhz") else 1965.0) * 1e6 / 1e12
-    roofline_chain = {"bound": "dependency chain (fp64 tile Cholesky, CUDA cores)", "kernel": "k_chain",
+    roofline_chain = {"bound": "dependency chain (fp64 tile Cholesky on DMMA)", "kernel": "k_chain",
                       "ms_per_launch": fac_ms, "solve_ms": sol_ms, "sequential_tile_columns": info2.chain_columns,
                       "us_per_column": 1e3 * fac_ms / max(info2.chain_columns, 1), "fp64_flops_executed": chol_flops,
                       "achieved": chol_flops / (fac_ms * 1e-3) / 1e12 if fac_ms > 0 else 0.0, "unit": "TFLOP/s",
                       "peak": fp64_peak, "peak_source": "64 fp64 FMA/clk/SM x 148 SMs x measured SM clock",
                       "frac": chol_flops / (fac_ms * 1e-3) / 1e12 / fp64_peak if fac_ms > 0 else 0.0,
-                      "tensor_pipe_utilisation": 0.0,
-                      "note": "fp64 on the CUDA cores to match the reference's SimplicialLLT<double>; the tensor pipe "
-                              "is not used by this stage (DESIGN.md section 3)"}
+                      "tensor_pipe_utilisation_pct": traffic_of("k_chain", args.config, world, "tensor_pipe_pct"),
+                      "note": "fp64 tile products on the tensor pipe (mma.sync.m8n8k4.f64 = SASS DMMA), whose fp64 rate on "
+                              "B200 equals the DFMA pipe's (64 FMA/clk/SM, profiles/dev); sm__pipe_tensor_cycles_active "
+                              "from the ncu capture named in profiles/traffic.json, null for other configs"}
 
     # ---- N-rank state against the 1-rank state (untimed) -------------------------------------------
     parity_n = None

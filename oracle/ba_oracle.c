@@ -6,12 +6,13 @@
  * ba_oracle_impl.h for the per-function citations.  Built by oracle/Makefile into
  * oracle/liboracle.so and called through ctypes by oracle/oracle.py.
  *
- * Parity pin: checked against outputs of the reference itself --
+ * Parity pin: checked against outputs of the reference itself (tests/test_oracle_golden.py) --
  *   geom_py mode + DSPO : tests/golden/geom_*.npz, produced in the build container by importing
  *                         the reference's src/geom/ba.py on CPU (tests/golden/make_golden.py);
- *   droid_cuda mode     : tests/golden/droid_*.npz, produced on the B200 box by the reference's
- *                         own CUDA droid_backends.ba rebuilt for sm_100 (oracle/build_ref.py,
- *                         tests/golden/make_golden_cuda.py).
+ *   droid_cuda mode and the geometry functions (frame_distance, depth_filter, iproj, projmap):
+ *                         tests/golden/droid_*.npz and geomfn.npz, produced on a B200 by the reference's
+ *                         own CUDA droid_backends rebuilt unmodified for sm_100 (oracle/build_ref.py,
+ *                         tests/golden/make_golden_cuda.py).  Both sets are committed.
  */
 #include <math.h>
 #include <stdint.h>
