@@ -73,6 +73,14 @@ def lib():
         L.gba_iproj.restype = ci
         L.gba_projmap.argtypes = [vp] * 5 + [ci, ci, ci, vp, vp, vp]
         L.gba_projmap.restype = ci
+        L.gba_proximity_scratch_bytes.argtypes = [ci, ci]
+        L.gba_proximity_scratch_bytes.restype = ctypes.c_size_t
+        L.gba_proximity_select.argtypes = [vp, ci, ci, ci, ci, ci, cf, ci, ci, vp, ctypes.c_size_t, vp, vp, ci, vp, vp]
+        L.gba_proximity_select.restype = ci
+        L.gba_valid_depth_mask.argtypes = [vp, vp, ci, ci, ci, ci, vp, vp, vp, vp]
+        L.gba_valid_depth_mask.restype = ci
+        L.gba_mono_filter.argtypes = [vp, vp, vp, vp, ci, ci, ci, cf, vp, vp, ci, ci, vp, vp, vp, vp]
+        L.gba_mono_filter.restype = ci
         L.gba_set_timing.argtypes = [vp, ci]
         L.gba_get_timing.argtypes = [vp, ctypes.POINTER(cf), ctypes.POINTER(ci)]
         L.gba_set_timing.restype = ci

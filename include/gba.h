@@ -255,6 +255,37 @@ int gba_iproj(const float *poses, const float *disps, const float *intrinsics, i
 int gba_projmap(const float *poses, const float *disps, const float *intrinsics, const int64_t *ii, const int64_t *jj,
                 int n_pairs, int ht, int wd, float *coords, float *valid, void *stream);
 
+/* ---- proximity edge selection ------------------------------------------------
+ * Replaces the host loops of FactorGraph.add_backend_proximity_factors (src/factor_graph.py:386-462): thresholds on
+ * the bidirectional frame distance, the local-window edges, sort, greedy selection with suppression of the
+ * (2 nms + 1)^2 neighbourhood, the max_factors cap, and (loop != 0) the loop-closure variant.
+ *   d [ilen*jlen]  0.5 (frame_distance(i->j) + frame_distance(j->i)) for i in [t_start_loop, t_end) (rows) and
+ *                  j in [t_start, t_end) (columns), as DepthVideo.distance returns it (src/depth_video.py:166-196);
+ *                  loop == 0 forces t_start_loop = t_start like the reference.  Not modified.
+ *   scratch        gba_proximity_scratch_bytes(ilen, jlen) bytes of device memory
+ *   out_ii/out_jj  [cap] int32 edge list in the reference's order; out_n[0] = edges written, out_n[1] = 0, or 1 when
+ *                  the reference returns without adding edges (fewer than 3, or no loop edge), or 2 when cap was too small
+ * One CTA; equal distances are taken in ascending pair index (a stable sort).  Asynchronous on `stream`. */
+size_t gba_proximity_scratch_bytes(int ilen, int jlen);
+int gba_proximity_select(const float *d, int t_start, int t_start_loop, int t_end, int nms, int radius, float thresh,
+                         int max_factors, int loop, void *scratch, size_t scratch_bytes, int *out_ii, int *out_jj,
+                         int cap, int *out_n, void *stream);
+
+/* ---- valid-depth mask and mono_thres edge filter -----------------------------
+ * gba_valid_depth_mask replaces src/depth_video.py:340-361 after depth_filter: per listed keyframe, depth = 1 / disp,
+ * pixels with count < visible_num dropped, median = torch.nanmedian (lower middle value), mask = depth < 3 median.
+ *   disps, count [n,ht,wd] (the selected keyframes' rows); mask [n,ht,wd] one byte per pixel;
+ *   valid_cnt [n] = mask.sum(), mean_disp [n] = disps.mean() per keyframe (inputs of the filter below).
+ * gba_mono_filter replaces the loops of src/depth_video.py:245-261: invalid[f] = error/avg_disp > mono_thres | isnan(error)
+ * | scale < 0 | valid_cnt < ht*wd/2 for the first n keyframes; keep[e] = neither end of edge e is invalid;
+ * src_kept[f] (f < n_frames) = f is still the source of a kept edge (eta rows follow unique(ii): mask them with it).
+ * Device pointers, asynchronous on `stream`, no gba_ctx. */
+int gba_valid_depth_mask(const float *disps, const float *count, int n, int ht, int wd, int visible_num, uint8_t *mask,
+                         int *valid_cnt, float *mean_disp, void *stream);
+int gba_mono_filter(const float *error, const float *avg_disp, const float *scale, const int *valid_cnt, int n, int ht,
+                    int wd, float mono_thres, const int64_t *ii, const int64_t *jj, int n_edges, int n_frames,
+                    uint8_t *invalid, uint8_t *keep, uint8_t *src_kept, void *stream);
+
 /* ---- per-edge pose blocks for callers that cannot allocate --------------------------------
  * No counterpart in the reference: there, these numbers only exist inside ba_cuda.
  *

@@ -212,3 +212,61 @@ def dispatcher_case(seed=0, n=24, e=140, r=4, ht=24, wd=32, buf=32):
     pbuf = pad(g.poses)
     pbuf[n:, 6] = 1.0
     return g, pbuf, pad(g.disps), pad(g.mono_disps)
+
+
+# ---- proximity edge selection (reference src/factor_graph.py:386-462) -------------------------------------
+# name: (keyframes, (ht, wd), seed, t_start, t_start_loop, nms, radius, thresh, max_factors, loop)
+PROX_CASES = {
+    "global": (60, (16, 24), 1, 0, None, 2, 2, 12.0, 400, False),
+    "capped": (60, (16, 24), 2, 0, None, 1, 3, 30.0, 520, False),
+    "window": (48, (16, 24), 3, 4, 20, 2, 2, 14.0, 10 ** 6, False),
+    "loop": (64, (16, 24), 4, 0, 30, 2, 2, 14.0, 10 ** 6, True),
+}
+
+
+def prox_distances(n, hw, seed, t_start, t_loop, loop=False):
+    """a trajectory that revisits places (a slow circle) so that far-apart keyframes are close again; returns
+    poses, disps, intrinsics and the bidirectional frame distance of every (i in [t_loop, n), j in [t_start, n))
+    pair as the reference's DepthVideo.distance computes it (float32)"""
+    from oracle import oracle
+
+    ht, wd = hw
+    rng = np.random.default_rng(900 + seed)
+    intr = np.array([0.9 * wd, 0.9 * wd, wd / 2.0 - 0.5, ht / 2.0 - 0.5], dtype=np.float32)
+    poses = np.zeros((n, 7), dtype=np.float64)
+    ang = 2 * np.pi * np.arange(n) / (0.45 * n)  # a bit more than two laps
+    poses[:, 0] = 0.6 * np.cos(ang) + rng.normal(0, 0.01, n)
+    poses[:, 1] = 0.6 * np.sin(ang) + rng.normal(0, 0.01, n)
+    poses[:, 2] = rng.normal(0, 0.01, n)
+    poses[:, 6] = 1.0
+    disps = rng.uniform(0.2, 0.3, size=(n, ht, wd)).astype(np.float32)
+    t_loop = t_start if (t_loop is None or not loop) else t_loop  # factor_graph.py:387-388
+    ii, jj = np.meshgrid(np.arange(t_loop, n), np.arange(t_start, n), indexing="ij")
+    ii, jj = ii.reshape(-1), jj.reshape(-1)
+    p32 = poses.astype(np.float32)
+    d1 = oracle.frame_distance(p32, disps, intr, ii, jj, 0.25, precision="f32")
+    d2 = oracle.frame_distance(p32, disps, intr, jj, ii, 0.25, precision="f32")
+    return p32, disps, intr, (np.float32(0.5) * (d1 + d2)).astype(np.float32)
+
+
+def mask_case(seed=0, n=14, ht=24, wd=32):
+    """inputs of the valid-depth mask / mono_thres filter fixtures: disparities with far outliers, vote counts
+    0..6, one keyframe without any surviving pixel, one with an even and one with an odd number of survivors"""
+    rng = np.random.default_rng(700 + seed)
+    disps = rng.uniform(0.2, 1.5, size=(n, ht, wd)).astype(np.float32)
+    disps[rng.uniform(size=disps.shape) < 0.05] *= 0.02      # very far points: depth > 3 median
+    count = rng.integers(0, 7, size=(n, ht, wd)).astype(np.float32)
+    count[3] = 0.0                                            # nothing survives: nanmedian of all-NaN
+    count[4].reshape(-1)[:] = 0.0
+    count[4].reshape(-1)[:10] = 6.0                           # even number of survivors
+    count[5].reshape(-1)[:] = 0.0
+    count[5].reshape(-1)[:11] = 6.0                           # odd number
+    count[6][: ht // 2 + 4] = 0.0                             # fewer than half of the pixels valid
+    error = rng.uniform(0.0, 0.2, size=n).astype(np.float32)
+    error[7] = np.nan
+    scale = rng.uniform(0.5, 1.5, size=n).astype(np.float32)
+    scale[8] = -0.3
+    e = 60
+    ii = rng.integers(0, n + 2, size=e).astype(np.int64)      # some edges touch keyframes beyond the first n
+    jj = rng.integers(0, n + 2, size=e).astype(np.int64)
+    return disps, count, error, scale, ii, jj

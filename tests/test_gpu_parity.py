@@ -812,6 +812,13 @@ def test_dispatcher_depth_scale_branch():
     eta = g.eta[: len(kx_all)]
     v.ba(target, weight, t(eta), t(g.ii), t(g.jj), t0=g.t0, t1=None, iters=2, lm=g.lm, ep=g.ep, opt_type="depth_scale")
     assert v.calls == ["depth_scale"]
+    # the device versions of the two Python loops of this branch (video_ops) against what the torch statements gave
+    import video_ops
+
+    m_dev, cnt_dev, mean_dev = video_ops.valid_depth_mask(t(poses), t(disps), t(g.intrinsics), torch.arange(n).cuda(),
+                                                          v.mv_thresh, v.visible_num)
+    assert torch.equal(m_dev, v.valid_depth_mask_small[:n])
+    assert torch.equal(cnt_dev.long(), v.valid_depth_mask_small[:n].sum(dim=[1, 2]))
     # ---- the same steps on the CPU oracle ----
     depths = 1.0 / disps[:n].astype(np.float64)
     thresh = (v.mv_thresh * depths.mean(axis=(1, 2))).astype(np.float32)
@@ -831,6 +838,11 @@ def test_dispatcher_depth_scale_branch():
     ii_t, jj_t = g.ii[~drop], g.jj[~drop]
     np.testing.assert_array_equal(v.last_filter[0].cpu().numpy(), ii_t)
     np.testing.assert_array_equal(v.last_filter[1].cpu().numpy(), jj_t)
+    inv_dev, keep_dev, src_dev = video_ops.mono_filter(t(e.astype(np.float32)), mean_dev, t(s.astype(np.float32)), cnt_dev,
+                                                       g.disps.shape[1], g.disps.shape[2], v.mono_thres, t(g.ii), t(g.jj),
+                                                       poses.shape[0])
+    np.testing.assert_array_equal(inv_dev.cpu().numpy(), invalid)
+    np.testing.assert_array_equal(keep_dev.cpu().numpy(), ~drop)
     eta_t = eta[np.isin(kx_all, np.unique(ii_t))]
     assert v.last_filter[2] == eta_t.shape[0]
     tg = np.ascontiguousarray(g.targets.transpose(0, 2, 3, 1))[~drop]
