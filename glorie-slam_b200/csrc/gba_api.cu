@@ -467,6 +467,10 @@ extern "C" int gba_ba_build(gba_ctx *c) {
       }
       gs_cc = std::max(c->gsplit, std::min(16, ntile));
     }
+    // GBA_DETERMINISTIC=1 (parity runs): one CTA per keyframe in both Gram kernels, so that no fp32 sum is merged by
+    // atomics and the fp32 inputs of the reduced system are reproducible run to run (slower when there are fewer
+    // keyframes than SMs).  The remaining unordered sums are fp64 (pose blocks, Schur assembly, closure tiles, rhs).
+    if (getenv("GBA_DETERMINISTIC")) gs_tc = gs_cc = 1;
     const bool need_cc = st.max_deg > p.tc_maxdeg;
     if ((p.tc_maxdeg > 0 && gs_tc > 1) || (need_cc && gs_cc > 1))
       CK(cudaMemsetAsync(c->gram, 0, (size_t)st.gram_floats * sizeof(float), s));

@@ -99,6 +99,30 @@ __device__ __forceinline__ double *sys_at(const BaParams &p, int r, int c) {
   return p.sys + (size_t)slot * GBA_NB2 + (r % GBA_NB) * GBA_NB + (c % GBA_NB);
 }
 
+// Relative pose G_ij = T_j * T_i^-1 of two keyframes stored as (t, q xyzw): quaternion q and translation t
+// (relSE3 + actSO3 of droid_kernels.cu:58-68,96-107; the only place this formula lives).
+__device__ __forceinline__ void rel_se3(const float *Pi, const float *Pj, float (&q)[4], float (&t)[3]) {
+  const float *qi = Pi + 3, *qj = Pj + 3;
+  q[0] = -qj[3] * qi[0] + qj[0] * qi[3] - qj[1] * qi[2] + qj[2] * qi[1];
+  q[1] = -qj[3] * qi[1] + qj[1] * qi[3] - qj[2] * qi[0] + qj[0] * qi[2];
+  q[2] = -qj[3] * qi[2] + qj[2] * qi[3] - qj[0] * qi[1] + qj[1] * qi[0];
+  q[3] = qj[3] * qi[3] + qj[0] * qi[0] + qj[1] * qi[1] + qj[2] * qi[2];
+  // t_ij = t_j - q_ij * t_i
+  const float uv0 = 2.f * (q[1] * Pi[2] - q[2] * Pi[1]);
+  const float uv1 = 2.f * (q[2] * Pi[0] - q[0] * Pi[2]);
+  const float uv2 = 2.f * (q[0] * Pi[1] - q[1] * Pi[0]);
+  t[0] = Pj[0] - (Pi[0] + q[3] * uv0 + (q[1] * uv2 - q[2] * uv1));
+  t[1] = Pj[1] - (Pi[1] + q[3] * uv1 + (q[2] * uv0 - q[0] * uv2));
+  t[2] = Pj[2] - (Pi[2] + q[3] * uv2 + (q[0] * uv1 - q[1] * uv0));
+}
+// rotation matrix (row major) equivalent to the quaternion sandwich X + w uv + q x uv, uv = 2 q x X
+__device__ __forceinline__ void quat_to_rot(const float (&q)[4], float *R) {
+  const float x = q[0], y = q[1], z = q[2], w = q[3];
+  R[0] = 1.f - 2.f * (y * y + z * z); R[1] = 2.f * (x * y - w * z); R[2] = 2.f * (x * z + w * y);
+  R[3] = 2.f * (x * y + w * z); R[4] = 1.f - 2.f * (x * x + z * z); R[5] = 2.f * (y * z - w * x);
+  R[6] = 2.f * (x * z - w * y); R[7] = 2.f * (y * z + w * x); R[8] = 1.f - 2.f * (x * x + y * y);
+}
+
 // y = B x with B = -Ad(G_ij)^T  (J_i = B J_j; droid_kernels.cu:79-94,325-326; se3.h:58-67,84-86)
 template <typename T>
 __device__ __forceinline__ void apply_B(const float *R, const float *t, const T *x, T *y) {

@@ -63,22 +63,9 @@ __global__ void __launch_bounds__(FD_NT) k_frame_distance(const float *__restric
     // G_ij = T_j * T_i^-1 (relSE3, droid_kernels.cu:96-107), every thread for itself
     float R[9], t[3];
     {
-      const float *Pi = poses + 7 * (size_t)i, *Pj = poses + 7 * (size_t)j, *qi = Pi + 3, *qj = Pj + 3;
       float qq[4];
-      qq[0] = -qj[3] * qi[0] + qj[0] * qi[3] - qj[1] * qi[2] + qj[2] * qi[1];
-      qq[1] = -qj[3] * qi[1] + qj[1] * qi[3] - qj[2] * qi[0] + qj[0] * qi[2];
-      qq[2] = -qj[3] * qi[2] + qj[2] * qi[3] - qj[0] * qi[1] + qj[1] * qi[0];
-      qq[3] = qj[3] * qi[3] + qj[0] * qi[0] + qj[1] * qi[1] + qj[2] * qi[2];
-      const float uv0 = 2.f * (qq[1] * Pi[2] - qq[2] * Pi[1]);
-      const float uv1 = 2.f * (qq[2] * Pi[0] - qq[0] * Pi[2]);
-      const float uv2 = 2.f * (qq[0] * Pi[1] - qq[1] * Pi[0]);
-      t[0] = Pj[0] - (Pi[0] + qq[3] * uv0 + (qq[1] * uv2 - qq[2] * uv1));
-      t[1] = Pj[1] - (Pi[1] + qq[3] * uv1 + (qq[2] * uv0 - qq[0] * uv2));
-      t[2] = Pj[2] - (Pi[2] + qq[3] * uv2 + (qq[0] * uv1 - qq[1] * uv0));
-      const float x = qq[0], y = qq[1], zq = qq[2], w = qq[3];
-      R[0] = 1.f - 2.f * (y * y + zq * zq); R[1] = 2.f * (x * y - w * zq); R[2] = 2.f * (x * zq + w * y);
-      R[3] = 2.f * (x * y + w * zq); R[4] = 1.f - 2.f * (x * x + zq * zq); R[5] = 2.f * (y * zq - w * x);
-      R[6] = 2.f * (x * zq - w * y); R[7] = 2.f * (y * zq + w * x); R[8] = 1.f - 2.f * (x * x + y * y);
+      rel_se3(poses + 7 * (size_t)i, poses + 7 * (size_t)j, qq, t);
+      quat_to_rot(qq, R);
     }
     float accum = 0.f, valid = 0.f;
 #pragma unroll
@@ -183,18 +170,9 @@ __global__ void __launch_bounds__(DF_NT) k_depth_filter(const float *__restrict_
     const bool ok = jx >= 0 && jx < n_frames;
     s_rel[tid][7] = ok ? 1.f : 0.f;
     if (ok) {
-      const float *Pi = poses + 7 * (size_t)ix, *Pj = poses + 7 * (size_t)jx, *qi = Pi + 3, *qj = Pj + 3;
-      float qq[4];
-      qq[0] = -qj[3] * qi[0] + qj[0] * qi[3] - qj[1] * qi[2] + qj[2] * qi[1];
-      qq[1] = -qj[3] * qi[1] + qj[1] * qi[3] - qj[2] * qi[0] + qj[0] * qi[2];
-      qq[2] = -qj[3] * qi[2] + qj[2] * qi[3] - qj[0] * qi[1] + qj[1] * qi[0];
-      qq[3] = qj[3] * qi[3] + qj[0] * qi[0] + qj[1] * qi[1] + qj[2] * qi[2];
-      const float uv0 = 2.f * (qq[1] * Pi[2] - qq[2] * Pi[1]);
-      const float uv1 = 2.f * (qq[2] * Pi[0] - qq[0] * Pi[2]);
-      const float uv2 = 2.f * (qq[0] * Pi[1] - qq[1] * Pi[0]);
-      s_rel[tid][0] = Pj[0] - (Pi[0] + qq[3] * uv0 + (qq[1] * uv2 - qq[2] * uv1));
-      s_rel[tid][1] = Pj[1] - (Pi[1] + qq[3] * uv1 + (qq[2] * uv0 - qq[0] * uv2));
-      s_rel[tid][2] = Pj[2] - (Pi[2] + qq[3] * uv2 + (qq[0] * uv1 - qq[1] * uv0));
+      float qq[4], tt[3];
+      rel_se3(poses + 7 * (size_t)ix, poses + 7 * (size_t)jx, qq, tt);
+      s_rel[tid][0] = tt[0]; s_rel[tid][1] = tt[1]; s_rel[tid][2] = tt[2];
       s_rel[tid][3] = qq[0]; s_rel[tid][4] = qq[1]; s_rel[tid][5] = qq[2]; s_rel[tid][6] = qq[3];
     }
   }
@@ -377,18 +355,9 @@ __global__ void __launch_bounds__(PJ_NT) k_projmap(const float *__restrict__ pos
   __shared__ float s_rel[8];
   const int n = blockIdx.y, ix = (int)ii[n], jx = (int)jj[n];
   if (threadIdx.x == 0) {  // relSE3 (droid_kernels.cu:96-107)
-    const float *Pi = poses + 7 * (size_t)ix, *Pj = poses + 7 * (size_t)jx, *qi = Pi + 3, *qj = Pj + 3;
-    float qq[4];
-    qq[0] = -qj[3] * qi[0] + qj[0] * qi[3] - qj[1] * qi[2] + qj[2] * qi[1];
-    qq[1] = -qj[3] * qi[1] + qj[1] * qi[3] - qj[2] * qi[0] + qj[0] * qi[2];
-    qq[2] = -qj[3] * qi[2] + qj[2] * qi[3] - qj[0] * qi[1] + qj[1] * qi[0];
-    qq[3] = qj[3] * qi[3] + qj[0] * qi[0] + qj[1] * qi[1] + qj[2] * qi[2];
-    const float uv0 = 2.f * (qq[1] * Pi[2] - qq[2] * Pi[1]);
-    const float uv1 = 2.f * (qq[2] * Pi[0] - qq[0] * Pi[2]);
-    const float uv2 = 2.f * (qq[0] * Pi[1] - qq[1] * Pi[0]);
-    s_rel[0] = Pj[0] - (Pi[0] + qq[3] * uv0 + (qq[1] * uv2 - qq[2] * uv1));
-    s_rel[1] = Pj[1] - (Pi[1] + qq[3] * uv1 + (qq[2] * uv0 - qq[0] * uv2));
-    s_rel[2] = Pj[2] - (Pi[2] + qq[3] * uv2 + (qq[0] * uv1 - qq[1] * uv0));
+    float qq[4], tt[3];
+    rel_se3(poses + 7 * (size_t)ix, poses + 7 * (size_t)jx, qq, tt);
+    s_rel[0] = tt[0]; s_rel[1] = tt[1]; s_rel[2] = tt[2];
     s_rel[3] = qq[0]; s_rel[4] = qq[1]; s_rel[5] = qq[2]; s_rel[6] = qq[3];
   }
   __syncthreads();

@@ -218,31 +218,9 @@ __global__ void k_edge_geo(BaParams p) {
     t[1] = t[2] = 0.f;
     g.flags = 1;
   } else {
-    const float *Pi = p.poses + 7 * (size_t)i, *Pj = p.poses + 7 * (size_t)j;
-    const float *qi = Pi + 3, *qj = Pj + 3;
-    q[0] = -qj[3] * qi[0] + qj[0] * qi[3] - qj[1] * qi[2] + qj[2] * qi[1];
-    q[1] = -qj[3] * qi[1] + qj[1] * qi[3] - qj[2] * qi[0] + qj[0] * qi[2];
-    q[2] = -qj[3] * qi[2] + qj[2] * qi[3] - qj[0] * qi[1] + qj[1] * qi[0];
-    q[3] = qj[3] * qi[3] + qj[0] * qi[0] + qj[1] * qi[1] + qj[2] * qi[2];
-    // t_ij = t_j - q_ij * t_i  (actSO3, droid_kernels.cu:58-68)
-    const float uv0 = 2.f * (q[1] * Pi[2] - q[2] * Pi[1]);
-    const float uv1 = 2.f * (q[2] * Pi[0] - q[0] * Pi[2]);
-    const float uv2 = 2.f * (q[0] * Pi[1] - q[1] * Pi[0]);
-    t[0] = Pj[0] - (Pi[0] + q[3] * uv0 + (q[1] * uv2 - q[2] * uv1));
-    t[1] = Pj[1] - (Pi[1] + q[3] * uv1 + (q[2] * uv0 - q[0] * uv2));
-    t[2] = Pj[2] - (Pi[2] + q[3] * uv2 + (q[0] * uv1 - q[1] * uv0));
+    rel_se3(p.poses + 7 * (size_t)i, p.poses + 7 * (size_t)j, q, t);
   }
-  // rotation matrix equivalent to the quaternion sandwich X + w*uv + q x uv, uv = 2 q x X
-  const float x = q[0], y = q[1], z = q[2], w = q[3];
-  g.R[0] = 1.f - 2.f * (y * y + z * z);
-  g.R[1] = 2.f * (x * y - w * z);
-  g.R[2] = 2.f * (x * z + w * y);
-  g.R[3] = 2.f * (x * y + w * z);
-  g.R[4] = 1.f - 2.f * (x * x + z * z);
-  g.R[5] = 2.f * (y * z - w * x);
-  g.R[6] = 2.f * (x * z - w * y);
-  g.R[7] = 2.f * (y * z + w * x);
-  g.R[8] = 1.f - 2.f * (x * x + y * y);
+  quat_to_rot(q, g.R);
   g.t[0] = t[0];
   g.t[1] = t[1];
   g.t[2] = t[2];

@@ -67,22 +67,9 @@ __global__ void __launch_bounds__(SB_NT) k_edge_blocks_static(const float *__res
       q[0] = q[1] = q[2] = 0.f; q[3] = 1.f;
       t[0] = -0.1f; t[1] = t[2] = 0.f;
     } else {
-      const float *Pi = poses + 7 * (size_t)i, *Pj = poses + 7 * (size_t)j, *qi = Pi + 3, *qj = Pj + 3;
-      q[0] = -qj[3] * qi[0] + qj[0] * qi[3] - qj[1] * qi[2] + qj[2] * qi[1];
-      q[1] = -qj[3] * qi[1] + qj[1] * qi[3] - qj[2] * qi[0] + qj[0] * qi[2];
-      q[2] = -qj[3] * qi[2] + qj[2] * qi[3] - qj[0] * qi[1] + qj[1] * qi[0];
-      q[3] = qj[3] * qi[3] + qj[0] * qi[0] + qj[1] * qi[1] + qj[2] * qi[2];
-      const float uv0 = 2.f * (q[1] * Pi[2] - q[2] * Pi[1]);
-      const float uv1 = 2.f * (q[2] * Pi[0] - q[0] * Pi[2]);
-      const float uv2 = 2.f * (q[0] * Pi[1] - q[1] * Pi[0]);
-      t[0] = Pj[0] - (Pi[0] + q[3] * uv0 + (q[1] * uv2 - q[2] * uv1));
-      t[1] = Pj[1] - (Pi[1] + q[3] * uv1 + (q[2] * uv0 - q[0] * uv2));
-      t[2] = Pj[2] - (Pi[2] + q[3] * uv2 + (q[0] * uv1 - q[1] * uv0));
+      rel_se3(poses + 7 * (size_t)i, poses + 7 * (size_t)j, q, t);
     }
-    const float x = q[0], y = q[1], z = q[2], w = q[3];
-    s_R[0] = 1.f - 2.f * (y * y + z * z); s_R[1] = 2.f * (x * y - w * z); s_R[2] = 2.f * (x * z + w * y);
-    s_R[3] = 2.f * (x * y + w * z); s_R[4] = 1.f - 2.f * (x * x + z * z); s_R[5] = 2.f * (y * z - w * x);
-    s_R[6] = 2.f * (x * z - w * y); s_R[7] = 2.f * (y * z + w * x); s_R[8] = 1.f - 2.f * (x * x + y * y);
+    quat_to_rot(q, s_R);
     s_t[0] = t[0]; s_t[1] = t[1]; s_t[2] = t[2];
     s_stereo = (i == j) || !in_range;
   }

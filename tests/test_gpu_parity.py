@@ -711,6 +711,23 @@ def test_geom_mode_clamps_every_row():
     assert rel(r.disps, o.disps) < STATE_RTOL
 
 
+def test_deterministic_switch(monkeypatch):
+    """GBA_DETERMINISTIC=1 removes the fp32 atomics (pixel splits of the Gram kernels): what is left are unordered
+    fp64 sums, far below fp32 resolution -- two runs then give the same fp32 state to 1e-7 (bitwise in practice),
+    and the same state as the default path within the noise allowance the other tests use (1e-5)"""
+    g = small_graphs()["B"]  # 20 keyframes: the default path splits every keyframe's pixels over several CTAs
+    monkeypatch.setenv("GBA_DETERMINISTIC", "1")
+    a, b = run_ba(g), run_ba(g)
+    monkeypatch.delenv("GBA_DETERMINISTIC")
+    c = run_ba(g)
+    assert rel(a.poses, b.poses) < 1e-7 and rel(a.disps, b.disps) < 1e-7
+    assert rel(c.poses, a.poses) < 1e-5 and rel(c.disps, a.disps) < 1e-5
+    o = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj, g.t0, g.t1,
+                  g.iters, g.lm, g.ep, precision="f64")
+    assert rel(sign_normalise(a.poses), sign_normalise(o.poses)) < STATE_RTOL and rel(a.disps, o.disps) < STATE_RTOL
+    print("deterministic runs bitwise equal:", np.array_equal(a.poses, b.poses) and np.array_equal(a.disps, b.disps))
+
+
 # ------------------------------------------------------------------------------------------
 # boundary hardening
 # ------------------------------------------------------------------------------------------
