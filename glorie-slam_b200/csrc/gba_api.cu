@@ -377,15 +377,12 @@ extern "C" int gba_ba_begin(gba_ctx *c, float *poses, float *disps, const float 
     if ((size_t)2 * GRAM_T * RS * sizeof(float) + (size_t)st.max_deg * 68 > (size_t)kGramSmemMax)
       return fail_msg(c, GBA_ECAPACITY, "out-degree %d too large for the shared-memory Gram tile", st.max_deg);
   }
-  // launch shape of the streaming passes: largest CTA footprint that still gives >= 2 CTAs per SM
+  // launch shape of the streaming passes (measured at config E: 128 threads x 8 pixels beats 256 x 8 for the
+  // linearisation, 0.39 vs 0.42 ms, and 128 x 4 is best for the back-substitution, 0.14 vs 0.19 ms):
+  // k_linearize takes the 1024-pixel footprint when that still gives >= 2 CTAs per SM, else 512; k_backsub always 512
   const int K = std::max(st.K, 1), want = 2 * c->sm_count;
   const int foot[3] = {2048, 1024, 512};
-  c->variant = 2;
-  for (int v = 0; v < 3; v++)
-    if ((long long)K * ((c->HW + foot[v] - 1) / foot[v]) >= want) {
-      c->variant = v;
-      break;
-    }
+  c->variant = ((long long)K * ((c->HW + 1023) / 1024) >= want) ? 1 : 2;
   p.nchunk = (c->HW + foot[c->variant] - 1) / foot[c->variant];
   const int ntile = (c->HW + GRAM_T - 1) / GRAM_T;
   // Gram CTAs per keyframe: enough CTAs to fill the GPU (2 resident per SM), and among the small
@@ -575,14 +572,9 @@ static int solve_tail(gba_ctx *c, bool sharded) {
   stage_end(c);
   if (!p.motion_only && st.K > 0) {
     stage_begin(c, GBA_STAGE_BACKSUB);
-    dim3 grid(p.nchunk, st.K);
-    // (semantics mode, layout) x (CTA footprint): compile-time variants, chosen once per launch
-#define GBA_LAUNCH_K_BACKSUB(MODE, IL)                                                    \
-  do {                                                                                   \
-    if (c->variant == 0) k_backsub<256, 2, MODE, IL><<<grid, 256, 0, s>>>(p);            \
-    else if (c->variant == 1) k_backsub<128, 2, MODE, IL><<<grid, 128, 0, s>>>(p);       \
-    else k_backsub<128, 1, MODE, IL><<<grid, 128, 0, s>>>(p);                            \
-  } while (0)
+    dim3 grid((c->HW + 511) / 512, st.K);
+    // (semantics mode, layout): compile-time variants, chosen once per launch
+#define GBA_LAUNCH_K_BACKSUB(MODE, IL) k_backsub<128, 1, MODE, IL><<<grid, 128, 0, s>>>(p)
     if (p.mode == 0 && !p.il) GBA_LAUNCH_K_BACKSUB(0, false);
     else if (p.mode == 0) GBA_LAUNCH_K_BACKSUB(0, true);
     else if (!p.il) GBA_LAUNCH_K_BACKSUB(1, false);

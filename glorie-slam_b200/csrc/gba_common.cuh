@@ -277,6 +277,85 @@ __device__ __forceinline__ unsigned long long mul2(unsigned long long a, unsigne
   return r;
 }
 
+__device__ __forceinline__ unsigned long long add2(unsigned long long a, unsigned long long b) {
+  unsigned long long r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ unsigned long long fma2r(unsigned long long a, unsigned long long b, unsigned long long c) {
+  unsigned long long r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ unsigned long long dup2(float v) { return pack2(v, v); }
+
+// ---------------------------------------------------------------------------------------------
+// pix_hat for TWO pixels of one edge at once (same image row, consecutive columns): every fp32 operation of the
+// scalar version becomes one packed f32x2 instruction on the pair -- the same roundings in the same order, half
+// the issue slots (these kernels are bound by instruction issue, not by HBM).  Signs are not materialised:
+// ju' = (e, 0, -ae, -ab, opa, -b), jv' = (0, e, -be, -opb, ab, a); consumers negate the constant operand instead.
+// ---------------------------------------------------------------------------------------------
+struct EdgeConst2 {  // per edge, packed (v, v)
+  unsigned long long R0, R1, R2, R3, R4, R5, R6, R7, R8, t0, t1, t2, nt2;
+};
+__device__ __forceinline__ EdgeConst2 make_edge_const2(const float *R, const float *t) {
+  EdgeConst2 c;
+  c.R0 = dup2(R[0]); c.R1 = dup2(R[1]); c.R2 = dup2(R[2]); c.R3 = dup2(R[3]); c.R4 = dup2(R[4]); c.R5 = dup2(R[5]);
+  c.R6 = dup2(R[6]); c.R7 = dup2(R[7]); c.R8 = dup2(R[8]); c.t0 = dup2(t[0]); c.t1 = dup2(t[1]); c.t2 = dup2(t[2]);
+  c.nt2 = dup2(-t[2]);
+  return c;
+}
+struct PixHat2 {
+  unsigned long long wu, wv, jzu, jzv;           // folded weights (0 where invalid), jz'
+  unsigned long long e, a, b, ae, ab, be, opa, opb;
+  unsigned long long X, Y, d;                     // for the residuals (pix_res2)
+};
+template <int MODE>
+__device__ __forceinline__ void pix_hat2(const EdgeConst2 &c, const PixConst &k, unsigned long long x2, float y0,
+                                         unsigned long long z2, unsigned long long wgu2, unsigned long long wgv2,
+                                         PixHat2 &o) {
+  const unsigned long long y2 = dup2(y0);
+  o.X = fma2r(c.R0, x2, fma2r(c.R1, y2, fma2r(c.t0, z2, c.R2)));
+  o.Y = fma2r(c.R3, x2, fma2r(c.R4, y2, fma2r(c.t1, z2, c.R5)));
+  const unsigned long long Z = fma2r(c.R6, x2, fma2r(c.R7, y2, fma2r(c.t2, z2, c.R8)));
+  float Z0, Z1;
+  unpack2(Z, Z0, Z1);
+  bool i0, i1;
+  float d0, d1;
+  if (MODE == 0) {  // droid_kernels.cu:26,302-306
+    i0 = Z0 < 0.25f; i1 = Z1 < 0.25f;
+    d0 = i0 ? 0.0f : __fdividef(1.0f, Z0);
+    d1 = i1 ? 0.0f : __fdividef(1.0f, Z1);
+  } else {  // projective_ops.py:44,112
+    i0 = !(Z0 > 0.2f); i1 = !(Z1 > 0.2f);
+    d0 = (Z0 < 0.1f) ? 1.0f : __fdividef(1.0f, Z0);
+    d1 = (Z1 < 0.1f) ? 1.0f : __fdividef(1.0f, Z1);
+  }
+  o.d = pack2(d0, d1);
+  o.a = mul2(o.X, o.d);
+  o.b = mul2(o.Y, o.d);
+  o.e = mul2(z2, o.d);
+  const unsigned long long gate = pack2(i0 ? 0.0f : 1.0f, i1 ? 0.0f : 1.0f);
+  // invalid ? 0 : kw * wg  ==  (kw * wg) * gate exactly (gate is 0 or 1; kw * wg is finite)
+  o.wu = mul2(mul2(dup2(k.kwu), wgu2), gate);
+  o.wv = mul2(mul2(dup2(k.kwv), wgv2), gate);
+  o.ab = mul2(o.a, o.b);
+  o.ae = mul2(o.a, o.e);
+  o.be = mul2(o.b, o.e);
+  const unsigned long long one = dup2(1.0f);
+  o.opa = fma2r(o.a, o.a, one);
+  o.opb = fma2r(o.b, o.b, one);
+  o.jzu = mul2(o.d, fma2r(c.nt2, o.a, c.t0));
+  o.jzv = mul2(o.d, fma2r(c.nt2, o.b, c.t1));
+}
+// residuals / fx, fy of the pair: ru' = (tu * ifx - cx/fx) - a
+__device__ __forceinline__ void pix_res2(const PixHat2 &o, const PixConst &k, unsigned long long tu2,
+                                         unsigned long long tv2, unsigned long long &ru, unsigned long long &rv) {
+  const unsigned long long m1 = dup2(-1.0f);
+  ru = fma2r(o.a, m1, fma2r(tu2, dup2(k.ifx), dup2(-k.cxf)));
+  rv = fma2r(o.b, m1, fma2r(tv2, dup2(k.ify), dup2(-k.cyf)));
+}
+
 // Sum NV (<= 32) per-lane values across the warp so that lane l ends up holding the total of
 // v[l]: 31 shuffles instead of 5 per value (butterfly that halves the live values per stage).
 __device__ __forceinline__ float warp_transpose_reduce32(float (&v)[32], int lane) {

@@ -853,7 +853,7 @@ __global__ void k_damp(BaParams p, float lm, float ep, int seg_lo, int seg_n, in
 // Replaces EvT6x1 + accum + disp_retr (droid_kernels.cu:1095-1115,1409-1418,933-946,1428-1431).
 // --------------------------------------------------------------------------------------------
 template <int NT, int NV, int MODE, bool IL>
-__global__ void __launch_bounds__(NT) k_backsub(BaParams p) {
+__global__ void __launch_bounds__(NT, (NT >= 256) ? 3 : 6) k_backsub(BaParams p) {
   __shared__ EdgeGeo s_geo[LIN_EB];
   __shared__ float s_delta[LIN_EB][8];
   __shared__ int s_eid[LIN_EB];
@@ -869,18 +869,24 @@ __global__ void __launch_bounds__(NT) k_backsub(BaParams p) {
   const int lo = (MODE == 0) ? 1 : 0;
   const bool kvalid = (pcr >= lo && pcr < p.P);
 
+  // pixels are handled as PAIRS (px, px+1) with packed f32x2 arithmetic: pair q of group g = pixels 2q, 2q+1
   int px[NV];
-  float x0[NV], y0[NV], z[NV][4], dw[NV][4];
+  float y0[NV], z[NV][4];
+  unsigned long long x2[NV][2], z2[NV][2], dw[NV][2];
 #pragma unroll
   for (int g = 0; g < NV; g++) {
     px[g] = (chunk * NV + g) * (NT * 4) + tid * 4;
     float4 zz = make_float4(0.f, 0.f, 0.f, 0.f);
     if (px[g] < HW) zz = *reinterpret_cast<const float4 *>(p.disps + (size_t)frame * HW + px[g]);
     z[g][0] = zz.x; z[g][1] = zz.y; z[g][2] = zz.z; z[g][3] = zz.w;
-    x0[g] = ((float)(px[g] % p.wd) - cx) / fx;
+    const float x0 = ((float)(px[g] % p.wd) - cx) / fx;
     y0[g] = ((float)(px[g] / p.wd) - cy) / fy;
 #pragma unroll
-    for (int i = 0; i < 4; i++) dw[g][i] = 0.f;
+    for (int q = 0; q < 2; q++) {
+      x2[g][q] = pack2(fmaf((float)(2 * q), pk.ifx, x0), fmaf((float)(2 * q + 1), pk.ifx, x0));
+      z2[g][q] = pack2(z[g][2 * q], z[g][2 * q + 1]);
+      dw[g][q] = 0ull;
+    }
   }
   const int e0 = p.eptr[k], e1 = p.eptr[k + 1];
   for (int eb = e0; eb < e1; eb += LIN_EB) {
@@ -908,29 +914,31 @@ __global__ void __launch_bounds__(NT) k_backsub(BaParams p) {
     __syncthreads();
     for (int q = 0; q < nb; q++) {
       const int n = s_eid[q];
-      const float *R = s_geo[q].R, *t = s_geo[q].t, *dl = s_delta[q];
-      const float *tg = p.targets + (size_t)n * 2 * HW, *wg = p.weights + (size_t)n * 2 * HW;
-      float4 tu[NV], tv[NV], wu[NV], wv[NV];
+      const float *dl = s_delta[q];
+      const EdgeConst2 ec = make_edge_const2(s_geo[q].R, s_geo[q].t);
+      // J . delta with the signs of ju' = (e, 0, -ae, -ab, opa, -b), jv' = (0, e, -be, -opb, ab, a) on the constants
+      const unsigned long long D0 = dup2(dl[0]), D1 = dup2(dl[1]), nD2 = dup2(-dl[2]), nD3 = dup2(-dl[3]), D4 = dup2(dl[4]),
+                               D5 = dup2(dl[5]), nD5 = dup2(-dl[5]);
+      const float *wg = p.weights + (size_t)n * 2 * HW;
+      float4 wu[NV], wv[NV];
 #pragma unroll
       for (int g = 0; g < NV; g++) {
-        if (px[g] < HW) {
-          ldg_uv4(tg, HW, px[g], IL, tu[g], tv[g]);
-          ldg_uv4(wg, HW, px[g], IL, wu[g], wv[g]);
-        } else {
-          tu[g] = tv[g] = wu[g] = wv[g] = make_float4(0.f, 0.f, 0.f, 0.f);
-        }
+        if (px[g] < HW) ldg_uv4(wg, HW, px[g], IL, wu[g], wv[g]);  // weights only: E . delta carries no residual
+        else wu[g] = wv[g] = make_float4(0.f, 0.f, 0.f, 0.f);
       }
 #pragma unroll
       for (int g = 0; g < NV; g++) {
-        const float tua[4] = {tu[g].x, tu[g].y, tu[g].z, tu[g].w}, tva[4] = {tv[g].x, tv[g].y, tv[g].z, tv[g].w};
-        const float wua[4] = {wu[g].x, wu[g].y, wu[g].z, wu[g].w}, wva[4] = {wv[g].x, wv[g].y, wv[g].z, wv[g].w};
+        const unsigned long long wu2[2] = {pack2(wu[g].x, wu[g].y), pack2(wu[g].z, wu[g].w)};
+        const unsigned long long wv2[2] = {pack2(wv[g].x, wv[g].y), pack2(wv[g].z, wv[g].w)};
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
-          PixHat L;
-          pix_hat<MODE>(R, t, pk, fmaf((float)i, pk.ifx, x0[g]), y0[g], z[g][i], tua[i], tva[i], wua[i], wva[i], L);
-          const float du = fmaf(L.e, dl[0], fmaf(L.nae, dl[2], fmaf(L.nab, dl[3], fmaf(L.opa, dl[4], L.nb * dl[5]))));
-          const float dv = fmaf(L.e, dl[1], fmaf(L.nbe, dl[2], fmaf(L.nopb, dl[3], fmaf(L.ab, dl[4], L.a * dl[5]))));
-          dw[g][i] = fmaf(L.wv * L.jzv, dv, fmaf(L.wu * L.jzu, du, dw[g][i]));
+        for (int h = 0; h < 2; h++) {
+          PixHat2 L;
+          pix_hat2<MODE>(ec, pk, x2[g][h], y0[g], z2[g][h], wu2[h], wv2[h], L);
+          const unsigned long long du =
+              fma2r(L.e, D0, fma2r(L.ae, nD2, fma2r(L.ab, nD3, fma2r(L.opa, D4, mul2(L.b, nD5)))));
+          const unsigned long long dv =
+              fma2r(L.e, D1, fma2r(L.be, nD2, fma2r(L.opb, nD3, fma2r(L.ab, D4, mul2(L.a, D5)))));
+          dw[g][h] = fma2r(mul2(L.wv, L.jzv), dv, fma2r(mul2(L.wu, L.jzu), du, dw[g][h]));
         }
       }
     }
@@ -941,10 +949,12 @@ __global__ void __launch_bounds__(NT) k_backsub(BaParams p) {
     const float4 q4 = *reinterpret_cast<const float4 *>(p.Q + (size_t)k * HW + px[g]);
     const float4 w4 = *reinterpret_cast<const float4 *>(p.W + (size_t)k * HW + px[g]);
     const float qa[4] = {q4.x, q4.y, q4.z, q4.w}, wa[4] = {w4.x, w4.y, w4.z, w4.w};
-    float dzv[4], zn[4];
+    float dwa[4], dzv[4], zn[4];
+    unpack2(dw[g][0], dwa[0], dwa[1]);
+    unpack2(dw[g][1], dwa[2], dwa[3]);
 #pragma unroll
     for (int i = 0; i < 4; i++) {
-      dzv[i] = qa[i] * (wa[i] - dw[g][i]);
+      dzv[i] = qa[i] * (wa[i] - dwa[i]);
       zn[i] = z[g][i] + dzv[i];
       if (MODE == 1 && zn[i] < 0.f) zn[i] = 0.f;  // ba.py:119
     }
