@@ -383,6 +383,7 @@ extern "C" int gba_ba_begin(gba_ctx *c, float *poses, float *disps, const float 
   const int K = std::max(st.K, 1), want = 2 * c->sm_count;
   const int foot[3] = {2048, 1024, 512};
   c->variant = ((long long)K * ((c->HW + 1023) / 1024) >= want) ? 1 : 2;
+  if (const char *ev = getenv("GBA_VARIANT")) c->variant = std::max(0, std::min(2, atoi(ev)));  // diagnostics
   p.nchunk = (c->HW + foot[c->variant] - 1) / foot[c->variant];
   const int ntile = (c->HW + GRAM_T - 1) / GRAM_T;
   // Gram CTAs per keyframe: enough CTAs to fill the GPU (2 resident per SM), and among the small

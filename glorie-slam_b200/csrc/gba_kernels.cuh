@@ -241,8 +241,10 @@ __global__ void k_edge_geo(BaParams p) {
 // --------------------------------------------------------------------------------------------
 #define LIN_EB 8  // edges per shared-memory batch
 
+// occupancy targets measured at config E: 128 x 8 pixels at 4 CTAs per SM (125 registers) 0.32 ms, 3 CTAs (168
+// registers) 0.38, 5 CTAs (96, spills) 0.35; 128 x 4 pixels: 6 CTAs (80 registers) 0.34, 4 CTAs 0.41
 template <int NT, int NV, int MODE, bool IL>
-__global__ void __launch_bounds__(NT, (NT >= 256) ? 2 : 3) k_linearize(BaParams p) {
+__global__ void __launch_bounds__(NT, (NT >= 256) ? 2 : (NV == 1 ? 6 : 4)) k_linearize(BaParams p) {
   constexpr int NW = NT / 32;
   __shared__ EdgeGeo s_geo[LIN_EB];
   __shared__ int s_eid[LIN_EB];
