@@ -290,7 +290,7 @@ __device__ __forceinline__ unsigned long long fma2r(unsigned long long a, unsign
 __device__ __forceinline__ unsigned long long dup2(float v) { return pack2(v, v); }
 
 // ---------------------------------------------------------------------------------------------
-// pix_hat for TWO pixels of one edge at once (same image row, consecutive columns): every fp32 operation of the
+// pix_hat for TWO pixels of one edge at once: every fp32 operation of the
 // scalar version becomes one packed f32x2 instruction on the pair -- the same roundings in the same order, half
 // the issue slots (these kernels are bound by instruction issue, not by HBM).  Signs are not materialised:
 // ju' = (e, 0, -ae, -ab, opa, -b), jv' = (0, e, -be, -opb, ab, a); consumers negate the constant operand instead.
@@ -311,10 +311,9 @@ struct PixHat2 {
   unsigned long long X, Y, d;                     // for the residuals (pix_res2)
 };
 template <int MODE>
-__device__ __forceinline__ void pix_hat2(const EdgeConst2 &c, const PixConst &k, unsigned long long x2, float y0,
-                                         unsigned long long z2, unsigned long long wgu2, unsigned long long wgv2,
-                                         PixHat2 &o) {
-  const unsigned long long y2 = dup2(y0);
+__device__ __forceinline__ void pix_hat2(const EdgeConst2 &c, const PixConst &k, unsigned long long x2,
+                                         unsigned long long y2, unsigned long long z2, unsigned long long wgu2,
+                                         unsigned long long wgv2, PixHat2 &o) {
   o.X = fma2r(c.R0, x2, fma2r(c.R1, y2, fma2r(c.t0, z2, c.R2)));
   o.Y = fma2r(c.R3, x2, fma2r(c.R4, y2, fma2r(c.t1, z2, c.R5)));
   const unsigned long long Z = fma2r(c.R6, x2, fma2r(c.R7, y2, fma2r(c.t2, z2, c.R8)));

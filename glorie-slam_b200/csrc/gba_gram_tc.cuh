@@ -73,7 +73,7 @@
 
 __host__ __device__ __forceinline__ size_t gram_tc_smem(int max_deg) {
   return (size_t)GT_STAGES * GT_STAGE_BYTES + (size_t)GT_IS * GT_IN_BYTES + 256 +
-         (size_t)(max_deg < GT_MAXDEG ? max_deg : GT_MAXDEG) * 96 + 32;
+         (size_t)(max_deg < GT_MAXDEG ? max_deg : GT_MAXDEG) * (96 + sizeof(EdgeConst2)) + 32;
 }
 
 namespace tc {
@@ -217,7 +217,8 @@ __global__ void __launch_bounds__(GT_NT, 1) k_gram_tc(BaParams p) {
   uint64_t *s_bar = reinterpret_cast<uint64_t *>(s_raw + (size_t)GT_STAGES * GT_STAGE_BYTES + (size_t)GT_IS * GT_IN_BYTES);
   uint32_t *s_tmem = reinterpret_cast<uint32_t *>(s_bar + 2 * GT_STAGES + 4 + 2 * GT_IS);
   EdgeGeo *s_geo = reinterpret_cast<EdgeGeo *>(reinterpret_cast<unsigned char *>(s_bar) + 256);
-  const float **s_row = reinterpret_cast<const float **>(s_geo + deg);  // [2 deg + 3] input row bases
+  EdgeConst2 *s_ec2 = reinterpret_cast<EdgeConst2 *>(s_geo + deg);  // per edge: R, t duplicated into f32x2 operands
+  const float **s_row = reinterpret_cast<const float **>(s_ec2 + deg);  // [2 deg + 3] input row bases
   const uint32_t bar0 = tc::smem_u32(s_bar);
   auto full_bar = [&](int s) { return bar0 + 8u * s; };
   auto empty_bar = [&](int s) { return bar0 + 8u * (GT_STAGES + s); };
@@ -266,6 +267,10 @@ __global__ void __launch_bounds__(GT_NT, 1) k_gram_tc(BaParams p) {
   }
   for (int i = tid; i < deg * 16; i += GT_NT)
     reinterpret_cast<float *>(s_geo)[i] = reinterpret_cast<const float *>(p.geo + p.eidx[e0 + (i >> 4)])[i & 15];
+  for (int i = tid; i < deg; i += GT_NT) {
+    const EdgeGeo *gg = p.geo + p.eidx[e0 + i];
+    s_ec2[i] = make_edge_const2(gg->R, gg->t);
+  }
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
@@ -348,40 +353,57 @@ __global__ void __launch_bounds__(GT_NT, 1) k_gram_tc(BaParams p) {
           off[h][c] = (uint32_t)(r & 7) * 16u + (uint32_t)(r >> 3) * GT_SBO;
         }
       }
+      // the two pixels of the slot (tiles it0, it0 + 1) go through the arithmetic as one f32x2 pair
+      static_assert(GT_TPI == 2, "the producers pair the two tiles of a slot");
+      float csq[2], xs[2], ys[2];
+      unsigned char *hi[2], *lo[2];
 #pragma unroll
-      for (int u = 0; u < GT_TPI; u++) {
+      for (int u = 0; u < 2; u++) {
         const int it = it0 + u, stage = it % GT_STAGES;
         const int pix = (tile0 + it) * GT_K + lane;
-        const float csq = sqrtf(cqv[u]);
+        csq[u] = sqrtf(cqv[u]);
         const int prow = (int)(((float)pix + 0.5f) * inv_wd), pcol = pix - prow * p.wd;  // exact for pix < 2^22
-        const float x0 = ((float)pcol - cx) * pk.ifx, y0 = ((float)prow - cy) * pk.ify;
-        unsigned char *hi = s_ops + (size_t)stage * GT_STAGE_BYTES + lane_off, *lo = hi + GT_BUF;
+        xs[u] = ((float)pcol - cx) * pk.ifx;
+        ys[u] = ((float)prow - cy) * pk.ify;
+        hi[u] = s_ops + (size_t)stage * GT_STAGE_BYTES + lane_off;
+        lo[u] = hi[u] + GT_BUF;
+      }
+      const unsigned long long x2 = pack2(xs[0], xs[1]), y2 = pack2(ys[0], ys[1]), z2 = pack2(czq[0], czq[1]);
 #pragma unroll
-        for (int h = 0; h < NE; h++) {
-          const EdgeGeo &ge = s_geo[b0 + h * GT_NPW];
-          PixHat L;
-          pix_hat<MODE>(ge.R, ge.t, pk, x0, y0, czq[u], 0.f, 0.f, cwu[h][u], cwv[h][u], L);  // residuals unused
-          const float g = csq * gate[h];
-          const float su = g * L.wu * L.jzu, sv = g * L.wv * L.jzv;
-          float e[6];
-          e[0] = su * L.e;
-          e[1] = sv * L.e;
-          e[2] = fmaf(su, L.nae, sv * L.nbe);
-          e[3] = fmaf(su, L.nab, sv * L.nopb);
-          e[4] = fmaf(su, L.opa, sv * L.ab);
-          e[5] = fmaf(su, L.nb, sv * L.a);
+      for (int h = 0; h < NE; h++) {
+        const EdgeConst2 &ec = s_ec2[b0 + h * GT_NPW];
+        PixHat2 L;
+        pix_hat2<MODE>(ec, pk, x2, y2, z2, pack2(cwu[h][0], cwu[h][1]), pack2(cwv[h][0], cwv[h][1]), L);
+        const unsigned long long g2 = pack2(csq[0] * gate[h], csq[1] * gate[h]);
+        const unsigned long long su = mul2(mul2(g2, L.wu), L.jzu), sv = mul2(mul2(g2, L.wv), L.jzv);
+        const unsigned long long m1 = dup2(-1.0f), nsu = mul2(su, m1), nsv = mul2(sv, m1);
+        // rows of sqrt(Q) E: su ju' + sv jv' with ju' = (e, 0, -ae, -ab, opa, -b), jv' = (0, e, -be, -opb, ab, a)
+        unsigned long long e2[6];
+        e2[0] = mul2(su, L.e);
+        e2[1] = mul2(sv, L.e);
+        e2[2] = fma2r(nsu, L.ae, mul2(nsv, L.be));
+        e2[3] = fma2r(nsu, L.ab, mul2(nsv, L.opb));
+        e2[4] = fma2r(su, L.opa, mul2(sv, L.ab));
+        e2[5] = fma2r(nsu, L.b, mul2(sv, L.a));
 #pragma unroll
-          for (int c = 0; c < 6; c++) {
-            const float hv = tc::tf32_rna(e[c]);
-            *reinterpret_cast<float *>(hi + off[h][c]) = hv;
-            *reinterpret_cast<float *>(lo + off[h][c]) = e[c] - hv;
+        for (int c = 0; c < 6; c++) {
+          float ev[2];
+          unpack2(e2[c], ev[0], ev[1]);
+#pragma unroll
+          for (int u = 0; u < 2; u++) {
+            const float hv = tc::tf32_rna(ev[u]);
+            *reinterpret_cast<float *>(hi[u] + off[h][c]) = hv;
+            *reinterpret_cast<float *>(lo[u] + off[h][c]) = ev[u] - hv;
           }
         }
-        if (b0 == 0) {  // the extra row sqrt(Q) w_k rides with edge 0
-          const uint32_t offw = (uint32_t)(Rw & 7) * 16u + (uint32_t)(Rw >> 3) * GT_SBO;
-          const float x = csq * cwk[u], hv = tc::tf32_rna(x);
-          *reinterpret_cast<float *>(hi + offw) = hv;
-          *reinterpret_cast<float *>(lo + offw) = x - hv;
+      }
+      if (b0 == 0) {  // the extra row sqrt(Q) w_k rides with edge 0
+        const uint32_t offw = (uint32_t)(Rw & 7) * 16u + (uint32_t)(Rw >> 3) * GT_SBO;
+#pragma unroll
+        for (int u = 0; u < 2; u++) {
+          const float x = csq[u] * cwk[u], hv = tc::tf32_rna(x);
+          *reinterpret_cast<float *>(hi[u] + offw) = hv;
+          *reinterpret_cast<float *>(lo[u] + offw) = x - hv;
         }
       }
     };

@@ -935,7 +935,7 @@ __global__ void __launch_bounds__(NT, (NT >= 256) ? 3 : 6) k_backsub(BaParams p)
 #pragma unroll
         for (int h = 0; h < 2; h++) {
           PixHat2 L;
-          pix_hat2<MODE>(ec, pk, x2[g][h], y0[g], z2[g][h], wu2[h], wv2[h], L);
+          pix_hat2<MODE>(ec, pk, x2[g][h], dup2(y0[g]), z2[g][h], wu2[h], wv2[h], L);
           const unsigned long long du =
               fma2r(L.e, D0, fma2r(L.ae, nD2, fma2r(L.ab, nD3, fma2r(L.opa, D4, mul2(L.b, nD5)))));
           const unsigned long long dv =
