@@ -394,6 +394,7 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # stdout carries the one JSON line only
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
     args.warmup = max(args.warmup, 3)
 

@@ -21,7 +21,7 @@ thread_local char g_create_err[512] = "";  // also written by gba_noalloc.cu
 struct gba_ctx {
   int device, N_max, E_max, ht, wd, HW, sm_count;
   // index structures
-  int *kx, *fmap, *deg, *eptr, *eidx, *ek;
+  int *kx, *fmap, *deg, *eptr, *eidx, *ek, *cc_list;
   unsigned long long *goff;
   Status *st_d, *st_h;
   // workspaces
@@ -40,6 +40,8 @@ struct gba_ctx {
   // state of the current call
   BaParams p;
   cudaStream_t stream;
+  cudaStream_t side;           // k_gram (the few high-degree keyframes) runs here, beside k_gram_tc
+  cudaEvent_t ev_fork, ev_join;
   int begun, launches, variant, gsplit, total_fail, last_P;
   int seg_lo, seg_n, first_rank;  // edge-sharded solve: this rank's band segments (seg_n = 0: not sharded)
   size_t sys_count;
@@ -108,12 +110,15 @@ extern "C" const char *gba_last_error(const gba_ctx *c) { return c ? c->err : g_
 extern "C" void gba_destroy(gba_ctx *c) {
   if (!c) return;
   cudaSetDevice(c->device);
-  void *ptrs[] = {c->kx, c->fmap, c->deg, c->eptr, c->eidx, c->ek, c->goff, c->st_d, c->geo, c->hpart, c->edge_hv,
+  void *ptrs[] = {c->cc_list, c->kx, c->fmap, c->deg, c->eptr, c->eidx, c->ek, c->goff, c->st_d, c->geo, c->hpart, c->edge_hv,
                   c->Q, c->W, c->gram, c->dx, c->dzbuf, c->dspo_part, c->dwq, c->sys, c->tslot, c->perm, c->iperm, c->dspo_bad, c->wdog,
                   c->sb.tbits, c->sb.colrows, c->sb.colcnt, c->sb.rowcols, c->sb.rowcnt, c->sb.invL, c->sb.fail,
                   c->flags, c->upd, c->sb.trace};
   for (void *q : ptrs)
     if (q) cudaFree(q);
+  if (c->side) cudaStreamDestroy(c->side);
+  if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+  if (c->ev_join) cudaEventDestroy(c->ev_join);
   if (c->st_h) cudaFreeHost(c->st_h);
   if (c->h_cnt) cudaFreeHost(c->h_cnt);
   if (c->ev_pool) {
@@ -173,6 +178,10 @@ extern "C" int gba_create(gba_ctx **out, int device, int max_frames, int max_edg
   CKC(dalloc(&c->kx, N));
   CKC(dalloc(&c->fmap, N));
   CKC(dalloc(&c->deg, N));
+  CKC(dalloc(&c->cc_list, N));
+  CKC(cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
+  CKC(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+  CKC(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
   CKC(dalloc(&c->eptr, N + 1));
   CKC(dalloc(&c->eidx, E));
   CKC(dalloc(&c->ek, E));
@@ -346,7 +355,7 @@ extern "C" int gba_ba_begin(gba_ctx *c, float *poses, float *disps, const float 
   p.N = n_frames; p.E = n_edges; p.HW = c->HW; p.wd = c->wd; p.t0 = t0; p.t1 = t1; p.P = t1 - t0;
   p.mode = mode & ~GBA_LAYOUT_INTERLEAVED; p.il = (mode & GBA_LAYOUT_INTERLEAVED) ? 1 : 0;
   p.motion_only = motion_only ? 1 : 0; p.depth_only = depth_only ? 1 : 0; p.lm = lm; p.ep = ep;
-  p.kx = c->kx; p.fmap = c->fmap; p.deg = c->deg; p.eptr = c->eptr; p.eidx = c->eidx; p.ek = c->ek;
+  p.cc_list = c->cc_list; p.kx = c->kx; p.fmap = c->fmap; p.deg = c->deg; p.eptr = c->eptr; p.eidx = c->eidx; p.ek = c->ek;
   p.owned = owned; p.goff = c->goff; p.st = c->st_d; p.geo = c->geo; p.hpart = c->hpart; p.edge_hv = c->edge_hv;
   p.Q = c->Q; p.W = c->W; p.gram = c->gram; p.dx = c->dx; p.dz_out = c->dzbuf; p.sys = c->sys; p.tslot = c->tslot;
   p.perm = c->perm;
@@ -469,9 +478,23 @@ extern "C" int gba_ba_build(gba_ctx *c) {
     // atomics and the fp32 inputs of the reduced system are reproducible run to run (slower when there are fewer
     // keyframes than SMs).  The remaining unordered sums are fp64 (pose blocks, Schur assembly, closure tiles, rhs).
     if (getenv("GBA_DETERMINISTIC")) gs_tc = gs_cc = 1;
-    const bool need_cc = st.max_deg > p.tc_maxdeg;
+    const bool need_cc = st.n_cc > 0;
+    if (need_cc && !getenv("GBA_DETERMINISTIC"))  // few keyframes: split their pixels until the CTAs fill the machine
+      gs_cc = std::min((c->HW + GRAM_T - 1) / GRAM_T, std::max(gs_cc, (2 * c->sm_count + st.n_cc - 1) / st.n_cc));
     if ((p.tc_maxdeg > 0 && gs_tc > 1) || (need_cc && gs_cc > 1))
       CK(cudaMemsetAsync(c->gram, 0, (size_t)st.gram_floats * sizeof(float), s));
+    const bool both = need_cc && p.tc_maxdeg > 0;
+    if (need_cc) {  // the keyframes with more out-edges than k_gram_tc takes (cc_list), beside it on the side stream
+      cudaStream_t sc = both ? c->side : s;
+      if (both) {
+        CK(cudaEventRecord(c->ev_fork, s));
+        CK(cudaStreamWaitEvent(sc, c->ev_fork, 0));
+      }
+      const int RS = gram_pitch((6 * st.max_deg + 1 + 7) / 8);
+      k_gram<<<dim3(gs_cc, st.n_cc), GRAM_NT, (size_t)2 * GRAM_T * RS * sizeof(float) + (size_t)st.max_deg * 68, sc>>>(p);
+      LAUNCH_CHECK("k_gram");
+      if (both) CK(cudaEventRecord(c->ev_join, sc));
+    }
     if (p.tc_maxdeg > 0) {  // tensor-core Gram for the keyframes with <= GT_MAXDEG out-edges
       const dim3 gg(gs_tc, st.K);
       const size_t sm = gram_tc_smem(st.max_deg);
@@ -481,11 +504,7 @@ extern "C" int gba_ba_build(gba_ctx *c) {
       else k_gram_tc<1, true><<<gg, GT_NT, sm, s>>>(p);
       LAUNCH_CHECK("k_gram_tc");
     }
-    if (need_cc) {
-      const int RS = gram_pitch((6 * st.max_deg + 1 + 7) / 8);
-      k_gram<<<dim3(gs_cc, st.K), GRAM_NT, (size_t)2 * GRAM_T * RS * sizeof(float) + (size_t)st.max_deg * 68, s>>>(p);
-      LAUNCH_CHECK("k_gram");
-    }
+    if (both) CK(cudaStreamWaitEvent(s, c->ev_join, 0));
     stage_end(c);
     stage_begin(c, GBA_STAGE_SCHUR);
     k_schur<<<st.K, SCHUR_NT, (size_t)6 * (6 * st.max_deg + 1) * sizeof(float), s>>>(p);
@@ -683,7 +702,7 @@ extern "C" int gba_plan(gba_ctx *c, const int64_t *ii, const int64_t *jj, int n_
   memset(&p, 0, sizeof(p));
   p.ii = ii; p.jj = jj; p.N = n_frames; p.E = n_edges; p.HW = c->HW; p.wd = c->wd; p.t0 = t0; p.t1 = t1; p.P = t1 - t0;
   p.mode = GBA_MODE_DROID_CUDA;
-  p.kx = c->kx; p.fmap = c->fmap; p.deg = c->deg; p.eptr = c->eptr; p.eidx = c->eidx; p.ek = c->ek;
+  p.cc_list = c->cc_list; p.kx = c->kx; p.fmap = c->fmap; p.deg = c->deg; p.eptr = c->eptr; p.eidx = c->eidx; p.ek = c->ek;
   p.goff = c->goff; p.st = c->st_d; p.tslot = c->tslot; p.perm = c->perm; p.iperm = c->iperm; p.nT = c->nT_max;
   c->last_P = p.P;
   return build_index(c, nullptr, 0, true);
@@ -740,7 +759,7 @@ extern "C" int gba_dspo(gba_ctx *c, const float *poses, float *disps, const floa
   p.poses = const_cast<float *>(poses); p.disps = disps; p.intr = intrinsics; p.ii = ii; p.jj = jj;
   p.N = n_frames; p.E = n_edges; p.HW = c->HW; p.wd = c->wd; p.t0 = 0; p.t1 = n_frames; p.P = n_frames;
   p.mode = GBA_MODE_GEOM_PY;  // kx = unique(ii) (ba.py:139)
-  p.kx = c->kx; p.fmap = c->fmap; p.deg = c->deg; p.eptr = c->eptr; p.eidx = c->eidx; p.ek = c->ek;
+  p.cc_list = c->cc_list; p.kx = c->kx; p.fmap = c->fmap; p.deg = c->deg; p.eptr = c->eptr; p.eidx = c->eidx; p.ek = c->ek;
   p.goff = c->goff; p.st = c->st_d; p.geo = c->geo;
   int rc = build_index(c, nullptr, 0, false);
   if (rc) return rc;

@@ -40,7 +40,7 @@ struct Status {          // device -> host after the index build
   int n_pos;             // pose positions of the reduced system incl. padding
   int cc_slot0;          // first slot of the closure x closure tiles (they are numbered last)
   int last_fail;         // code of the most recent failed factorisation: 1 pivot <= 0, 3 / 4 a pipeline watchdog
-  int pad3;
+  int n_cc;              // keyframes whose out-degree exceeds tc_maxdeg: the CUDA-core Gram's work list (cc_list)
   unsigned long long gram_floats;  // total size of the per-frame Gram buffers
 };
 
@@ -53,6 +53,7 @@ struct BaParams {
   float lm, ep;
   // index structures
   int *kx, *fmap, *deg, *eptr, *eidx, *ek;
+  int *cc_list;  // [n_cc] keyframes of k_gram (k_prep_scan)
   const unsigned char *owned;
   unsigned long long *goff;
   Status *st;

@@ -107,13 +107,14 @@ __global__ void k_prep_edges(BaParams p) {
 // one CTA: CSR row pointers, per-frame Gram offsets, max degree
 __global__ void __launch_bounds__(1024) k_prep_scan(BaParams p) {
   __shared__ int s_warp[32];
-  __shared__ int s_carry, s_maxdeg;
+  __shared__ int s_carry, s_maxdeg, s_ncc;
   __shared__ unsigned long long s_gcarry;
   __shared__ unsigned long long s_gwarp[32];
   const int tid = threadIdx.x, K = p.st->K;
   if (tid == 0) {
     s_carry = 0;
     s_maxdeg = 0;
+    s_ncc = 0;
     s_gcarry = 0ull;
     p.eptr[0] = 0;
   }
@@ -139,6 +140,7 @@ __global__ void __launch_bounds__(1024) k_prep_scan(BaParams p) {
       s_gwarp[tid >> 5] = gv;
     }
     atomicMax(&s_maxdeg, d);
+    if (k < K && d > p.tc_maxdeg && (!p.owned || p.owned[k])) p.cc_list[atomicAdd(&s_ncc, 1)] = k;
     __syncthreads();
     if (tid < 32) {
       int w = s_warp[tid];
@@ -171,6 +173,7 @@ __global__ void __launch_bounds__(1024) k_prep_scan(BaParams p) {
   }
   if (tid == 0) {
     p.st->max_deg = s_maxdeg;
+    p.st->n_cc = s_ncc;
     p.st->gram_floats = s_gcarry;
   }
 }
@@ -509,11 +512,8 @@ __device__ __forceinline__ void named_bar_arrive(int id) { asm volatile("bar.arr
 // extra column G[:, 6 deg] = sum_pix E Q w.
 __global__ void __launch_bounds__(GRAM_NT, 2) k_gram(BaParams p) {
   extern __shared__ float s_tile[];
-  const int k = blockIdx.y;
-  if (k >= p.st->K) return;
-  if (p.owned && !p.owned[k]) return;
+  const int k = p.cc_list[blockIdx.y];  // the keyframes with more than tc_maxdeg out-edges; the others are k_gram_tc's
   const int e0 = p.eptr[k], deg = p.eptr[k + 1] - e0;
-  if (deg == 0 || deg <= p.tc_maxdeg) return;  // small keyframes are k_gram_tc's
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int Rw = 6 * deg;              // rows of E; shared-memory column Rw holds sqrt(Q) * w
   const int nb = (Rw + 7) / 8;         // 8-row blocks of G proper
