@@ -507,7 +507,7 @@ extern "C" int gba_ba_build(gba_ctx *c) {
     if (both) CK(cudaStreamWaitEvent(s, c->ev_join, 0));
     stage_end(c);
     stage_begin(c, GBA_STAGE_SCHUR);
-    k_schur<<<st.K, SCHUR_NT, (size_t)6 * (6 * st.max_deg + 1) * sizeof(float), s>>>(p);
+    k_schur<<<st.K, SCHUR_NT, (size_t)(6 * (6 * st.max_deg + 1) + st.max_deg) * sizeof(float), s>>>(p);
     LAUNCH_CHECK("k_schur");
     stage_end(c);
   }

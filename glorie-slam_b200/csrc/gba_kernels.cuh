@@ -765,21 +765,42 @@ __global__ void __launch_bounds__(SCHUR_NT) k_schur(BaParams p) {
   double *rhs = p.sys + (size_t)p.st->n_slots * GBA_NB2;
   const int pcr = p.kx[k] - p.t0;
   const int pc = (pcr >= 0 && pcr < p.P) ? p.perm[pcr] : -1;
-  auto pos_of = [&](int q) {  // position of edge q's destination pose in the permuted system
+  // position of each edge's destination pose in the permuted system: three dependent loads, once per edge
+  int *s_pos = reinterpret_cast<int *>(s_U + 6 * (Rw + 1));
+  for (int q = tid; q < deg; q += SCHUR_NT) {
     const int pj = p.geo[p.eidx[e0 + q]].pj;
-    return pj >= 0 ? p.perm[pj] : -1;
-  };
+    s_pos[q] = pj >= 0 ? p.perm[pj] : -1;
+  }
+  __syncthreads();
+  auto pos_of = [&](int q) { return s_pos[q]; };
 
   // (a) edge-row x edge-row blocks, lower triangle only
   for (int idx = tid; idx < deg * deg; idx += SCHUR_NT) {
     const int n = idx / deg, m = idx - n * deg;
     const int a = pos_of(n), b = pos_of(m);
     if (a < 0 || b < 0 || a < b) continue;
+    // all 36 values first (independent loads), then the slots of the <= 4 tiles the 6 x 6 block touches
+    // (6 does not divide the tile size), then the adds -- not a dependent value + slot load per element
+    float gv[36];
+#pragma unroll
     for (int r = 0; r < 6; r++)
+#pragma unroll
+      for (int c = 0; c < 6; c++) gv[6 * r + c] = gram_at(G, Rp, 6 * n + r, 6 * m + c);
+    const int R0 = 6 * a, C0 = 6 * b;
+    const int tr0 = R0 / GBA_NB, tr1 = (R0 + 5) / GBA_NB, tc0 = C0 / GBA_NB, tc1 = (C0 + 5) / GBA_NB;
+    const int s00 = p.tslot[tr0 * p.nT + tc0];
+    const int s01 = (tc1 != tc0 && tr0 >= tc1) ? p.tslot[tr0 * p.nT + tc1] : s00;
+    const int s10 = (tr1 != tr0) ? p.tslot[tr1 * p.nT + tc0] : s00;
+    const int s11 = (tr1 != tr0 || tc1 != tc0) ? p.tslot[tr1 * p.nT + tc1] : s00;
+#pragma unroll
+    for (int r = 0; r < 6; r++)
+#pragma unroll
       for (int c = 0; c < 6; c++) {
-        const int Rg = 6 * a + r, Cg = 6 * b + c;
+        const int Rg = R0 + r, Cg = C0 + c;
         if (Rg < Cg) continue;
-        atomicAdd(sys_at(p, Rg, Cg), -(double)gram_at(G, Rp, 6 * n + r, 6 * m + c));
+        const bool hr = Rg / GBA_NB != tr0, hc = Cg / GBA_NB != tc0;
+        const int slot = hr ? (hc ? s11 : s10) : (hc ? s01 : s00);
+        atomicAdd(p.sys + (size_t)slot * GBA_NB2 + (Rg % GBA_NB) * GBA_NB + (Cg % GBA_NB), -(double)gv[6 * r + c]);
       }
   }
   // (b) rhs: v -= E Q w  (Ev6x1 + update_rhs, droid_kernels.cu:1298-1308)
