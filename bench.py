@@ -15,6 +15,7 @@ closure block + rhs (GBA_REPLICATED_SOLVE=1: the older scheme, whole system all-
 
 Printed JSON (one line, rank 0): the driver contract plus
   roofline            the dominant HBM kernel: algorithmic bytes of one launch / its CUDA-event time
+  roofline_backsub    the second streaming kernel (k_backsub, weights only: 8 B per edge pixel), same form
   roofline_iteration  SURVEY 8(d): B_alg = 16 E HW + 16 K HW per iteration over the SUM of the HBM-streaming
                       stages of an iteration (every pass that re-reads the edge inputs counts against it)
   roofline_gram / roofline_chain   the tensor-core Gram and the fp64 tile Cholesky
@@ -512,6 +513,15 @@ def main():
     roofline = {"bound": "hbm", "kernel": "k_linearize", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
                 "frac": achieved / pk["hbm_gbs"], "traffic": traffic_of("k_linearize", args.config, world),
                 "peak_source": pk_src, "algorithmic_bytes_per_launch": alg_bytes, "ms_per_launch": lin_ms}
+    # the second streaming kernel: k_backsub reads the weights only (8 B per edge pixel: E . delta carries no residual)
+    # and per depth-keyframe pixel disparity 4 + Q/W 8 in, disparity 4 + dz 4 out
+    bs_bytes = 8.0 * E_local * HW + 20.0 * K_local * HW
+    bs_ms = st_ms("backsub")
+    roofline_backsub = {"bound": "hbm", "kernel": "k_backsub", "unit": "GB/s", "peak": pk["hbm_gbs"],
+                        "achieved": bs_bytes / (bs_ms * 1e-3) / 1e9 if bs_ms > 0 else 0.0,
+                        "frac": bs_bytes / (bs_ms * 1e-3) / 1e9 / pk["hbm_gbs"] if bs_ms > 0 else 0.0,
+                        "traffic": traffic_of("k_backsub", args.config, world),
+                        "algorithmic_bytes_per_launch": bs_bytes, "ms_per_launch": bs_ms}
     # SURVEY 8(d) per iteration: B_alg = 16 E HW + 16 K HW once, against EVERY stage that streams the edge inputs
     b_alg = 16.0 * E_local * HW + 16.0 * K_local * HW
     hbm_ms = st_ms("linearize") + st_ms("gram") + st_ms("backsub")
@@ -701,7 +711,8 @@ def main():
                                  if plan is not None else "replicated after an all-reduce of the whole system"),
                        "l2": "inputs (%.0f MB per rank) larger than L2" % (input_bytes / 1e6) if l2_flush is None
                              else "256 MB L2 flush between steps"},
-            "roofline": roofline, "roofline_iteration": roofline_iteration, "roofline_gram": roofline_gram,
+            "roofline": roofline, "roofline_backsub": roofline_backsub, "roofline_iteration": roofline_iteration,
+            "roofline_gram": roofline_gram,
             "roofline_chain": roofline_chain, "layout_handoff": layout, "stages": stages, "dspo": dspo,
             "cpu_baseline": cb, "e2e": e2e, "reference_cuda": ref_cuda, "parity_n_ranks": parity_n,
             "gpu_launches": int(launches_per_step * args.steps), "gpu_launches_per_step": int(launches_per_step),
