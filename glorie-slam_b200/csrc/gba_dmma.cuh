@@ -125,7 +125,9 @@ __device__ __forceinline__ void dm_diag8(DmPotrfSmem &s, int o, int lane) {
   }
 }
 
-__device__ bool dm_potrf64(const double *T, double *XI, double *bvec, DmPotrfSmem &s) {
+// Lprev != nullptr: the tile left of this one, L[k,k-1], whose product has NOT been subtracted yet -- the update
+// T - Lprev Lprev^T is applied here in shared memory (one hop less on the chain than a separate update task).
+__device__ bool dm_potrf64(const double *T, double *XI, double *bvec, DmPotrfSmem &s, const double *Lprev = nullptr) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, t = lane & 3;
 #ifdef DM_TIMERS
   long long dm_last = clock64();
@@ -141,11 +143,57 @@ __device__ bool dm_potrf64(const double *T, double *XI, double *bvec, DmPotrfSme
       const int e = 2 * (tid + 256 * q), r = e >> 6, c = e & 63;
       s.S[r][c] = v[q].x;
       s.S[r][c + 1] = v[q].y;
+      if (!Lprev) {
+        s.M[r][c] = (r == c) ? 1.0 : 0.0;
+        s.M[r][c + 1] = (r == c + 1) ? 1.0 : 0.0;
+      }
+    }
+    if (Lprev) {  // M holds L[k,k-1] for the moment
+#pragma unroll
+      for (int q = 0; q < 8; q++) v[q] = __ldcg(reinterpret_cast<const double2 *>(Lprev) + tid + 256 * q);
+#pragma unroll
+      for (int q = 0; q < 8; q++) {
+        const int e = 2 * (tid + 256 * q), r = e >> 6, c = e & 63;
+        s.M[r][c] = v[q].x;
+        s.M[r][c + 1] = v[q].y;
+      }
+    }
+  }
+  __syncthreads();
+  if (Lprev) {
+    // S -= M M^T on the lower block triangle (36 blocks of 8 x 8, K = 64): block rows r and 7 - r go to the warps
+    // r and r + 4, 5 + 4 blocks, every block an independent DMMA chain
+    const int r1 = warp & 3, r2 = 7 - r1, first = (warp < 4) ? 0 : 5, nblk = (warp < 4) ? 5 : 4;
+    double acc[5][2];
+#pragma unroll
+    for (int q = 0; q < 5; q++) acc[q][0] = acc[q][1] = 0.0;
+#pragma unroll 2
+    for (int k = 0; k < GBA_NB; k += 4) {
+#pragma unroll
+      for (int q = 0; q < 5; q++) {
+        if (q < nblk) {
+          const int idx = first + q, bi = idx <= r1 ? r1 : r2, cj = idx <= r1 ? idx : idx - r1 - 1;
+          dmma884(acc[q], s.M[8 * bi + g][k + t], s.M[8 * cj + g][k + t]);
+        }
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 5; q++) {
+      if (q < nblk) {
+        const int idx = first + q, bi = idx <= r1 ? r1 : r2, cj = idx <= r1 ? idx : idx - r1 - 1;
+        double *dst = &s.S[8 * bi + g][8 * cj + 2 * t];
+        dst[0] -= acc[q][0];
+        dst[1] -= acc[q][1];
+      }
+    }
+    __syncthreads();  // every warp is done reading M
+#pragma unroll
+    for (int q = 0; q < 8; q++) {
+      const int e = 2 * (tid + 256 * q), r = e >> 6, c = e & 63;
       s.M[r][c] = (r == c) ? 1.0 : 0.0;
       s.M[r][c + 1] = (r == c + 1) ? 1.0 : 0.0;
     }
   }
-  __syncthreads();
   // the 8 x 8 diagonal blocks are read as full symmetric blocks: mirror their lower triangles
   for (int e = tid; e < 8 * 64; e += 256) {
     const int blk = e >> 6, r = (e >> 3) & 7, c = e & 7;

@@ -339,10 +339,12 @@ __device__ __forceinline__ double *rhs_ptr(const BaParams &p) { return p.sys + (
 // Cholesky of the diagonal tile: inverse of its factor into invL[kk] (the factor itself is never needed
 // again: the solves and substitutions use the inverse), forward substitution y_kk = inv(L_kk) b_kk.
 // A pivot that is not positive and finite raises the failure flag (SimplicialLLT: NumericalIssue).
-__device__ void role_potrf(const BaParams &p, const SolverBufs &sb, int kk, double *s_buf) {
+__device__ void role_potrf(const BaParams &p, const SolverBufs &sb, int kk, bool fused, double *s_buf) {
   DmPotrfSmem &s = *reinterpret_cast<DmPotrfSmem *>(s_buf);
   const double *T = p.sys + (size_t)p.tslot[kk * p.nT + kk] * GBA_NB2;
-  const bool ok = dm_potrf64(T, sb.invL + (size_t)kk * GBA_NB2, rhs_ptr(p) + kk * GBA_NB, s);
+  // fused: the previous column of the chain has not updated this tile; its tile L[kk,kk-1] is solved (k_chain)
+  const double *Lprev = fused ? p.sys + (size_t)p.tslot[kk * p.nT + kk - 1] * GBA_NB2 : nullptr;
+  const bool ok = dm_potrf64(T, sb.invL + (size_t)kk * GBA_NB2, rhs_ptr(p) + kk * GBA_NB, s, Lprev);
   if (!ok && threadIdx.x == 0) *sb.fail = 1;
 }
 
@@ -523,22 +525,26 @@ __global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int ns
       if (spine && t < ninit) {
         role = 0;
         kk = nsl > 0 ? (seg0 + t) * segT : band;
-      } else if (t < total) {
-        for (;;) {  // tickets only grow: the walk over the sequence is amortised
+      } else {
+        while (spos < nband + clo) {  // tickets only grow: the walk over the sequence is amortised
           const int col = seq(spos), nx = next_of(spos, col);
           const int cnt = sb.colcnt[col], pairs = cnt * (cnt + 1) / 2, nxt = nx >= 0 ? 1 : 0;
-          // spine block(k): T(k, 0, *)  S(k, pair 0, *)  P(next(k));  bulk block(k): T(k, a >= 1, *)  S(k, other pairs)
-          const int n = spine ? (cnt > 0 ? 2 * SPLIT : 0) + nxt : (cnt > 0 ? SPLIT * (cnt - 1) + pairs - 1 : 0);
+          // FUSED: the next column of the same chain sits right below the diagonal -- its factorisation applies
+          // this column's update of its diagonal tile itself (dm_potrf64, Lprev) instead of waiting for an update task
+          const bool fz = cnt > 0 && nx == col + 1 && !(spos < nband && nx >= band) && sb.colrows[col * p.nT] == nx;
+          // spine block(k): T(k, 0, *)  [S(k, pair 0, *) unless fused]  P(next(k));
+          // bulk block(k): T(k, a >= 1, *)  S(k, other pairs)
+          const int n = spine ? (cnt > 0 ? (fz ? SPLIT : 2 * SPLIT) : 0) + nxt : (cnt > 0 ? SPLIT * (cnt - 1) + pairs - 1 : 0);
           if (t < base + n) {
             int o = t - base;
             kk = col;
             if (spine) {
               if (cnt > 0 && o < SPLIT) {
                 role = 1; a = 0; q = o;
-              } else if (cnt > 0 && o < 2 * SPLIT) {
+              } else if (cnt > 0 && !fz && o < 2 * SPLIT) {
                 role = 2; a = 0; b = 0; q = o - SPLIT;
               } else {
-                role = 0; kk = nx;
+                role = 0; kk = nx; b = fz ? 1 : 0;
               }
             } else {
               if (o < SPLIT * (cnt - 1)) {
@@ -584,13 +590,14 @@ __global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int ns
       }
 #pragma unroll
       for (int o = 16; o >= 1; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
-      if (tid == 0) s_need[0] = n * SPLIT;
+      if (tid == 0) s_need[0] = (n - ((role == 0 && b) ? 1u : 0u)) * SPLIT;  // fused: column kk - 1 sends no update
     }
     __syncthreads();
     const unsigned need = s_need[0];
     const unsigned *updp = sb.upd + p.tslot[ti * p.nT + tj];
     if (tid == 0) {
       if (role == 1) chain_wait(&sb.flagA[kk], 1u, sb.fail);
+      if (role == 0 && b) chain_wait(sb.upd + p.tslot[kk * p.nT + kk - 1], (unsigned)SPLIT * CHAIN_TDONE, sb.fail);
       if (role >= 2) {  // both operand tiles solved: their counters carry one CHAIN_TDONE per slab
         chain_wait(sb.upd + p.tslot[ti * p.nT + kk], (unsigned)SPLIT * CHAIN_TDONE, sb.fail);
         chain_wait(sb.upd + p.tslot[tj * p.nT + kk], (unsigned)SPLIT * CHAIN_TDONE, sb.fail);
@@ -601,7 +608,7 @@ __global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int ns
     __syncthreads();
     const bool failed = __ldcg(sb.fail) != 0;
     if (role == 0) {
-      if (!failed) role_potrf(p, sb, kk, s_buf);
+      if (!failed) role_potrf(p, sb, kk, b != 0, s_buf);
       __threadfence();
       __syncthreads();
       if (tid == 0) atomicExch(&sb.flagA[kk], 1u);

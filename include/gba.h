@@ -17,7 +17,10 @@
  *     (droid_kernels.cu:1207-1210, chol.py:13-15) the pose update is zero; the count of such
  *     iterations is reported by gba_query().
  *   - a context is bound to one device and is not re-entrant; calls are asynchronous on
- *     `stream` except for one small status read-back after the index build.
+ *     `stream` except for one small status read-back after the index build.  Inside an iteration
+ *     one kernel (the Gram of the few keyframes with more than 21 out-edges) runs on a non-blocking
+ *     stream owned by the context, forked from and joined to `stream` by events: everything the call
+ *     does is ordered before whatever the caller enqueues on `stream` afterwards.
  *   - per-pixel arrays (disps, disps_sens, targets, weights, eta, mono_disps, Q, W) are read with
  *     16-byte vector loads: their base pointers must be 16-byte aligned (torch allocations are);
  *     a misaligned pointer is refused with GBA_EINVAL.
