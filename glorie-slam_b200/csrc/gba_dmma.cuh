@@ -135,27 +135,24 @@ __device__ bool dm_potrf64(const double *T, double *XI, double *bvec, DmPotrfSme
   if (tid == 0) s.bad = 0;
   if (tid < GBA_NB) s.b[tid] = __ldcg(bvec + tid);
   {  // tile -> S (coalesced 16-byte loads; only the lower triangle of T is valid), M = I
-    double2 v[8];
+    double2 v[8], l[8];
 #pragma unroll
     for (int q = 0; q < 8; q++) v[q] = __ldcg(reinterpret_cast<const double2 *>(T) + tid + 256 * q);
+    if (Lprev) {  // both tiles in flight together: one L2 latency
+#pragma unroll
+      for (int q = 0; q < 8; q++) l[q] = __ldcg(reinterpret_cast<const double2 *>(Lprev) + tid + 256 * q);
+    }
 #pragma unroll
     for (int q = 0; q < 8; q++) {
       const int e = 2 * (tid + 256 * q), r = e >> 6, c = e & 63;
       s.S[r][c] = v[q].x;
       s.S[r][c + 1] = v[q].y;
-      if (!Lprev) {
+      if (Lprev) {  // M holds L[k,k-1] for the moment
+        s.M[r][c] = l[q].x;
+        s.M[r][c + 1] = l[q].y;
+      } else {
         s.M[r][c] = (r == c) ? 1.0 : 0.0;
         s.M[r][c + 1] = (r == c + 1) ? 1.0 : 0.0;
-      }
-    }
-    if (Lprev) {  // M holds L[k,k-1] for the moment
-#pragma unroll
-      for (int q = 0; q < 8; q++) v[q] = __ldcg(reinterpret_cast<const double2 *>(Lprev) + tid + 256 * q);
-#pragma unroll
-      for (int q = 0; q < 8; q++) {
-        const int e = 2 * (tid + 256 * q), r = e >> 6, c = e & 63;
-        s.M[r][c] = v[q].x;
-        s.M[r][c + 1] = v[q].y;
       }
     }
   }
@@ -167,7 +164,7 @@ __device__ bool dm_potrf64(const double *T, double *XI, double *bvec, DmPotrfSme
     double acc[5][2];
 #pragma unroll
     for (int q = 0; q < 5; q++) acc[q][0] = acc[q][1] = 0.0;
-#pragma unroll 2
+#pragma unroll 4
     for (int k = 0; k < GBA_NB; k += 4) {
 #pragma unroll
       for (int q = 0; q < 5; q++) {

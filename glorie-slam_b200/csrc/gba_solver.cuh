@@ -481,7 +481,7 @@ __device__ __forceinline__ void chain_wait(const unsigned *ptr, unsigned target,
 }
 
 template <int SLAB>
-__global__ void __launch_bounds__(256) k_chain(BaParams p, SolverBufs sb, int nseg, int segT, int total_spine,
+__global__ void __launch_bounds__(256, 2) k_chain(BaParams p, SolverBufs sb, int nseg, int segT, int total_spine,
                                                int total_bulk, int n_spine, int phase, int seg_lo, int seg_n) {
   extern __shared__ double s_buf[];
   constexpr int SPLIT = GBA_NB / SLAB;
