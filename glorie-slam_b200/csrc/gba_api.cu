@@ -561,8 +561,12 @@ static int launch_chain(gba_ctx *c, int phase) {
   // spine CTAs: 4 slabs in flight per independent chain (band segments run side by side), at least 8
   const int spine_width = std::min(c->chain_capacity / 2, std::max(8, 4 * chains));
   const int n_bulk = (int)std::max<long long>(1, std::min<long long>(total_bulk, (long long)c->chain_capacity - spine_width));
+  // a grid of exactly two CTAs on every SM: spine CTAs by SM (pairs) instead of by block index, see k_chain
+  const bool by_sm = spine_width + n_bulk == 2 * c->sm_count && c->chain_capacity == 2 * c->sm_count &&
+                     spine_width % 2 == 0 && !getenv("GBA_CHAIN_SPINE_BY_BLOCK");
   k_chain<16><<<spine_width + n_bulk, 256, kSolverSmem, s>>>(p, c->sb, nseg, segT, (int)total_spine, (int)total_bulk,
-                                                           spine_width, phase, seg_lo, phase == 1 ? c->seg_n : 0);
+                                                           by_sm ? -spine_width : spine_width, phase, seg_lo,
+                                                           phase == 1 ? c->seg_n : 0);
   LAUNCH_CHECK("k_chain");
   return GBA_OK;
 }

@@ -505,7 +505,17 @@ __global__ void __launch_bounds__(256, 2) k_chain(BaParams p, SolverBufs sb, int
   // handed out in sequence order; a waiting task only waits for tasks that precede it in the combined order,
   // and the earliest unfinished task of the combined order is always the head of its own queue, hence taken
   // and runnable: no deadlock for any grid size >= n_spine + 1.
-  const bool spine = (int)blockIdx.x < n_spine;
+  // n_spine < 0: the grid fills the machine with exactly two CTAs per SM, and the spine CTAs are the PAIRS living on
+  // the SMs 0 .. -n_spine/2 - 1: a factorisation then never shares its SM (issue slots, DMMA pipe) with a bulk
+  // update running flat out, only with another spine task (12.4 us alone against 15-18 us beside a bulk CTA).
+  bool spine;
+  if (n_spine < 0) {
+    unsigned smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    spine = (int)smid < (-n_spine) / 2;
+  } else {
+    spine = (int)blockIdx.x < n_spine;
+  }
   unsigned *ticket = spine ? &sb.ticket[0] : &sb.ticket[1];
   const int total = spine ? total_spine : total_bulk;
   auto seq = [&](int s_) { return s_ < nband ? (seg0 + s_ % nsl) * segT + s_ / nsl : band + (s_ - nband); };
