@@ -559,7 +559,8 @@ static int launch_chain(gba_ctx *c, int phase) {
   CK(cudaMemsetAsync(c->upd, 0, (size_t)st.n_slots * sizeof(unsigned int), s));
   if (c->sb.trace) CK(cudaMemsetAsync(c->sb.trace, 0, sizeof(unsigned long long), s));  // keeps the last launch
   // spine CTAs: 4 slabs in flight per independent chain (band segments run side by side), at least 8
-  const int spine_width = std::min(c->chain_capacity / 2, std::max(8, 4 * chains));
+  int spine_width = std::min(c->chain_capacity / 2, std::max(8, 4 * chains));
+  if (const char *e = getenv("GBA_CHAIN_SPINE")) spine_width = std::min(c->chain_capacity / 2, std::max(2, atoi(e) * chains) & ~1);  // tuning aid
   const int n_bulk = (int)std::max<long long>(1, std::min<long long>(total_bulk, (long long)c->chain_capacity - spine_width));
   // a grid of exactly two CTAs on every SM: spine CTAs by SM (pairs) instead of by block index, see k_chain
   const bool by_sm = spine_width + n_bulk == 2 * c->sm_count && c->chain_capacity == 2 * c->sm_count &&

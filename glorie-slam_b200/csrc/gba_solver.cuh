@@ -517,7 +517,7 @@ __global__ void __launch_bounds__(256, 2) k_chain(BaParams p, SolverBufs sb, int
     spine = (int)blockIdx.x < n_spine;
   }
   unsigned *ticket = spine ? &sb.ticket[0] : &sb.ticket[1];
-  const int total = spine ? total_spine : total_bulk;
+  (void)total_spine; (void)total_bulk;  // upper bounds, used by the host to size the grid: the lists end with the sequence
   auto seq = [&](int s_) { return s_ < nband ? (seg0 + s_ % nsl) * segT + s_ / nsl : band + (s_ - nband); };
   auto next_of = [&](int s_, int kk_) {  // column whose potrf is issued inside block(kk_), or -1
     if (s_ < nband) {
