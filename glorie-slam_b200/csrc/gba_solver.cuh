@@ -446,6 +446,9 @@ __device__ __forceinline__ unsigned ld_acquire(const unsigned *p) {
 // after the last band column of the sequence, nothing at the end of the other segments:
 //     P(first column of every segment) | block(seq 0) | block(seq 1) | ...
 //     block(k) = T(k,*)  S(k,pair 0)  P(next(k))  S(k,rest)
+// split over two ticket queues (k_chain): SPINE = T(k,0,*) S(k,pair 0) P(next(k)), BULK = the rest.  When the next
+// column of the same chain sits right below the diagonal, S(k,pair 0) does not exist: P(k+1) waits for T(k,0,*) and
+// subtracts L[k+1,k] L[k+1,k]^T from its tile itself (FUSED, dm_potrf64).
 // A persistent CTA takes the next ticket, waits for the task's inputs, runs it, publishes it:
 //     P(k)       waits until tile (k,k) has received every update of the columns before k     -> flagA[k]
 //     T(k,a,q)   waits for flagA[k] and for tile (i_a,k) to be fully updated        -> upd[(i_a,k)] += TDONE
