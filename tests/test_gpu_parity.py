@@ -728,6 +728,19 @@ def test_deterministic_switch(monkeypatch):
     print("deterministic runs bitwise equal:", np.array_equal(a.poses, b.poses) and np.array_equal(a.disps, b.disps))
 
 
+def test_spine_placement_variants(monkeypatch):
+    """k_chain picks its critical-path CTAs by SM when the grid fills the machine (default) or by block index
+    (GBA_CHAIN_SPINE_BY_BLOCK=1, also what smaller grids use): same factorisation, so the same state up to the
+    order of the fp64 atomics"""
+    g = synth.make_config("C")
+    a = run_ba(g)
+    monkeypatch.setenv("GBA_CHAIN_SPINE_BY_BLOCK", "1")
+    b = run_ba(g)
+    monkeypatch.delenv("GBA_CHAIN_SPINE_BY_BLOCK")
+    assert a.info.chol_failures == 0 and b.info.chol_failures == 0
+    assert rel(a.poses, b.poses) < 1e-6 and rel(a.disps, b.disps) < 1e-6
+
+
 # ------------------------------------------------------------------------------------------
 # boundary hardening
 # ------------------------------------------------------------------------------------------
