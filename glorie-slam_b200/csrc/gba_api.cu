@@ -154,7 +154,7 @@ extern "C" int gba_create(gba_ctx **out, int device, int max_frames, int max_edg
   c->wd = wd;
   c->HW = ht * wd;
   const size_t N = max_frames, E = std::max(max_edges, 1), HW = c->HW;
-  c->pos_cap = max_frames + 17 * ORD_ALIGN;  // room for the segment padding of the ordering
+  c->pos_cap = max_frames + 26 * ORD_ALIGN;  // room for the padding of the segments and of the second-level separators
   c->nT_max = (6 * c->pos_cap + GBA_NB - 1) / GBA_NB;
   const size_t nT = c->nT_max, ld = nT * GBA_NB;
   if (nT > TS_MAXT) {
@@ -285,7 +285,7 @@ static int build_index(gba_ctx *c, const int64_t *kx_global, int n_kx, bool want
   int rc = build_csr(c, kx_global, n_kx);
   if (rc) return rc;
   if (want_tiles) {
-    k_order<<<1, 1024, (size_t)((p.P + 3) / 4) * 4, s>>>(p, c->pos_cap);
+    k_order<<<1, 1024, (size_t)((p.P + 3) / 4) * 4, s>>>(p, c->pos_cap, getenv("GBA_NO_LEVEL2") ? 1 : 0);
     LAUNCH_CHECK("k_order");
     CK(cudaMemsetAsync(c->sb.tbits, 0, (size_t)p.nT * TS_WORDS * sizeof(unsigned int), s));
     k_tile_mark<false><<<p.N, 128, 0, s>>>(p, c->sb.tbits);
@@ -549,10 +549,8 @@ static int launch_chain(gba_ctx *c, int phase) {
   }
   if (phase != 1) {
     for (int kk = band; kk < nT; kk++) add_col(kk, kk + 1 < nT);
-    if (chains == 0) {
-      chains = 1;
-      total_spine += 1;
-    }
+    total_spine += st.n_seg2 + 1;  // (upper bounds: they only size the grid)
+    if (chains == 0) chains = std::max(1, st.n_seg2);
   }
   if (total_bulk >= (1LL << 30)) return fail_msg(c, GBA_ECAPACITY, "reduced system too large for the tile task graph");
   CK(cudaMemsetAsync(c->flags, 0, (size_t)5 * c->nT_max * sizeof(unsigned int), s));  // flagA .. ticket (not cntY / ticket2)
@@ -567,7 +565,7 @@ static int launch_chain(gba_ctx *c, int phase) {
                      spine_width % 2 == 0 && !getenv("GBA_CHAIN_SPINE_BY_BLOCK");
   k_chain<16><<<spine_width + n_bulk, 256, kSolverSmem, s>>>(p, c->sb, nseg, segT, (int)total_spine, (int)total_bulk,
                                                            by_sm ? -spine_width : spine_width, phase, seg_lo,
-                                                           phase == 1 ? c->seg_n : 0);
+                                                           phase == 1 ? c->seg_n : 0, st.n_seg2, st.seg2_tiles);
   LAUNCH_CHECK("k_chain");
   return GBA_OK;
 }
@@ -847,7 +845,8 @@ extern "C" int gba_query(gba_ctx *c, gba_info *info) {
   info->n_active_tiles = st.n_slots;
   info->kernel_launches = c->launches;
   // sequential tile columns of the factorisation: one band segment's worth plus the closure block
-  info->chain_columns = (st.n_seg > 1 ? st.seg_tiles : 0) + (st.n_tiles - (st.n_seg > 1 ? st.n_seg * st.seg_tiles : 0));
+  info->chain_columns = (st.n_seg > 1 ? st.seg_tiles : 0) + st.seg2_tiles +
+                        (st.n_tiles - (st.n_seg > 1 ? st.n_seg * st.seg_tiles : 0) - st.n_seg2 * st.seg2_tiles);
   info->last_fail_code = st.last_fail;
   info->n_segments = st.n_seg;
   info->segment_tiles = st.seg_tiles;

@@ -41,6 +41,8 @@ struct Status {          // device -> host after the index build
   int cc_slot0;          // first slot of the closure x closure tiles (they are numbered last)
   int last_fail;         // code of the most recent failed factorisation: 1 pivot <= 0, 3 / 4 a pipeline watchdog
   int n_cc;              // keyframes whose out-degree exceeds tc_maxdeg: the CUDA-core Gram's work list (cc_list)
+  int n_seg2;            // second dissection level: separators factorised side by side at the head of the closure block
+  int seg2_tiles;        // tile columns of each of them
   unsigned long long gram_floats;  // total size of the per-frame Gram buffers
 };
 

@@ -48,9 +48,9 @@ struct SolverBufs {
 // ---------------------------------------------------------------------------------------------
 #define ORD_NC 8
 #define ORD_ALIGN 32  // pose positions; 32 * 6 rows = 3 tiles
-__global__ void __launch_bounds__(1024) k_order(BaParams p, int pos_cap) {
+__global__ void __launch_bounds__(1024) k_order(BaParams p, int pos_cap, int no_level2) {
   __shared__ int s_cnt[ORD_NC], s_reff[ORD_NC];
-  __shared__ int s_best, s_warp[32], s_nseg, s_seglen, s_hb, s_SL;
+  __shared__ int s_best, s_warp[32], s_nseg, s_seglen, s_hb, s_SL, s_nA, s_SLA;
   extern __shared__ unsigned int s_flagw[];  // one byte per pose: bit c = in C for candidate c
   unsigned char *s_flag = reinterpret_cast<unsigned char *>(s_flagw);
   const int tid = threadIdx.x, P = p.P;
@@ -105,7 +105,10 @@ __global__ void __launch_bounds__(1024) k_order(BaParams p, int pos_cap) {
       const int len = (nB - nsep + ns - 1) / ns;                               // real poses per segment
       const int SL = (ns == 1) ? len : (len + ORD_ALIGN - 1) / ORD_ALIGN * ORD_ALIGN;
       if ((ns == 1 ? nB : ns * SL) + nC + nsep > pos_cap) break;
-      const int chain = (6 * SL + GBA_NB - 1) / GBA_NB + (6 * (nC + nsep) + GBA_NB - 1) / GBA_NB;
+      // second level: every other separator is independent of the others once the segments are gone
+      const int nA = ns >= 4 ? ns / 2 : 0, SLA = (hb + ORD_ALIGN - 1) / ORD_ALIGN * ORD_ALIGN;
+      const int chain = (6 * SL + GBA_NB - 1) / GBA_NB + (nA ? 6 * SLA / GBA_NB : 0) +
+                        (6 * (nC + nsep - nA * hb) + GBA_NB - 1) / GBA_NB;
       if (chain < best_chain) {
         best_chain = chain;
         best_seg = ns;
@@ -116,10 +119,18 @@ __global__ void __launch_bounds__(1024) k_order(BaParams p, int pos_cap) {
     s_seglen = best_len;
     s_hb = hb;
     s_SL = (best_seg == 1) ? best_len : (best_len + ORD_ALIGN - 1) / ORD_ALIGN * ORD_ALIGN;
+    // separators 0, 2, 4, ... (between the segments 2m and 2m + 1) touch disjoint pairs of segments: once the
+    // segments are eliminated they are coupled only to their odd neighbours and to C -- they are factorised side
+    // by side as a second set of chains, in front of the dense rest (odd separators + C)
+    s_SLA = (hb + ORD_ALIGN - 1) / ORD_ALIGN * ORD_ALIGN;
+    s_nA = best_seg >= 4 ? best_seg / 2 : 0;
+    if (s_nA && best_seg * s_SL + s_nA * s_SLA + nC + (best_seg - 1 - s_nA) * hb > pos_cap) s_nA = 0;
+    if (no_level2) s_nA = 0;
   }
   __syncthreads();
-  const int bc = s_best, nseg = s_nseg, seglen = s_seglen, hb = s_hb, SL = s_SL;
+  const int bc = s_best, nseg = s_nseg, seglen = s_seglen, hb = s_hb, SL = s_SL, nA = s_nA, SLA = s_SLA;
   const int band_end = nseg * SL;  // first position of the closure block (nseg == 1: == nB)
+  const int core0 = band_end + nA * SLA;  // first position of the dense rest of the closure block
   // band index b of a non-C pose = number of non-C poses before it.  With nseg > 1 the band is
   // [seg 0: seglen][sep: hb][seg 1: seglen][sep: hb] ... ; separators go to the closure block.
   // Closure positions are handed out in temporal order: a second scan counts closure members.
@@ -152,7 +163,7 @@ __global__ void __launch_bounds__(1024) k_order(BaParams p, int pos_cap) {
     const int total_band = s_warp[31] + carry_band;
     __syncthreads();
     // is this pose a closure member (C or separator)?
-    int seg = 0, off = 0, clo = inC;
+    int seg = 0, off = 0, clo = inC, posA = -1;
     if (i < P && !inC) {
       const int bidx = bincl - 1;
       if (nseg > 1) {
@@ -162,8 +173,10 @@ __global__ void __launch_bounds__(1024) k_order(BaParams p, int pos_cap) {
           seg = nseg - 1;
           off = bidx - seg * (seglen + hb);
         }
-        if (off >= seglen && seg < nseg - 1) clo = 1;      // separator
-        else if (off >= SL) clo = 1;                        // overflow of the last segment
+        if (off >= seglen && seg < nseg - 1) {              // separator number seg
+          if (nA && (seg & 1) == 0) posA = band_end + (seg >> 1) * SLA + (off - seglen);
+          else clo = 1;
+        } else if (off >= SL) clo = 1;                      // overflow of the last segment
       } else
         off = bidx;
     }
@@ -190,7 +203,7 @@ __global__ void __launch_bounds__(1024) k_order(BaParams p, int pos_cap) {
     const int total_clo = s_warp[31] + carry_clo;
     __syncthreads();
     if (i < P) {
-      const int pos = clo ? band_end + cincl - 1 : seg * SL + off;
+      const int pos = posA >= 0 ? posA : (clo ? core0 + cincl - 1 : seg * SL + off);
       p.perm[i] = pos;
       p.iperm[pos] = i;
     }
@@ -198,8 +211,10 @@ __global__ void __launch_bounds__(1024) k_order(BaParams p, int pos_cap) {
     carry_clo = total_clo;
   }
   if (tid == 0) {
-    const int npos = band_end + carry_clo;
-    p.st->n_closure = carry_clo;
+    const int npos = core0 + carry_clo;
+    p.st->n_closure = carry_clo + nA * hb;
+    p.st->n_seg2 = nA;
+    p.st->seg2_tiles = nA ? 6 * SLA / GBA_NB : 0;
     p.st->band_w = cand[bc] > 1000000 ? -1 : cand[bc];
     p.st->n_seg = nseg;
     p.st->seg_tiles = (nseg == 1) ? 0 : 6 * SL / GBA_NB;
@@ -485,7 +500,8 @@ __device__ __forceinline__ void chain_wait(const unsigned *ptr, unsigned target,
 
 template <int SLAB>
 __global__ void __launch_bounds__(256, 2) k_chain(BaParams p, SolverBufs sb, int nseg, int segT, int total_spine,
-                                               int total_bulk, int n_spine, int phase, int seg_lo, int seg_n) {
+                                               int total_bulk, int n_spine, int phase, int seg_lo, int seg_n,
+                                               int nseg2, int segT2) {
   extern __shared__ double s_buf[];
   constexpr int SPLIT = GBA_NB / SLAB;
   __shared__ int s_task[5];  // role, kk, a, b, q
@@ -495,13 +511,21 @@ __global__ void __launch_bounds__(256, 2) k_chain(BaParams p, SolverBufs sb, int
   // segments [seg_lo, seg_lo + seg_n) only (their updates of closure tiles are unordered atomics), phase 2 = the
   // closure block alone, after the ranks have summed it (updates of band columns are then already in the tiles:
   // only the columns >= band count as predecessors).
+  // Three stages of columns: the band segments [0, band) side by side, then -- second dissection level -- nseg2
+  // separators [band, band2) side by side (segT2 tile columns each, k_order), then the dense rest [band2, nT) as
+  // one chain.  The closure block of the sharded solve is everything from `band` on.
   const int band = nseg > 1 ? nseg * segT : 0;
+  const int band2 = band + nseg2 * segT2;
   const int nsl = phase == 1 ? seg_n : (phase == 2 ? 0 : (nseg > 1 ? nseg : 0));  // band segments in play
   const int seg0 = phase == 1 ? seg_lo : 0;
-  const int nband = nsl * segT, clo = phase == 1 ? 0 : nT - band;  // sequence positions: band part, closure part
-  const int ninit = nsl > 0 ? nsl : 1;
+  const int nsA = phase == 1 ? 0 : nseg2;                                           // second-level chains in play
+  const int nband = nsl * segT, nbandA = nsA * segT2;                              // sequence positions of the two
+  const int clo = phase == 1 ? 0 : nT - band2;                                      // ... and of the dense rest
+  const int npos = nband + nbandA + clo;
+  const int ninit = nsl > 0 ? nsl : (nsA > 0 ? nsA : 1);
   const int minbit = phase == 2 ? band : 0;
-  const int atomic_from = (nsl > 0) ? band : (1 << 30);
+  // a tile beyond the end of the stage that updates it is shared by that stage's chains: atomic adds, no order
+  auto atomic_from_of = [&](int col) { return col < band ? band : (col < band2 ? band2 : (1 << 30)); };
   // Two ticket queues.  SPINE: the tasks every following column waits for -- P(k), the solve of the tile below
   // the diagonal and the update of the next diagonal tile -- served by the first n_spine CTAs only, so that
   // they never queue behind a wave of bulk updates.  BULK: everything else.  Inside each queue tickets are
@@ -521,13 +545,32 @@ __global__ void __launch_bounds__(256, 2) k_chain(BaParams p, SolverBufs sb, int
   }
   unsigned *ticket = spine ? &sb.ticket[0] : &sb.ticket[1];
   (void)total_spine; (void)total_bulk;  // upper bounds, used by the host to size the grid: the lists end with the sequence
-  auto seq = [&](int s_) { return s_ < nband ? (seg0 + s_ % nsl) * segT + s_ / nsl : band + (s_ - nband); };
-  auto next_of = [&](int s_, int kk_) {  // column whose potrf is issued inside block(kk_), or -1
+  auto seq = [&](int s_) {
+    if (s_ < nband) return (seg0 + s_ % nsl) * segT + s_ / nsl;
+    s_ -= nband;
+    if (s_ < nbandA) return band + (s_ % nsA) * segT2 + s_ / nsA;
+    return band2 + (s_ - nbandA);
+  };
+  // the potrf(s) issued inside block(kk_): the next column of the same chain (n = 1, chain = true), or -- at the
+  // last sequence position of a stage -- the first columns of all chains of the next stage (first, stride, n)
+  struct Next { int first, stride, n; bool chain; };
+  auto stage_heads = [&](int from_stage) {  // heads of the first non-empty stage after from_stage (0 band, 1 level 2)
+    Next r = {-1, 0, 0, false};
+    if (from_stage == 0 && nbandA > 0) { r.first = band; r.stride = segT2; r.n = nsA; }
+    else if (clo > 0) { r.first = band2; r.stride = 0; r.n = 1; }
+    return r;
+  };
+  auto next_of = [&](int s_, int kk_) {
+    Next r = {-1, 0, 0, false};
     if (s_ < nband) {
-      if (s_ / nsl + 1 < segT) return kk_ + 1;
-      return (s_ == nband - 1 && clo > 0) ? band : -1;
-    }
-    return kk_ + 1 < nT ? kk_ + 1 : -1;
+      if (s_ / nsl + 1 < segT) { r.first = kk_ + 1; r.n = 1; r.chain = true; }
+      else if (s_ == nband - 1) r = stage_heads(0);
+    } else if (s_ < nband + nbandA) {
+      const int sa = s_ - nband;
+      if (sa / nsA + 1 < segT2) { r.first = kk_ + 1; r.n = 1; r.chain = true; }
+      else if (sa == nbandA - 1) r = stage_heads(1);
+    } else if (kk_ + 1 < nT) { r.first = kk_ + 1; r.n = 1; r.chain = true; }
+    return r;
   };
   int spos = 0, base = spine ? ninit : 0;  // sequence position and first ticket of its block (thread 0 only)
   for (;;) {
@@ -537,17 +580,19 @@ __global__ void __launch_bounds__(256, 2) k_chain(BaParams p, SolverBufs sb, int
       int role = -1, kk = 0, a = 0, b = 0, q = 0;
       if (spine && t < ninit) {
         role = 0;
-        kk = nsl > 0 ? (seg0 + t) * segT : band;
+        kk = nsl > 0 ? (seg0 + t) * segT : (nsA > 0 ? band + t * segT2 : band2);
       } else {
-        while (spos < nband + clo) {  // tickets only grow: the walk over the sequence is amortised
-          const int col = seq(spos), nx = next_of(spos, col);
-          const int cnt = sb.colcnt[col], pairs = cnt * (cnt + 1) / 2, nxt = nx >= 0 ? 1 : 0;
+        while (spos < npos) {  // tickets only grow: the walk over the sequence is amortised
+          const int col = seq(spos);
+          const Next nx = next_of(spos, col);
+          const int cnt = sb.colcnt[col], pairs = cnt * (cnt + 1) / 2;
           // FUSED: the next column of the same chain sits right below the diagonal -- its factorisation applies
           // this column's update of its diagonal tile itself (dm_potrf64, Lprev) instead of waiting for an update task
-          const bool fz = cnt > 0 && nx == col + 1 && !(spos < nband && nx >= band) && sb.colrows[col * p.nT] == nx;
-          // spine block(k): T(k, 0, *)  [S(k, pair 0, *) unless fused]  P(next(k));
+          const bool fz = cnt > 0 && nx.chain && sb.colrows[col * p.nT] == nx.first;
+          // spine block(k): T(k, 0, *)  [S(k, pair 0, *) unless fused]  P(next(k)) ...;
           // bulk block(k): T(k, a >= 1, *)  S(k, other pairs)
-          const int n = spine ? (cnt > 0 ? (fz ? SPLIT : 2 * SPLIT) : 0) + nxt : (cnt > 0 ? SPLIT * (cnt - 1) + pairs - 1 : 0);
+          const int ncrit = cnt > 0 ? (fz ? SPLIT : 2 * SPLIT) : 0;
+          const int n = spine ? ncrit + nx.n : (cnt > 0 ? SPLIT * (cnt - 1) + pairs - 1 : 0);
           if (t < base + n) {
             int o = t - base;
             kk = col;
@@ -557,7 +602,7 @@ __global__ void __launch_bounds__(256, 2) k_chain(BaParams p, SolverBufs sb, int
               } else if (cnt > 0 && !fz && o < 2 * SPLIT) {
                 role = 2; a = 0; b = 0; q = o - SPLIT;
               } else {
-                role = 0; kk = nx; b = fz ? 1 : 0;
+                role = 0; kk = nx.first + (o - ncrit) * nx.stride; b = fz ? 1 : 0;
               }
             } else {
               if (o < SPLIT * (cnt - 1)) {
@@ -589,7 +634,8 @@ __global__ void __launch_bounds__(256, 2) k_chain(BaParams p, SolverBufs sb, int
     else if (role == 1) { ti = sb.colrows[kk * p.nT + a]; tj = kk; }
     else { ti = sb.colrows[kk * p.nT + a]; tj = sb.colrows[kk * p.nT + b]; }
     // closure tile updated from a band column: atomic, unordered
-    const bool unordered = role >= 2 && tj >= atomic_from && kk < band;  // (band columns only exist when nsl > 0)
+    const int atomic_from = atomic_from_of(kk);
+    const bool unordered = role >= 2 && tj >= atomic_from;
     if (tid < 32) {
       unsigned n = 0;
       if (tid < TS_WORDS && !unordered) {
@@ -631,12 +677,12 @@ __global__ void __launch_bounds__(256, 2) k_chain(BaParams p, SolverBufs sb, int
       __syncthreads();
       if (tid == 0) atomicAdd(const_cast<unsigned *>(updp), CHAIN_TDONE);
     } else if (role == 2) {
-      if (!failed) role_syrk<SLAB>(p, sb, kk, a, b, q, kk < band ? atomic_from : (1 << 30), s_buf);
+      if (!failed) role_syrk<SLAB>(p, sb, kk, a, b, q, atomic_from, s_buf);
       __threadfence();
       __syncthreads();
       if (tid == 0) atomicAdd(const_cast<unsigned *>(updp), 1u);
     } else {  // a whole tile at once: a quarter of the tasks, the L[j,kk] operand is loaded once instead of 4 times
-      if (!failed) role_syrk<GBA_NB>(p, sb, kk, a, b, 0, kk < band ? atomic_from : (1 << 30), s_buf);
+      if (!failed) role_syrk<GBA_NB>(p, sb, kk, a, b, 0, atomic_from, s_buf);
       __threadfence();
       __syncthreads();
       if (tid == 0) atomicAdd(const_cast<unsigned *>(updp), (unsigned)SPLIT);
