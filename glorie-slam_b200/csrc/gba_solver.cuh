@@ -44,7 +44,13 @@ struct SolverBufs {
 //     all tile columns to seg_tiles + closure tile columns.
 //  3. Segments start on a multiple of 32 pose positions (= 3 tiles exactly) so that no tile is
 //     shared by two segments; the unused positions are padding (unit diagonal).
-// Layout of positions: [segment 0 | pad][segment 1 | pad] ... [separators and C, temporal order].
+//  4. Second level (n_seg >= 4): the separators 0, 2, 4, ... touch disjoint pairs of segments, so once the
+//     segments are eliminated they are coupled only to the odd separators and to C.  Each becomes a chain of its
+//     own (padded to 32 positions) at the head of the closure block; the chains are factorised side by side like
+//     the segments, then the dense rest (odd separators + C) as one chain: seg_tiles + seg2_tiles + dense tile
+//     columns in sequence.
+// Layout of positions: [segment 0 | pad][segment 1 | pad] ... [separator 0 | pad][separator 2 | pad] ...
+//                      [odd separators and C, temporal order].
 // ---------------------------------------------------------------------------------------------
 #define ORD_NC 8
 #define ORD_ALIGN 32  // pose positions; 32 * 6 rows = 3 tiles
@@ -453,8 +459,10 @@ __device__ __forceinline__ unsigned ld_acquire(const unsigned *p) {
 // is ~28.  Here the updates of a column run underneath the critical path of the following ones.
 //
 // Column sequence: the band segments are independent, so their columns are interleaved (step t of
-// every segment, then step t+1, ...), followed by the closure columns in order:
-//     seq(s) = (s % nseg) * segT + s / nseg   for s < band = nseg * segT,      seq(s) = s   otherwise.
+// every segment, then step t+1, ...), followed by the second-level separators interleaved the same way, followed
+// by the dense rest of the closure block in order:
+//     seq(s) = (s % nseg) * segT + s / nseg   for s < band = nseg * segT,   likewise from band on for the nseg2
+//     separators of segT2 columns,   seq(s) = s   otherwise.
 // Tasks, in ticket order (P = potrf, T = trsm slab of 16 rows, S = update; pair 0 is the tile below the
 // diagonal, the one the next potrf waits for: it is updated in 4 slabs by 4 CTAs, the other tiles
 // whole).  next(k) is k+1 inside a segment and inside the closure block, the first closure column
