@@ -269,7 +269,7 @@ def test_tensor_core_gram_matches_cuda_core_gram(n, ht, wd, monkeypatch):
     assert get_array(r.ctx, _gba.GET_WATCHDOG, (256,), np.int32)[0] == 0  # no pipeline wait ever expired
 
 
-@pytest.mark.parametrize("n,e,r", [(60, 700, 3), (260, 4200, 8)])
+@pytest.mark.parametrize("n,e,r", [(60, 700, 3), (260, 4200, 8), (640, 3860, 3)])
 def test_task_graph_factorisation_matches_oracle(n, e, r):
     """k_chain (the whole factorisation as one dependency graph of tile tasks, several band segments and a
     closure block in the larger graph) and k_back against the dense fp64 Cholesky of the oracle"""
@@ -281,6 +281,7 @@ def test_task_graph_factorisation_matches_oracle(n, e, r):
         assert r1.info.chain_columns < r1.info.n_tiles  # nested dissection shortened the chain
         assert r1.info.n_segments > 1
     assert r1.info.kernel_launches < 60
+    print("n %d: %d tiles, %d segments x %d tiles, chain of %d tile columns" % (n, r1.info.n_tiles, r1.info.n_segments, r1.info.segment_tiles, r1.info.chain_columns))
     o = oracle.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj, g.t0, g.t1,
                   g.iters, g.lm, g.ep, precision="f64")
     assert rel(sign_normalise(r1.poses), sign_normalise(o.poses)) < STATE_RTOL
